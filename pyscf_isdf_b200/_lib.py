@@ -1,0 +1,211 @@
+"""ctypes binding of libisdf_b200.so (the C-ABI in include/isdf_b200.h).
+
+Mirrors how the reference reaches its native AO kernel
+(numpy.ctypeslib.load_library + raw pointers,
+pyscf/pbc/gto/eval_gto.py:139-151, pyscf/lib/misc.py:91-103).  There is no
+CPU fallback: if the CUDA library is missing or no B200 is visible, every
+entry point raises.
+"""
+import ctypes
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libisdf_b200.so')
+
+c_int, c_ll, c_dbl, c_vp, c_sz = (ctypes.c_int, ctypes.c_longlong, ctypes.c_double,
+                                  ctypes.c_void_p, ctypes.c_size_t)
+
+# name -> (restype, argtypes); must list every symbol declared in include/isdf_b200.h
+SIGNATURES = {
+    'isdf_create': (c_int, [c_int, ctypes.POINTER(c_vp)]),
+    'isdf_destroy': (c_int, [c_vp]),
+    'isdf_set_stream': (c_int, [c_vp, c_vp]),
+    'isdf_last_error': (ctypes.c_char_p, []),
+    'isdf_num_sms': (c_int, [c_vp]),
+    'isdf_launch_count': (c_ll, [c_vp, c_int]),
+    'isdf_stage_time_ms': (c_int, [c_vp, c_int, ctypes.POINTER(ctypes.c_float)]),
+    'isdf_eval_ao': (c_int, [c_vp, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp,
+                             c_vp, c_int, c_vp, c_ll, c_ll, c_vp, c_ll]),
+    'isdf_select_ip_ws_bytes': (c_sz, [c_int, c_ll, c_int]),
+    'isdf_select_ip': (c_int, [c_vp, c_vp, c_int, c_ll, c_ll, c_int, c_dbl, c_vp, c_ll,
+                               c_vp, c_vp, c_vp, c_vp, c_sz]),
+    'isdf_fit_aux_ws_bytes': (c_sz, [c_int, c_ll, c_int]),
+    'isdf_fit_aux': (c_int, [c_vp, c_vp, c_int, c_ll, c_ll, c_vp, c_int, c_vp, c_ll, c_vp, c_sz]),
+    'isdf_fit_aux_from_factor': (c_int, [c_vp, c_vp, c_ll, c_ll, c_vp, c_int, c_vp, c_sz]),
+    'isdf_build_W_ws_bytes': (c_sz, [c_int, c_vp]),
+    'isdf_build_W': (c_int, [c_vp, c_vp, c_int, c_ll, c_vp, c_vp, c_vp, c_vp, c_ll, c_vp, c_sz]),
+    'isdf_coulomb_apply': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_vp, c_vp, c_ll, c_vp, c_sz]),
+    'isdf_get_jk_ws_bytes': (c_sz, [c_int, c_int]),
+    'isdf_get_jk': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int,
+                            c_vp, c_vp, c_vp, c_sz]),
+    'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
+                           c_vp, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_int, c_int]),
+    'isdf_gather_cols': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_int, c_vp, c_ll]),
+}
+
+STAGE_AO, STAGE_SELECT, STAGE_FIT, STAGE_COULOMB, STAGE_JK, STAGE_FFT, STAGE_GEMM = range(7)
+
+_lib = None
+
+
+def load_library():
+    """Load libisdf_b200.so and declare prototypes; raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            'libisdf_b200.so not found at %s: build it with '
+            '`python -c "import __graft_entry__ as g; g.build()"` '
+            '(there is no CPU fallback for the ISDF hot path)' % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = load_library().isdf_last_error()
+        raise RuntimeError('libisdf_b200 error %d: %s' % (rc, msg.decode() if msg else '?'))
+
+
+def hptr(a):
+    """host pointer of a C-contiguous numpy array"""
+    assert a.flags.c_contiguous
+    return a.ctypes.data_as(c_vp)
+
+
+def pad8(n):
+    return (int(n) + 7) // 8 * 8
+
+
+class Handle:
+    """Owns one isdf_handle bound to one GPU (one process per GPU)."""
+
+    def __init__(self, device=None):
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError('pyscf_isdf_b200 needs a CUDA device (B200, sm_100a); '
+                               'there is no CPU fallback')
+        self.lib = load_library()
+        if device is None:
+            device = torch.cuda.current_device()
+        self.device = int(device)
+        self.torch_device = torch.device('cuda', self.device)
+        h = c_vp()
+        check(self.lib.isdf_create(self.device, ctypes.byref(h)))
+        self.h = h
+        with torch.cuda.device(self.device):
+            self.stream = torch.cuda.current_stream()
+        check(self.lib.isdf_set_stream(self.h, c_vp(self.stream.cuda_stream)))
+
+    def __del__(self):
+        try:
+            if getattr(self, 'h', None):
+                self.lib.isdf_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    # -- helpers ---------------------------------------------------------------
+    def empty(self, *shape, dtype=None):
+        import torch
+        return torch.empty(*shape, dtype=dtype or torch.float64, device=self.torch_device)
+
+    def workspace(self, nbytes):
+        import torch
+        return torch.empty(int(nbytes), dtype=torch.uint8, device=self.torch_device)
+
+    def stage_ms(self, stage):
+        out = ctypes.c_float()
+        check(self.lib.isdf_stage_time_ms(self.h, stage, ctypes.byref(out)))
+        return out.value
+
+    def launches(self):
+        return (self.lib.isdf_launch_count(self.h, 0), self.lib.isdf_launch_count(self.h, 1))
+
+    # -- stage wrappers (thin; shapes documented in include/isdf_b200.h) ------
+    def eval_ao(self, atm, bas, env, a, mesh, Ls, rcut, g0, g1, phi, ldphi):
+        atm = np.ascontiguousarray(atm, dtype=np.int32)
+        bas = np.ascontiguousarray(bas, dtype=np.int32)
+        env = np.ascontiguousarray(env, dtype=np.float64)
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        mesh = np.ascontiguousarray(mesh, dtype=np.int32)
+        Ls = np.ascontiguousarray(Ls, dtype=np.float64)
+        rcut = np.ascontiguousarray(rcut, dtype=np.float64)
+        check(self.lib.isdf_eval_ao(self.h, hptr(atm), len(atm), hptr(bas), len(bas), hptr(env), len(env),
+                                    hptr(a), hptr(mesh), hptr(Ls), len(Ls), hptr(rcut),
+                                    g0, g1, c_vp(phi.data_ptr()), ldphi))
+
+    def select_ip(self, phi, nao, ng, ldphi, npts, tol, Lt, ldl):
+        nbytes = self.lib.isdf_select_ip_ws_bytes(nao, ng, npts)
+        ws = self.workspace(nbytes)
+        ip = np.zeros(npts, dtype=np.int64)
+        resid = np.zeros(npts, dtype=np.float64)
+        rank = c_int(0)
+        check(self.lib.isdf_select_ip(self.h, c_vp(phi.data_ptr()), nao, ng, ldphi, npts, float(tol),
+                                      c_vp(Lt.data_ptr()), ldl, hptr(ip), hptr(resid),
+                                      ctypes.byref(rank), c_vp(ws.data_ptr()), nbytes))
+        r = rank.value
+        return ip[:r].copy(), resid[:r].copy()
+
+    def fit_aux(self, phi, nao, ng, ldphi, ip, zeta, ldz):
+        ip = np.ascontiguousarray(ip, dtype=np.int64)
+        nbytes = self.lib.isdf_fit_aux_ws_bytes(nao, ng, len(ip))
+        ws = self.workspace(nbytes)
+        check(self.lib.isdf_fit_aux(self.h, c_vp(phi.data_ptr()), nao, ng, ldphi, hptr(ip), len(ip),
+                                    c_vp(zeta.data_ptr()), ldz, c_vp(ws.data_ptr()), nbytes))
+
+    def fit_aux_from_factor(self, Lt, ldl, ng, ip):
+        ip = np.ascontiguousarray(ip, dtype=np.int64)
+        nbytes = self.lib.isdf_fit_aux_ws_bytes(1, ng, len(ip))
+        ws = self.workspace(nbytes)
+        check(self.lib.isdf_fit_aux_from_factor(self.h, c_vp(Lt.data_ptr()), ldl, ng, hptr(ip), len(ip),
+                                                c_vp(ws.data_ptr()), nbytes))
+
+    def build_W(self, zeta, npts, ldz, mesh, a, W, V=None, ldv=0):
+        mesh = np.ascontiguousarray(mesh, dtype=np.int32)
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        nbytes = self.lib.isdf_build_W_ws_bytes(npts, hptr(mesh))
+        ws = self.workspace(nbytes)
+        check(self.lib.isdf_build_W(self.h, c_vp(zeta.data_ptr()), npts, ldz, hptr(mesh), hptr(a),
+                                    c_vp(W.data_ptr()), c_vp(V.data_ptr()) if V is not None else None, ldv,
+                                    c_vp(ws.data_ptr()), nbytes))
+
+    def coulomb_apply(self, vin, ldin, nvec, mesh, a, vout, ldout, ws_bytes=None):
+        mesh = np.ascontiguousarray(mesh, dtype=np.int32)
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        ngh = int(mesh[0]) * int(mesh[1]) * (int(mesh[2]) // 2 + 1)
+        if ws_bytes is None:
+            ws_bytes = 16 * ngh * min(nvec, 64)
+        ws = self.workspace(ws_bytes)
+        check(self.lib.isdf_coulomb_apply(self.h, c_vp(vin.data_ptr()), ldin, nvec, hptr(mesh), hptr(a),
+                                          c_vp(vout.data_ptr()), ldout, c_vp(ws.data_ptr()), ws_bytes))
+
+    def get_jk(self, X, W, dm, nset, nao, npts, with_j, with_k, vj, vk, ws=None):
+        nbytes = self.lib.isdf_get_jk_ws_bytes(nao, npts)
+        if ws is None:
+            ws = self.workspace(nbytes)
+        check(self.lib.isdf_get_jk(self.h, c_vp(X.data_ptr()), c_vp(W.data_ptr()), c_vp(dm.data_ptr()),
+                                   nset, nao, npts, int(with_j), int(with_k),
+                                   c_vp(vj.data_ptr()) if vj is not None else None,
+                                   c_vp(vk.data_ptr()) if vk is not None else None,
+                                   c_vp(ws.data_ptr()), ws.numel()))
+
+    def dgemm(self, M, N, K, A, lda, a_kmajor, B, ldb, b_kmajor, C, ldc,
+              Cin=None, ldcin=0, E=None, lde=0, alpha=1.0, neg=0, epi=0, upper_only=0):
+        check(self.lib.isdf_dgemm(self.h, M, N, K, c_vp(A.data_ptr()), lda, int(a_kmajor),
+                                  c_vp(B.data_ptr()), ldb, int(b_kmajor), c_vp(C.data_ptr()), ldc,
+                                  c_vp(Cin.data_ptr()) if Cin is not None else None, ldcin,
+                                  c_vp(E.data_ptr()) if E is not None else None, lde,
+                                  float(alpha), int(neg), int(epi), int(upper_only)))
+
+    def gather_cols(self, src, ldin, nrows, idx, out, ldout):
+        idx = np.ascontiguousarray(idx, dtype=np.int64)
+        check(self.lib.isdf_gather_cols(self.h, c_vp(src.data_ptr()), ldin, nrows, hptr(idx), len(idx),
+                                        c_vp(out.data_ptr()), ldout))

@@ -1,0 +1,102 @@
+// Handle management, error reporting and the generic GEMM entry point.
+#include "common.cuh"
+#include "../../include/isdf_b200.h"
+#include <cstdarg>
+
+static thread_local char g_err[1024] = "";
+
+void isdf_set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* isdf_last_error(void) { return g_err; }
+
+extern "C" int isdf_create(int device, isdf_handle** out)
+{
+    ARG_CHECK(out != nullptr);
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    ARG_CHECK(device >= 0 && device < ndev);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        isdf_set_error("isdf_b200 is built for sm_100a only; device %d is sm_%d%d",
+                       device, prop.major, prop.minor);
+        return ISDF_ERR_ARG;
+    }
+    isdf_handle* h = new isdf_handle();
+    memset(h, 0, sizeof(*h));
+    h->device = device;
+    h->num_sms = prop.multiProcessorCount;
+    h->stream = 0;
+    for (int i = 0; i < NSTAGE_TIMERS; ++i) {
+        CUDA_TRY(cudaEventCreate(&h->ev0[i]));
+        CUDA_TRY(cudaEventCreate(&h->ev1[i]));
+    }
+    CUDA_TRY(cudaMalloc(&h->d_small, 1 << 20));
+    CUDA_TRY(cudaMallocHost(&h->h_pinned, 1 << 16));
+    *out = h;
+    return ISDF_OK;
+}
+
+extern "C" int isdf_destroy(isdf_handle* h)
+{
+    if (!h) return ISDF_OK;
+    cudaSetDevice(h->device);
+    for (int i = 0; i < NSTAGE_TIMERS; ++i) {
+        cudaEventDestroy(h->ev0[i]);
+        cudaEventDestroy(h->ev1[i]);
+    }
+    cudaFree(h->d_small);
+    cudaFreeHost(h->h_pinned);
+    delete h;
+    return ISDF_OK;
+}
+
+extern "C" int isdf_set_stream(isdf_handle* h, void* stream)
+{
+    ARG_CHECK(h != nullptr);
+    h->stream = (cudaStream_t)stream;
+    return ISDF_OK;
+}
+
+extern "C" int isdf_num_sms(isdf_handle* h) { return h ? h->num_sms : 0; }
+
+extern "C" long long isdf_launch_count(isdf_handle* h, int which)
+{
+    if (!h) return 0;
+    return which == 0 ? h->gemm_launches : h->other_launches;
+}
+
+extern "C" int isdf_stage_time_ms(isdf_handle* h, int stage, float* out)
+{
+    ARG_CHECK(h && out && stage >= 0 && stage < NSTAGE_TIMERS);
+    if (!h->ev_used[stage]) { *out = -1.f; return ISDF_OK; }
+    CUDA_TRY(cudaEventSynchronize(h->ev1[stage]));
+    CUDA_TRY(cudaEventElapsedTime(out, h->ev0[stage], h->ev1[stage]));
+    return ISDF_OK;
+}
+
+extern "C" int isdf_dgemm(isdf_handle* h, int M, int N, int K,
+                          const double* A, long long lda, int a_kmajor,
+                          const double* B, long long ldb, int b_kmajor,
+                          double* C, long long ldc,
+                          const double* Cin, long long ldcin,
+                          const double* E, long long lde,
+                          double alpha, int neg, int epi, int upper_only)
+{
+    ARG_CHECK(h != nullptr);
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.A = A; p.lda = lda; p.a_kmajor = a_kmajor;
+    p.B = B; p.ldb = ldb; p.b_kmajor = b_kmajor;
+    p.C = C; p.ldc = ldc; p.Cin = Cin; p.ldcin = ldcin;
+    p.E = E; p.lde = lde; p.alpha = alpha; p.neg = neg; p.epi = epi;
+    p.upper_only = upper_only;
+    return gemm_launch(h, p);
+}

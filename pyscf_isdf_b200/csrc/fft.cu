@@ -1,0 +1,498 @@
+// Stage 4: batched 3-D real FFT of the auxiliary functions fused with the
+// Coulomb kernel 4 pi/|G|^2, and the Coulomb metric W.
+//
+// Conventions restated from the reference: forward DFT unnormalised, inverse
+// carries 1/N (pyscf/pbc/tools/pbc.py:149-211); G vectors in FFT index order
+// (pyscf/pbc/gto/cell.py:523-596); coulG = 4 pi/|G|^2 with G=0 -> 0
+// (pyscf/pbc/tools/pbc.py:304,352-356).
+//
+// Hand-written mixed-radix Stockham FFTs in shared memory (radix 4/2/3/5/7 and
+// a direct DFT for any other prime factor, so odd and prime meshes such as
+// 35^3 or 71^3 work).  A 3-D transform is three passes, each reading and
+// writing coalesced row segments:
+//   z: real lines -> half spectrum (nz/2+1)          [R2C]
+//   y: columns of every (x) plane
+//   x: columns of the whole [nx, ny*nzh] matrix, with the Coulomb-kernel
+//      multiply fused (and, for V, the inverse x transform in the same kernel).
+#include "common.cuh"
+#include "../../include/isdf_b200.h"
+#include <vector>
+#include <cmath>
+#include <algorithm>
+
+namespace {
+
+constexpr int FFT_THREADS = 256;
+constexpr int MAX_RAD = 16;
+constexpr int BIG_RADIX_MAX = 256;
+
+struct FftPlan {
+    int n, nrad;
+    int rad[MAX_RAD];
+    const double2* tw;      // exp(-2 pi i k / n), k < n
+};
+
+__device__ __forceinline__ double2 cmul(double2 a, double2 b)
+{
+    return make_double2(fma(a.x, b.x, -a.y * b.y), fma(a.x, b.y, a.y * b.x));
+}
+__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
+
+template <int SIGN>
+__device__ __forceinline__ double2 twid(const double2* tw, int idx)
+{
+    double2 w = tw[idx];
+    if (SIGN > 0) w.y = -w.y;
+    return w;
+}
+
+// In-place small DFT of u[0..R) (R <= 7), sign SIGN
+template <int R, int SIGN>
+__device__ __forceinline__ void dft_small(double2* u, const double2* tw, int n)
+{
+    if (R == 2) {
+        const double2 a = u[0], b = u[1];
+        u[0] = cadd(a, b); u[1] = csub(a, b);
+    } else if (R == 4) {
+        const double2 s02 = cadd(u[0], u[2]), d02 = csub(u[0], u[2]);
+        const double2 s13 = cadd(u[1], u[3]), d13 = csub(u[1], u[3]);
+        // W = SIGN * i ;  W*d13 = SIGN * (-d13.y, d13.x)
+        const double2 wd = make_double2(-SIGN * d13.y, SIGN * d13.x);
+        u[0] = cadd(s02, s13); u[2] = csub(s02, s13);
+        u[1] = cadd(d02, wd);  u[3] = csub(d02, wd);
+    } else if (R == 3) {
+        const double2 t = cadd(u[1], u[2]);
+        const double2 m = make_double2(u[0].x - 0.5 * t.x, u[0].y - 0.5 * t.y);
+        const double c = 0.86602540378443864676 * SIGN;
+        const double2 d = csub(u[1], u[2]);
+        const double2 s = make_double2(-c * d.y, c * d.x);       // SIGN * i * (sqrt3/2) * d
+        u[0] = cadd(u[0], t); u[1] = cadd(m, s); u[2] = csub(m, s);
+    } else {
+        double2 v[R];
+        const int step = n / R;
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            double2 acc = u[0];
+#pragma unroll
+            for (int s = 1; s < R; ++s) acc = cadd(acc, cmul(u[s], twid<SIGN>(tw, ((q * s) % R) * step)));
+            v[q] = acc;
+        }
+#pragma unroll
+        for (int q = 0; q < R; ++q) u[q] = v[q];
+    }
+}
+
+template <int R, int SIGN>
+__device__ __forceinline__ void stage_small(const double2* __restrict__ in, double2* __restrict__ out,
+                                            const FftPlan& pl, int p, int nlines, int line_stride,
+                                            int elem_stride, bool line_fast)
+{
+    const int n = pl.n, t = n / R;
+    const int tws = n / (p * R);
+    for (int idx = threadIdx.x; idx < nlines * t; idx += blockDim.x) {
+        int line, i;
+        if (line_fast) { i = idx / nlines; line = idx - i * nlines; }
+        else { line = idx / t; i = idx - line * t; }
+        const int k = i % p;
+        const int j = (i - k) * R + k;
+        const double2* src = in + (long long)line * line_stride;
+        double2* dst = out + (long long)line * line_stride;
+        double2 u[R];
+#pragma unroll
+        for (int q = 0; q < R; ++q) {
+            double2 x = src[(i + q * t) * elem_stride];
+            if (q > 0 && k > 0) x = cmul(x, twid<SIGN>(pl.tw, q * k * tws));
+            u[q] = x;
+        }
+        dft_small<R, SIGN>(u, pl.tw, n);
+#pragma unroll
+        for (int q = 0; q < R; ++q) dst[(j + q * p) * elem_stride] = u[q];
+    }
+}
+
+template <int SIGN>
+__device__ void stage_big(const double2* __restrict__ in, double2* __restrict__ out, const FftPlan& pl,
+                          int r, int p, int nlines, int line_stride, int elem_stride, bool line_fast)
+{
+    const int n = pl.n, t = n / r;
+    const int tws = n / (p * r), step = n / r;
+    // one output element per work item: direct O(r^2) DFT for a large prime factor
+    for (int idx = threadIdx.x; idx < nlines * t * r; idx += blockDim.x) {
+        int line, rest;
+        if (line_fast) { rest = idx / nlines; line = idx - rest * nlines; }
+        else { line = idx / (t * r); rest = idx - line * (t * r); }
+        const int q = rest / t, i = rest - q * t;
+        const int k = i % p;
+        const int j = (i - k) * r + k;
+        const double2* src = in + (long long)line * line_stride;
+        double2 acc = make_double2(0.0, 0.0);
+        for (int s = 0; s < r; ++s) {
+            double2 x = src[(i + s * t) * elem_stride];
+            // twiddle w^(s*k*tws) * W_r^(q*s)
+            const int e = (int)(((long long)s * k * tws + (long long)((q * s) % r) * step) % n);
+            x = cmul(x, twid<SIGN>(pl.tw, e));
+            acc = cadd(acc, x);
+        }
+        out[(long long)line * line_stride + (j + q * p) * elem_stride] = acc;
+    }
+}
+
+// FFT of `nlines` lines living in shared memory; returns the buffer holding the result.
+template <int SIGN>
+__device__ double2* fft_smem(double2* a, double2* b, const FftPlan& pl, int nlines,
+                             int line_stride, int elem_stride, bool line_fast)
+{
+    int p = 1;
+    for (int s = 0; s < pl.nrad; ++s) {
+        const int r = pl.rad[s];
+        switch (r) {
+        case 2: stage_small<2, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 3: stage_small<3, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 4: stage_small<4, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 5: stage_small<5, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 7: stage_small<7, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        default: stage_big<SIGN>(a, b, pl, r, p, nlines, line_stride, elem_stride, line_fast); break;
+        }
+        __syncthreads();
+        double2* tmp = a; a = b; b = tmp;
+        p *= r;
+    }
+    return a;
+}
+
+struct CoulGeom {
+    int mesh[3];
+    int nzh;
+    double b[9];        // reciprocal vectors (rows)
+    double scale;       // multiplies the kernel (1/ng for V)
+};
+
+__device__ __forceinline__ double coulG_at(const CoulGeom& g, int ix, int iy, int iz)
+{
+    const int fx = ix < (g.mesh[0] + 1) / 2 ? ix : ix - g.mesh[0];
+    const int fy = iy < (g.mesh[1] + 1) / 2 ? iy : iy - g.mesh[1];
+    const int fz = iz < (g.mesh[2] + 1) / 2 ? iz : iz - g.mesh[2];
+    const double gx = fx * g.b[0] + fy * g.b[3] + fz * g.b[6];
+    const double gy = fx * g.b[1] + fy * g.b[4] + fz * g.b[7];
+    const double gz = fx * g.b[2] + fy * g.b[5] + fz * g.b[8];
+    const double g2 = gx * gx + gy * gy + gz * gz;
+    return (fx == 0 && fy == 0 && fz == 0) ? 0.0 : 4.0 * 3.14159265358979323846 / g2;
+}
+
+// ---- z pass: real lines -> half spectrum ------------------------------------
+__global__ void __launch_bounds__(FFT_THREADS)
+fft_z_r2c_kernel(const double* __restrict__ in, long long ldin, double2* __restrict__ out, long long ldout,
+                 FftPlan pl, int nlines, int LB)
+{
+    extern __shared__ double2 sm[];
+    const int nz = pl.n, nzh = nz / 2 + 1;
+    double2* a = sm; double2* b = sm + LB * nz;
+    const int line0 = blockIdx.x * LB;
+    const int nl = min(LB, nlines - line0);
+    const double* src = in + (long long)blockIdx.y * ldin + (long long)line0 * nz;
+    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) a[idx] = make_double2(src[idx], 0.0);
+    __syncthreads();
+    double2* r = fft_smem<-1>(a, b, pl, nl, nz, 1, false);
+    double2* dst = out + (long long)blockIdx.y * ldout + (long long)line0 * nzh;
+    for (int idx = threadIdx.x; idx < nl * nzh; idx += blockDim.x) {
+        const int line = idx / nzh, e = idx - line * nzh;
+        dst[idx] = r[line * nz + e];
+    }
+}
+
+// ---- z pass: half spectrum -> real lines (unnormalised inverse) ----------------
+__global__ void __launch_bounds__(FFT_THREADS)
+fft_z_c2r_kernel(const double2* __restrict__ in, long long ldin, double* __restrict__ out, long long ldout,
+                 FftPlan pl, int nlines, int LB)
+{
+    extern __shared__ double2 sm[];
+    const int nz = pl.n, nzh = nz / 2 + 1;
+    double2* a = sm; double2* b = sm + LB * nz;
+    const int line0 = blockIdx.x * LB;
+    const int nl = min(LB, nlines - line0);
+    const double2* src = in + (long long)blockIdx.y * ldin + (long long)line0 * nzh;
+    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) {
+        const int line = idx / nz, e = idx - line * nz;
+        double2 v;
+        if (e < nzh) v = src[line * nzh + e];
+        else { v = src[line * nzh + (nz - e)]; v.y = -v.y; }
+        a[idx] = v;
+    }
+    __syncthreads();
+    double2* r = fft_smem<+1>(a, b, pl, nl, nz, 1, false);
+    double* dst = out + (long long)blockIdx.y * ldout + (long long)line0 * nz;
+    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) dst[idx] = r[idx].x;
+}
+
+// ---- column pass over a row-major [n, ncols] complex matrix --------------------
+// MODE 0: forward            MODE 3: inverse (unnormalised)
+// MODE 1: forward, then multiply by sqrt(w * coulG)   (x pass of the W build)
+// MODE 2: forward, multiply by coulG*scale, inverse   (x pass of the V build)
+template <int MODE>
+__global__ void __launch_bounds__(FFT_THREADS)
+fft_cols_kernel(double2* __restrict__ data, long long vec_stride, long long outer_stride,
+                FftPlan pl, int ncols, int CH, CoulGeom geo)
+{
+    extern __shared__ double2 sm[];
+    const int n = pl.n;
+    double2* a = sm; double2* b = sm + n * CH;
+    const int c0 = blockIdx.x * CH;
+    const int nc = min(CH, ncols - c0);
+    double2* base = data + (long long)blockIdx.z * vec_stride + (long long)blockIdx.y * outer_stride + c0;
+    for (int idx = threadIdx.x; idx < n * nc; idx += blockDim.x) {
+        const int i = idx / nc, c = idx - i * nc;
+        a[i * CH + c] = base[(long long)i * ncols + c];
+    }
+    __syncthreads();
+    double2* r;
+    if (MODE == 3) r = fft_smem<+1>(a, b, pl, nc, 1, CH, true);
+    else r = fft_smem<-1>(a, b, pl, nc, 1, CH, true);
+    if (MODE == 1 || MODE == 2) {
+        for (int idx = threadIdx.x; idx < n * nc; idx += blockDim.x) {
+            const int i = idx / nc, c = idx - i * nc;
+            const int col = c0 + c;
+            const int iy = col / geo.nzh, iz = col - iy * geo.nzh;
+            double f = coulG_at(geo, i, iy, iz);
+            if (MODE == 1) {
+                const bool self = (iz == 0) || (2 * iz == geo.mesh[2]);
+                f = sqrt(self ? f : 2.0 * f);
+            } else f *= geo.scale;
+            double2 v = r[i * CH + c];
+            v.x *= f; v.y *= f;
+            r[i * CH + c] = v;
+        }
+        __syncthreads();
+        if (MODE == 2) {
+            double2* other = (r == a) ? b : a;
+            r = fft_smem<+1>(r, other, pl, nc, 1, CH, true);
+        }
+    }
+    for (int idx = threadIdx.x; idx < n * nc; idx += blockDim.x) {
+        const int i = idx / nc, c = idx - i * nc;
+        base[(long long)i * ncols + c] = r[i * CH + c];
+    }
+}
+
+__global__ void symmetrize_upper_kernel(double* __restrict__ W, long long ld, int n)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y * blockDim.y + threadIdx.y;
+    if (i < n && j < n && j < i) W[(long long)i * ld + j] = W[(long long)j * ld + i];
+}
+
+// ---- host side -----------------------------------------------------------------
+int factorize(int n, int* rad)
+{
+    int k = 0;
+    const int small[5] = {4, 2, 3, 5, 7};
+    for (int f : small) while (n % f == 0 && k < MAX_RAD) { rad[k++] = f; n /= f; }
+    for (int p = 11; n > 1; p += 2) while (n % p == 0) { if (k >= MAX_RAD || p > BIG_RADIX_MAX) return -1; rad[k++] = p; n /= p; }
+    return k;
+}
+
+struct Plans {
+    FftPlan ax[3];
+    double2* d_tw;
+};
+
+int make_plans(isdf_handle* h, const int* mesh, Plans& P)
+{
+    std::vector<double2> tw;
+    size_t off[3];
+    for (int d = 0; d < 3; ++d) {
+        const int n = mesh[d];
+        ARG_CHECK(n >= 1 && n <= 1024);
+        P.ax[d].n = n;
+        P.ax[d].nrad = factorize(n, P.ax[d].rad);
+        if (P.ax[d].nrad < 0) { isdf_set_error("mesh size %d has an unsupported prime factor", n); return ISDF_ERR_ARG; }
+        off[d] = tw.size();
+        for (int k = 0; k < n; ++k) {
+            const long double ang = -2.0L * 3.141592653589793238462643383279502884L * k / n;
+            tw.push_back(make_double2((double)cosl(ang), (double)sinl(ang)));
+        }
+    }
+    CUDA_TRY(cudaMallocAsync((void**)&P.d_tw, sizeof(double2) * tw.size(), h->stream));
+    CUDA_TRY(cudaMemcpyAsync(P.d_tw, tw.data(), sizeof(double2) * tw.size(), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    for (int d = 0; d < 3; ++d) P.ax[d].tw = P.d_tw + off[d];
+    return ISDF_OK;
+}
+
+template <typename K>
+int set_smem(K kern, size_t smem)
+{
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    return ISDF_OK;
+}
+
+void fill_geom(CoulGeom& g, const int* mesh, const double* a, double scale)
+{
+    // reciprocal vectors b = 2 pi inv(a^T): rows b_i with a_i . b_j = 2 pi delta_ij
+    const double a00 = a[0], a01 = a[1], a02 = a[2], a10 = a[3], a11 = a[4], a12 = a[5], a20 = a[6], a21 = a[7], a22 = a[8];
+    const double det = a00 * (a11 * a22 - a12 * a21) - a01 * (a10 * a22 - a12 * a20) + a02 * (a10 * a21 - a11 * a20);
+    const double f = 2.0 * 3.14159265358979323846 / det;
+    // b_0 = 2pi (a1 x a2)/det, etc.
+    g.b[0] = f * (a11 * a22 - a12 * a21); g.b[1] = f * (a12 * a20 - a10 * a22); g.b[2] = f * (a10 * a21 - a11 * a20);
+    g.b[3] = f * (a21 * a02 - a22 * a01); g.b[4] = f * (a22 * a00 - a20 * a02); g.b[5] = f * (a20 * a01 - a21 * a00);
+    g.b[6] = f * (a01 * a12 - a02 * a11); g.b[7] = f * (a02 * a10 - a00 * a12); g.b[8] = f * (a00 * a11 - a01 * a10);
+    for (int d = 0; d < 3; ++d) g.mesh[d] = mesh[d];
+    g.nzh = mesh[2] / 2 + 1;
+    g.scale = scale;
+}
+
+int pick_lb(int n, size_t budget) { return (int)std::max<size_t>(1, std::min<size_t>(64, budget / (2 * sizeof(double2) * n))); }
+
+// forward 3-D transform of nvec real vectors into half spectra (spec[vec*lds + ...]);
+// xmode selects what the x pass fuses (0 plain, 1 sqrt(w coulG), 2 coulG*scale + inverse x)
+int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double* in, long long ldin,
+                   int nvec, double2* spec, long long lds, int xmode, const CoulGeom& geo)
+{
+    const int nx = mesh[0], ny = mesh[1], nz = mesh[2], nzh = nz / 2 + 1;
+    cudaStream_t s = h->stream;
+    const size_t budget = 96 * 1024;
+    {
+        const int LB = pick_lb(nz, budget);
+        const size_t smem = 2 * sizeof(double2) * LB * nz;
+        int rc; if ((rc = set_smem(fft_z_r2c_kernel, smem))) return rc;
+        dim3 grid((nx * ny + LB - 1) / LB, nvec);
+        fft_z_r2c_kernel<<<grid, FFT_THREADS, smem, s>>>(in, ldin, spec, lds, P.ax[2], nx * ny, LB);
+        CUDA_TRY(cudaGetLastError());
+    }
+    {
+        const int CH = std::min(pick_lb(ny, budget), nzh);
+        const size_t smem = 2 * sizeof(double2) * CH * ny;
+        int rc; if ((rc = set_smem(fft_cols_kernel<0>, smem))) return rc;
+        dim3 grid((nzh + CH - 1) / CH, nx, nvec);
+        fft_cols_kernel<0><<<grid, FFT_THREADS, smem, s>>>(spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
+        CUDA_TRY(cudaGetLastError());
+    }
+    {
+        const int ncols = ny * nzh;
+        const int CH = std::min(pick_lb(nx, budget), ncols);
+        const size_t smem = 2 * sizeof(double2) * CH * nx;
+        dim3 grid((ncols + CH - 1) / CH, 1, nvec);
+        int rc;
+        if (xmode == 1) {
+            if ((rc = set_smem(fft_cols_kernel<1>, smem))) return rc;
+            fft_cols_kernel<1><<<grid, FFT_THREADS, smem, s>>>(spec, lds, 0, P.ax[0], ncols, CH, geo);
+        } else if (xmode == 2) {
+            if ((rc = set_smem(fft_cols_kernel<2>, smem))) return rc;
+            fft_cols_kernel<2><<<grid, FFT_THREADS, smem, s>>>(spec, lds, 0, P.ax[0], ncols, CH, geo);
+        } else {
+            if ((rc = set_smem(fft_cols_kernel<0>, smem))) return rc;
+            fft_cols_kernel<0><<<grid, FFT_THREADS, smem, s>>>(spec, lds, 0, P.ax[0], ncols, CH, geo);
+        }
+        CUDA_TRY(cudaGetLastError());
+    }
+    h->other_launches += 3;
+    return ISDF_OK;
+}
+
+// inverse y and z passes (x already inverted): spectra -> real vectors
+int inverse_yz(isdf_handle* h, const Plans& P, const int* mesh, double2* spec, long long lds,
+               int nvec, double* out, long long ldout, const CoulGeom& geo)
+{
+    const int nx = mesh[0], ny = mesh[1], nz = mesh[2], nzh = nz / 2 + 1;
+    cudaStream_t s = h->stream;
+    const size_t budget = 96 * 1024;
+    {
+        const int CH = std::min(pick_lb(ny, budget), nzh);
+        const size_t smem = 2 * sizeof(double2) * CH * ny;
+        int rc; if ((rc = set_smem(fft_cols_kernel<3>, smem))) return rc;
+        dim3 grid((nzh + CH - 1) / CH, nx, nvec);
+        fft_cols_kernel<3><<<grid, FFT_THREADS, smem, s>>>(spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
+        CUDA_TRY(cudaGetLastError());
+    }
+    {
+        const int LB = pick_lb(nz, budget);
+        const size_t smem = 2 * sizeof(double2) * LB * nz;
+        int rc; if ((rc = set_smem(fft_z_c2r_kernel, smem))) return rc;
+        dim3 grid((nx * ny + LB - 1) / LB, nvec);
+        fft_z_c2r_kernel<<<grid, FFT_THREADS, smem, s>>>(spec, lds, out, ldout, P.ax[2], nx * ny, LB);
+        CUDA_TRY(cudaGetLastError());
+    }
+    h->other_launches += 2;
+    return ISDF_OK;
+}
+
+}  // namespace
+
+extern "C" size_t isdf_build_W_ws_bytes(int np, const int* h_mesh)
+{
+    const size_t ngh = (size_t)h_mesh[0] * h_mesh[1] * (h_mesh[2] / 2 + 1);
+    return sizeof(double2) * ngh * (size_t)np + 4096;
+}
+
+extern "C" int isdf_coulomb_apply(isdf_handle* h, const double* in, long long ldin, int nvec,
+                                  const int* h_mesh, const double* h_a,
+                                  double* out, long long ldout, void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && in && out && h_mesh && h_a && ws && nvec > 0);
+    const long long ng = (long long)h_mesh[0] * h_mesh[1] * h_mesh[2];
+    const size_t ngh = (size_t)h_mesh[0] * h_mesh[1] * (h_mesh[2] / 2 + 1);
+    ARG_CHECK(ldin >= ng && ldout >= ng);
+    const size_t per_vec = sizeof(double2) * ngh;
+    const int batch = (int)std::min<size_t>(nvec, ws_bytes / per_vec);
+    if (batch < 1) { isdf_set_error("coulomb_apply workspace too small: need >= %zu", per_vec); return ISDF_ERR_WS; }
+    Plans P; int rc;
+    if ((rc = make_plans(h, h_mesh, P))) return rc;
+    CoulGeom geo; fill_geom(geo, h_mesh, h_a, 1.0 / (double)ng);
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FFT], h->stream));
+    for (int v0 = 0; v0 < nvec; v0 += batch) {
+        const int nv = std::min(batch, nvec - v0);
+        if ((rc = forward_passes(h, P, h_mesh, in + (long long)v0 * ldin, ldin, nv, (double2*)ws, (long long)ngh, 2, geo))) return rc;
+        if ((rc = inverse_yz(h, P, h_mesh, (double2*)ws, (long long)ngh, nv, out + (long long)v0 * ldout, ldout, geo))) return rc;
+    }
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FFT], h->stream));
+    h->ev_used[ISDF_STAGE_FFT] = true;
+    CUDA_TRY(cudaFreeAsync(P.d_tw, h->stream));
+    return ISDF_OK;
+}
+
+extern "C" int isdf_build_W(isdf_handle* h, const double* zeta, int np, long long ldz,
+                            const int* h_mesh, const double* h_a,
+                            double* W, double* V, long long ldv,
+                            void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && zeta && h_mesh && h_a && W && ws && np > 0);
+    const long long ng = (long long)h_mesh[0] * h_mesh[1] * h_mesh[2];
+    const size_t ngh = (size_t)h_mesh[0] * h_mesh[1] * (h_mesh[2] / 2 + 1);
+    ARG_CHECK(ldz >= ng);
+    const size_t need = isdf_build_W_ws_bytes(np, h_mesh);
+    if (need > ws_bytes) { isdf_set_error("build_W workspace too small: need %zu have %zu", need, ws_bytes); return ISDF_ERR_WS; }
+    int rc;
+    cudaStream_t s = h->stream;
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_COULOMB], s));
+    if (V != nullptr) {
+        ARG_CHECK(ldv >= ng);
+        if ((rc = isdf_coulomb_apply(h, zeta, ldz, np, h_mesh, h_a, V, ldv, ws, ws_bytes))) return rc;
+    }
+    Plans P;
+    if ((rc = make_plans(h, h_mesh, P))) return rc;
+    const double det = h_a[0] * (h_a[4] * h_a[8] - h_a[5] * h_a[7]) - h_a[1] * (h_a[3] * h_a[8] - h_a[5] * h_a[6]) +
+                       h_a[2] * (h_a[3] * h_a[7] - h_a[4] * h_a[6]);
+    const double vol = fabs(det);
+    CoulGeom geo; fill_geom(geo, h_mesh, h_a, 1.0);
+    double2* Y = (double2*)ws;
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FFT], s));
+    if ((rc = forward_passes(h, P, h_mesh, zeta, ldz, np, Y, (long long)ngh, 1, geo))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FFT], s));
+    h->ev_used[ISDF_STAGE_FFT] = true;
+    // W = (vol/ng^2) Y Y^T over the weighted half spectrum (upper triangle, then mirrored)
+    GemmParams p;
+    p.M = np; p.N = np; p.K = (int)(2 * ngh);
+    p.A = (const double*)Y; p.lda = 2 * (long long)ngh; p.a_kmajor = 0;
+    p.B = (const double*)Y; p.ldb = 2 * (long long)ngh; p.b_kmajor = 0;
+    p.C = W; p.ldc = np; p.Cin = nullptr; p.ldcin = 0; p.E = nullptr; p.lde = 0;
+    p.alpha = vol / ((double)ng * (double)ng); p.neg = 0; p.epi = EPI_STORE; p.upper_only = 1;
+    if ((rc = gemm_launch(h, p))) return rc;
+    dim3 blk(32, 8), grd((np + 31) / 32, (np + 7) / 8);
+    symmetrize_upper_kernel<<<grd, blk, 0, s>>>(W, np, np);
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches++;
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_COULOMB], s));
+    h->ev_used[ISDF_STAGE_COULOMB] = true;
+    CUDA_TRY(cudaFreeAsync(P.d_tw, s));
+    return ISDF_OK;
+}

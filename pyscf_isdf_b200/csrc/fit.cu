@@ -1,0 +1,260 @@
+// Stage 3: auxiliary-basis fitting  zeta = A^-1 B,
+//   A = (X^T X)^2   [np, np]   (Hadamard square of the AO Gram at the IPs)
+//   B = (X^T Phi)^2 [np, ng]   (pair densities IP x grid), X = Phi[:, ip].
+// A = U^T U by a blocked right-looking Cholesky whose panel/trailing updates
+// are the library's FP64 GEMM; the two triangular solves on the [np, ng]
+// right-hand side are blocked the same way (diagonal blocks are inverted once,
+// everything else is GEMM).  Same Cholesky-then-TRSM pattern the reference
+// uses for its Gaussian DF fit (pyscf/pbc/df/rsdf_builder.py:226, :827).
+#include "common.cuh"
+#include "../../include/isdf_b200.h"
+#include <vector>
+#include <algorithm>
+
+namespace {
+
+constexpr int CB = 128;   // diagonal block
+static inline long long pad8(long long n) { return (n + 7) & ~7LL; }
+
+// Factor one diagonal block (upper, A = U^T U) in shared memory and invert it.
+// A: [cb, cb] block inside a row-major matrix (ld); Vinv: [CB, CB] block, ld CB.
+__global__ void __launch_bounds__(256)
+chol_diag_kernel(double* __restrict__ A, long long ld, int cb, double* __restrict__ Vinv, int* __restrict__ info,
+                 int block_id, int do_factor)
+{
+    extern __shared__ double S[];      // [cb][CB+1]
+    constexpr int LD = CB + 1;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < cb * cb; i += blockDim.x) {
+        const int r = i / cb, c = i - r * cb;
+        S[r * LD + c] = (c >= r) ? A[(long long)r * ld + c] : 0.0;
+    }
+    __syncthreads();
+    if (do_factor) {
+        for (int j = 0; j < cb; ++j) {
+            if (tid == 0) {
+                const double piv = S[j * LD + j];
+                if (!(piv > 0.0)) { if (*info == 0) *info = block_id * CB + j + 1; }
+                S[j * LD + j] = sqrt(piv > 0.0 ? piv : 1.0);
+            }
+            __syncthreads();
+            const double inv = 1.0 / S[j * LD + j];
+            for (int c = j + 1 + tid; c < cb; c += blockDim.x) S[j * LD + c] *= inv;
+            __syncthreads();
+            const int nrem = cb - j - 1;
+            for (int i = tid; i < nrem * nrem; i += blockDim.x) {
+                const int r = j + 1 + i / nrem, c = j + 1 + i % nrem;
+                if (c >= r) S[r * LD + c] -= S[j * LD + r] * S[j * LD + c];
+            }
+            __syncthreads();
+        }
+        for (int i = tid; i < cb * cb; i += blockDim.x) {
+            const int r = i / cb, c = i - r * cb;
+            A[(long long)r * ld + c] = S[r * LD + c];      // upper factor, zeros below
+        }
+    }
+    // inverse of the upper-triangular block, one column per thread
+    for (int i = tid; i < CB * CB; i += blockDim.x) Vinv[i] = 0.0;
+    __syncthreads();
+    if (tid < cb) {
+        const int c = tid;
+        Vinv[c * CB + c] = 1.0 / S[c * LD + c];
+        for (int i = c - 1; i >= 0; --i) {
+            double s = 0.0;
+            for (int j = i + 1; j <= c; ++j) s += S[i * LD + j] * Vinv[j * CB + c];
+            Vinv[i * CB + c] = -s / S[i * LD + i];
+        }
+    }
+}
+
+int gemm_call(isdf_handle* h, int M, int N, int K,
+              const double* A, long long lda, int ak, const double* B, long long ldb, int bk,
+              double* C, long long ldc, const double* Cin, int neg, int epi, int upper)
+{
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.A = A; p.lda = lda; p.a_kmajor = ak;
+    p.B = B; p.ldb = ldb; p.b_kmajor = bk; p.C = C; p.ldc = ldc; p.Cin = Cin; p.ldcin = ldc;
+    p.E = nullptr; p.lde = 0; p.alpha = 1.0; p.neg = neg; p.epi = epi; p.upper_only = upper;
+    return gemm_launch(h, p);
+}
+
+int diag_kernel_cfg()
+{
+    static bool done = false;
+    const size_t smem = sizeof(double) * CB * (CB + 1);
+    if (!done) {
+        CUDA_TRY(cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        done = true;
+    }
+    return ISDF_OK;
+}
+
+// In-place blocked Cholesky of the upper triangle of A[np, np]; Vinv gets the
+// inverted diagonal blocks (block i at Vinv + i*CB*CB); P is a [CB, np] scratch panel.
+int cholesky_upper(isdf_handle* h, double* A, long long lda_, int np, double* Vinv, double* P, int* d_info)
+{
+    const long long ldp = pad8(np);
+    int rc;
+    if ((rc = diag_kernel_cfg())) return rc;
+    const size_t smem = sizeof(double) * CB * (CB + 1);
+    cudaStream_t s = h->stream;
+    for (int r0 = 0, ib = 0; r0 < np; r0 += CB, ++ib) {
+        const int cb = std::min(CB, np - r0);
+        double* Aii = A + (long long)r0 * lda_ + r0;
+        chol_diag_kernel<<<1, 256, smem, s>>>(Aii, lda_, cb, Vinv + (size_t)ib * CB * CB, d_info, ib, 1);
+        CUDA_TRY(cudaGetLastError());
+        h->other_launches++;
+        const int r1 = r0 + cb, nrem = np - r1;
+        if (nrem <= 0) break;
+        // row panel: U[r0:r1, r1:] = U_ii^-T A[r0:r1, r1:] = Vinv^T * A_panel  (into P, then back)
+        if ((rc = gemm_call(h, cb, nrem, cb, Vinv + (size_t)ib * CB * CB, CB, 1,
+                            A + (long long)r0 * lda_ + r1, lda_, 1, P, ldp, nullptr, 0, EPI_STORE, 0))) return rc;
+        CUDA_TRY(cudaMemcpy2DAsync(A + (long long)r0 * lda_ + r1, sizeof(double) * lda_, P, sizeof(double) * ldp,
+                                   sizeof(double) * nrem, cb, cudaMemcpyDeviceToDevice, s));
+        // trailing update (upper triangle only): A[r1:, r1:] -= P^T P
+        double* A22 = A + (long long)r1 * lda_ + r1;
+        if ((rc = gemm_call(h, nrem, nrem, cb, P, ldp, 1, P, ldp, 1, A22, lda_, A22, 1, EPI_STORE, 1))) return rc;
+    }
+    return ISDF_OK;
+}
+
+// Diagonal-block inverses of an already-triangular U
+int invert_diag_blocks(isdf_handle* h, double* U, long long ldu, int np, double* Vinv, int* d_info)
+{
+    int rc;
+    if ((rc = diag_kernel_cfg())) return rc;
+    const size_t smem = sizeof(double) * CB * (CB + 1);
+    for (int r0 = 0, ib = 0; r0 < np; r0 += CB, ++ib) {
+        const int cb = std::min(CB, np - r0);
+        chol_diag_kernel<<<1, 256, smem, h->stream>>>(U + (long long)r0 * ldu + r0, ldu, cb,
+                                                      Vinv + (size_t)ib * CB * CB, d_info, ib, 0);
+        CUDA_TRY(cudaGetLastError());
+        h->other_launches++;
+    }
+    return ISDF_OK;
+}
+
+// Z <- U^-T Z  (forward substitution, blocked left-looking); tmp: [CB, ng]
+int solve_upper_trans(isdf_handle* h, const double* U, long long ldu, int np, const double* Vinv,
+                      double* Z, long long ldz, long long ng, double* tmp)
+{
+    int rc;
+    cudaStream_t s = h->stream;
+    for (int r0 = 0, ib = 0; r0 < np; r0 += CB, ++ib) {
+        const int cb = std::min(CB, np - r0);
+        double* Zi = Z + (long long)r0 * ldz;
+        if (r0 > 0)   // Z_i -= U[0:r0, r0:r0+cb]^T Z[0:r0]
+            if ((rc = gemm_call(h, cb, (int)ng, r0, U + r0, ldu, 1, Z, ldz, 1, Zi, ldz, Zi, 1, EPI_STORE, 0))) return rc;
+        // Z_i = Vinv^T Z_i
+        if ((rc = gemm_call(h, cb, (int)ng, cb, Vinv + (size_t)ib * CB * CB, CB, 1, Zi, ldz, 1,
+                            tmp, pad8(ng), nullptr, 0, EPI_STORE, 0))) return rc;
+        CUDA_TRY(cudaMemcpy2DAsync(Zi, sizeof(double) * ldz, tmp, sizeof(double) * pad8(ng),
+                                   sizeof(double) * ng, cb, cudaMemcpyDeviceToDevice, s));
+    }
+    return ISDF_OK;
+}
+
+// Z <- U^-1 Z  (backward substitution, blocked)
+int solve_upper(isdf_handle* h, const double* U, long long ldu, int np, const double* Vinv,
+                double* Z, long long ldz, long long ng, double* tmp)
+{
+    int rc;
+    cudaStream_t s = h->stream;
+    const int nblk = (np + CB - 1) / CB;
+    for (int ib = nblk - 1; ib >= 0; --ib) {
+        const int r0 = ib * CB;
+        const int cb = std::min(CB, np - r0);
+        const int r1 = r0 + cb;
+        double* Zi = Z + (long long)r0 * ldz;
+        if (r1 < np)  // Z_i -= U[r0:r1, r1:] Z[r1:]
+            if ((rc = gemm_call(h, cb, (int)ng, np - r1, U + (long long)r0 * ldu + r1, ldu, 0,
+                                Z + (long long)r1 * ldz, ldz, 1, Zi, ldz, Zi, 1, EPI_STORE, 0))) return rc;
+        // Z_i = Vinv Z_i
+        if ((rc = gemm_call(h, cb, (int)ng, cb, Vinv + (size_t)ib * CB * CB, CB, 0, Zi, ldz, 1,
+                            tmp, pad8(ng), nullptr, 0, EPI_STORE, 0))) return rc;
+        CUDA_TRY(cudaMemcpy2DAsync(Zi, sizeof(double) * ldz, tmp, sizeof(double) * pad8(ng),
+                                   sizeof(double) * ng, cb, cudaMemcpyDeviceToDevice, s));
+    }
+    return ISDF_OK;
+}
+
+struct FitWs { double* X; double* U; double* Vinv; double* tmp; int* info; };
+
+size_t carve_fit(FitWs& w, void* ws, size_t bytes, int nao, long long ng, int np)
+{
+    WsAlloc a(ws, bytes);
+    const size_t nblk = (np + CB - 1) / CB;
+    w.X = a.get<double>((size_t)nao * pad8(np));
+    w.U = a.get<double>((size_t)np * pad8(np));
+    w.Vinv = a.get<double>(nblk * CB * CB);
+    w.tmp = a.get<double>((size_t)CB * pad8(std::max<long long>(ng, np)));
+    w.info = a.get<int>(4);
+    return a.off + 256;
+}
+
+int check_info(isdf_handle* h, int* d_info, const char* what)
+{
+    int* hi = (int*)h->h_pinned;
+    CUDA_TRY(cudaMemcpyAsync(hi, d_info, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (*hi != 0) {
+        isdf_set_error("%s: matrix not positive definite at pivot %d", what, *hi);
+        return ISDF_ERR_NUMERIC;
+    }
+    return ISDF_OK;
+}
+
+}  // namespace
+
+extern "C" size_t isdf_fit_aux_ws_bytes(int nao, long long ng, int np)
+{
+    FitWs w;
+    return carve_fit(w, nullptr, 0, nao, ng, np);
+}
+
+extern "C" int isdf_fit_aux(isdf_handle* h, const double* phi, int nao, long long ng, long long ldphi,
+                            const long long* h_ip, int np, double* zeta, long long ldz,
+                            void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && phi && h_ip && zeta && ws && nao > 0 && ng > 0 && np > 0 && ldphi >= ng && ldz >= ng);
+    FitWs w;
+    const size_t need = carve_fit(w, ws, ws_bytes, nao, ng, np);
+    if (need > ws_bytes) { isdf_set_error("fit_aux workspace too small: need %zu have %zu", need, ws_bytes); return ISDF_ERR_WS; }
+    int rc;
+    cudaStream_t s = h->stream;
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FIT], s));
+    CUDA_TRY(cudaMemsetAsync(w.info, 0, sizeof(int) * 4, s));
+    const long long ldu = pad8(np);
+    if ((rc = isdf_gather_cols(h, phi, ldphi, nao, h_ip, np, w.X, ldu))) return rc;
+    // A = (X^T X)^2 (upper triangle), B = (X^T Phi)^2
+    if ((rc = gemm_call(h, np, np, nao, w.X, ldu, 1, w.X, ldu, 1, w.U, ldu, nullptr, 0, EPI_SQUARE, 1))) return rc;
+    if ((rc = gemm_call(h, np, (int)ng, nao, w.X, ldu, 1, phi, ldphi, 1, zeta, ldz, nullptr, 0, EPI_SQUARE, 0))) return rc;
+    if ((rc = cholesky_upper(h, w.U, ldu, np, w.Vinv, w.tmp, w.info))) return rc;
+    if ((rc = check_info(h, w.info, "isdf_fit_aux Cholesky"))) return rc;
+    if ((rc = solve_upper_trans(h, w.U, ldu, np, w.Vinv, zeta, ldz, ng, w.tmp))) return rc;
+    if ((rc = solve_upper(h, w.U, ldu, np, w.Vinv, zeta, ldz, ng, w.tmp))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FIT], s));
+    h->ev_used[ISDF_STAGE_FIT] = true;
+    return ISDF_OK;
+}
+
+extern "C" int isdf_fit_aux_from_factor(isdf_handle* h, double* Lt, long long ldl, long long ng,
+                                        const long long* h_ip, int np, void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && Lt && h_ip && ws && ng > 0 && np > 0 && ldl >= ng);
+    FitWs w;
+    const size_t need = carve_fit(w, ws, ws_bytes, 1, ng, np);
+    if (need > ws_bytes) { isdf_set_error("fit_aux workspace too small: need %zu have %zu", need, ws_bytes); return ISDF_ERR_WS; }
+    int rc;
+    cudaStream_t s = h->stream;
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FIT], s));
+    CUDA_TRY(cudaMemsetAsync(w.info, 0, sizeof(int) * 4, s));
+    // U[k, i] = Lt[k, ip_i]: transpose of the (lower-triangular) pivot rows of L
+    const long long ldu = pad8(np);
+    if ((rc = isdf_gather_cols(h, Lt, ldl, np, h_ip, np, w.U, ldu))) return rc;
+    if ((rc = invert_diag_blocks(h, w.U, ldu, np, w.Vinv, w.info))) return rc;
+    if ((rc = solve_upper(h, w.U, ldu, np, w.Vinv, Lt, ldl, ng, w.tmp))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FIT], s));
+    h->ev_used[ISDF_STAGE_FIT] = true;
+    return ISDF_OK;
+}

@@ -1,0 +1,265 @@
+"""ISDF density-fitting object: host-side mirror of the reference's ``with_df``
+plugin protocol, driving the sm_100a kernels through the C-ABI.
+
+Protocol (what ``pbc.scf.RHF/RKS`` touches on ``mf.with_df``), taken from
+pyscf/pbc/df/fft.py:155-359 and pyscf/pbc/scf/hf.py:521-698:
+``cell, kpts, mesh, stdout, verbose, max_memory, exxdiv, build(), reset(),
+dump_flags(), get_jk(dm, hermi, kpts, kpts_band, with_j, with_k, omega,
+exxdiv), update_mf(mf)``.  ``get_jk`` returns ``(vj, vk)`` with the shape of
+``dm``, float64 at the Gamma point, ``None`` for the part not requested.
+
+Stages (all on the GPU, no CPU fallback):
+  build():  1 AO values -> 2 interpolation points -> 3 aux fit -> 4 Coulomb W
+  get_jk(): 5 J/K contraction per SCF iteration.
+The mounted reference has no ISDF class; the constructor follows SURVEY.md
+section 8b (``ISDF(cell, kpts, c=15, n_ip=None, select='cholesky')``).
+"""
+import sys
+import time
+import numpy as np
+
+from . import _lib
+from .cell import madelung as _madelung
+
+
+class ISDF:
+    _keys = {'cell', 'kpts', 'mesh', 'c', 'n_ip', 'select', 'fit', 'tol', 'exxdiv',
+             'ip_index', 'ip_resid', 'W', 'aoR', 'aoR_ip', 'stdout', 'verbose', 'max_memory',
+             'keep_aoR', 'timings'}
+
+    def __init__(self, cell, kpts=np.zeros((1, 3)), c=15, n_ip=None, select='cholesky',
+                 fit='cholesky', tol=-1.0, device=None, keep_aoR=True):
+        self.cell = cell
+        self.stdout = sys.stdout
+        self.verbose = getattr(cell, 'verbose', 0)
+        self.max_memory = getattr(cell, 'max_memory', 4000)
+        self.kpts = np.reshape(kpts, (-1, 3))
+        self.c = c
+        self.n_ip = n_ip
+        self.select = select
+        self.fit = fit
+        self.tol = tol
+        self.exxdiv = None
+        self.keep_aoR = keep_aoR
+        self._device = device
+        self._handle = None
+        self._rsh_df = {}
+        self.timings = {}
+        self.reset()
+
+    # -- protocol attributes -------------------------------------------------
+    @property
+    def mesh(self):
+        return self.cell.mesh
+
+    @mesh.setter
+    def mesh(self, x):
+        self.cell.mesh = x
+        self.reset()
+
+    def reset(self, cell=None):
+        """Drop everything derived from the geometry (pyscf/pbc/df/fft.py:198-203)."""
+        if cell is not None:
+            self.cell = cell
+        self.ip_index = None
+        self.ip_resid = None
+        self.W = None
+        self.aoR = None
+        self.aoR_ip = None
+        self._ld = None
+        self._ovlp = None
+        self._madelung = None
+        self._jk_ws = None
+        return self
+
+    def dump_flags(self, verbose=None):
+        v = self.verbose if verbose is None else verbose
+        if v >= 4:
+            self.stdout.write('\n******** %s ********\n' % self.__class__)
+            self.stdout.write('mesh = %s (%d PWs)\n' % (list(self.mesh), int(np.prod(self.mesh))))
+            self.stdout.write('c = %s  n_ip = %s  select = %s  fit = %s\n' %
+                              (self.c, self.n_ip, self.select, self.fit))
+        return self
+
+    def check_sanity(self):
+        if self.select != 'cholesky':
+            raise NotImplementedError("select=%r (only 'cholesky' pivoting is implemented)" % self.select)
+        if self.fit not in ('cholesky', 'pivot_factor'):
+            raise ValueError("fit must be 'cholesky' or 'pivot_factor'")
+        if getattr(self.cell, 'dimension', 3) != 3:
+            raise RuntimeError('ISDF supports 3-D periodic cells only')   # cf. fft.py:216-220
+        if abs(self.kpts).sum() > 1e-9:
+            raise NotImplementedError('ISDF is Gamma-point only')
+        return self
+
+    def update_mf(self, mf):
+        """Attach to an SCF object and switch off the in-core ERI shortcut that
+        would bypass get_jk (pyscf/pbc/scf/hf.py:670-679, :796-802)."""
+        mf = mf.copy() if hasattr(mf, 'copy') else mf
+        mf.with_df = self
+        mf._eri = None
+        mf._is_mem_enough = lambda: False
+        return mf
+
+    @property
+    def handle(self):
+        if self._handle is None:
+            self._handle = _lib.Handle(self._device)
+        return self._handle
+
+    # -- stages 1-4 ----------------------------------------------------------------
+    def build(self):
+        import torch
+        self.check_sanity()
+        h = self.handle
+        cell = self.cell
+        mesh = np.asarray(cell.mesh, dtype=np.int32)
+        ng = int(np.prod(mesh))
+        nao = cell.nao_nr()
+        npts = int(self.n_ip) if self.n_ip else int(self.c * nao)
+        npts = min(npts, ng)
+        a = np.ascontiguousarray(cell.lattice_vectors(), dtype=np.float64)
+        ld = _lib.pad8(ng)
+        t0 = time.perf_counter()
+
+        # stage 1: AO values Phi[nao, ng]
+        rcut, Ls = cell.ao_eval_params()
+        phi = h.empty((nao, ld))
+        if ld > ng:
+            phi[:, ng:].zero_()
+        h.eval_ao(cell._atm, cell._bas, cell._env, a, mesh, Ls, rcut, 0, ng, phi, ld)
+
+        # stage 2: interpolation points (factor rows Lt[npts, ng] double as the zeta buffer)
+        big = h.empty((npts, ld))
+        ip, resid = h.select_ip(phi, nao, ng, ld, npts, self.tol, big, ld)
+        rank = len(ip)
+        if rank < npts and self.verbose >= 3:
+            self.stdout.write('ISDF: residual reached tol after %d of %d points\n' % (rank, npts))
+        npts = rank
+
+        # stage 3: aux functions zeta[npts, ng]
+        if self.fit == 'pivot_factor':
+            h.fit_aux_from_factor(big, ld, ng, ip)
+        else:
+            h.fit_aux(phi, nao, ng, ld, ip, big, ld)
+
+        # stage 4: Coulomb metric W[npts, npts]
+        W = h.empty((npts, npts))
+        h.build_W(big, npts, ld, mesh, a, W)
+
+        X = h.empty((nao, npts))
+        h.gather_cols(phi, ld, nao, ip, X, npts)
+        torch.cuda.synchronize(h.torch_device)
+        del big
+        self.timings = {
+            'ao_ms': h.stage_ms(_lib.STAGE_AO), 'select_ms': h.stage_ms(_lib.STAGE_SELECT),
+            'fit_ms': h.stage_ms(_lib.STAGE_FIT), 'coulomb_ms': h.stage_ms(_lib.STAGE_COULOMB),
+            'fft_ms': h.stage_ms(_lib.STAGE_FFT), 'build_wall_s': time.perf_counter() - t0}
+        self.n_ip = npts
+        self.ip_index = ip
+        self.ip_resid = resid
+        self.W = W
+        self.aoR_ip = X
+        self._ld = ld
+        self.aoR = phi if self.keep_aoR else None
+        self._jk_ws = None
+        return self
+
+    def aoR_host(self):
+        """[nao, ng] AO matrix copied to the host (tests / diagnostics)."""
+        if self.aoR is None:
+            raise RuntimeError('aoR was not kept (keep_aoR=False)')
+        ng = int(np.prod(self.mesh))
+        return self.aoR[:, :ng].cpu().numpy()
+
+    # -- overlap / Madelung for exxdiv='ewald' ---------------------------------------
+    def get_ovlp(self):
+        """S = (vol/ng) Phi Phi^T on the FFT grid.  (The reference takes S from
+        libcint's int1e_ovlp, pyscf/pbc/df/df_jk.py:1447; libcint is not
+        available here, and for GTH bases the grid quadrature is exact to the
+        mesh's precision.)"""
+        if self._ovlp is None:
+            if self.aoR is None:
+                raise RuntimeError('overlap needs the AO matrix: build with keep_aoR=True')
+            h = self.handle
+            nao = self.aoR.shape[0]
+            ng = int(np.prod(self.mesh))
+            S = h.empty((nao, nao))
+            h.dgemm(nao, nao, ng, self.aoR, self._ld, 0, self.aoR, self._ld, 0, S, nao,
+                    alpha=self.cell.vol / ng)
+            self._ovlp = S
+        return self._ovlp
+
+    def get_madelung(self):
+        if self._madelung is None:
+            self._madelung = _madelung(self.cell)
+        return self._madelung
+
+    # -- stage 5 -------------------------------------------------------------------------
+    def get_jk(self, dm, hermi=1, kpts=None, kpts_band=None, with_j=True, with_k=True,
+               omega=None, exxdiv=None):
+        """Signature and return convention of FFTDF.get_jk (pyscf/pbc/df/fft.py:298-315)."""
+        import torch
+        if omega is not None:
+            raise NotImplementedError('range-separated Coulomb (omega) is not supported by ISDF')
+        if kpts_band is not None:
+            raise NotImplementedError('kpts_band is not supported by ISDF')
+        if kpts is not None and abs(np.asarray(kpts)).sum() > 1e-9:
+            raise NotImplementedError('ISDF is Gamma-point only')
+        if exxdiv not in (None, 'ewald'):
+            raise NotImplementedError('exxdiv=%s' % exxdiv)
+        if self.W is None:
+            self.build()                       # SCF never calls build() itself
+        h = self.handle
+        nao, npts = self.aoR_ip.shape
+        dm0 = np.asarray(dm)
+        if np.iscomplexobj(dm0):
+            if abs(dm0.imag).max() > 1e-12:
+                raise NotImplementedError('complex density matrices (Gamma point only)')
+            dm0 = dm0.real
+        dms = np.ascontiguousarray(dm0.reshape(-1, nao, nao), dtype=np.float64)   # df_jk.py:1411-1416
+        nset = dms.shape[0]
+
+        d_dm = torch.from_numpy(dms).pin_memory().to(h.torch_device, non_blocking=True)
+        vj = h.empty((nset, nao, nao)) if with_j else None
+        vk = h.empty((nset, nao, nao)) if with_k else None
+        if self._jk_ws is None:
+            self._jk_ws = h.workspace(h.lib.isdf_get_jk_ws_bytes(nao, npts))
+        h.get_jk(self.aoR_ip, self.W, d_dm, nset, nao, npts, with_j, with_k, vj, vk, ws=self._jk_ws)
+        if with_k and exxdiv == 'ewald':
+            # vk += madelung * S D S   (pyscf/pbc/df/df_jk.py:1446-1455)
+            S = self.get_ovlp()
+            mad = self.get_madelung()
+            tmp = h.empty((nao, nao))
+            sds = h.empty((nao, nao))
+            for i in range(nset):
+                h.dgemm(nao, nao, nao, S, nao, 0, d_dm[i], nao, 1, tmp, nao)            # S D
+                h.dgemm(nao, nao, nao, tmp, nao, 0, S, nao, 1, sds, nao, alpha=mad)    # mad (S D) S
+                vk[i] += sds
+        out_j = vj.cpu().numpy().reshape(dm0.shape) if with_j else None
+        out_k = vk.cpu().numpy().reshape(dm0.shape) if with_k else None
+        return out_j, out_k
+
+    def get_j(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None):
+        return self.get_jk(dm, hermi, kpts, kpts_band, True, False, omega)[0]
+
+    def get_k(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None, exxdiv=None):
+        return self.get_jk(dm, hermi, kpts, kpts_band, False, True, omega, exxdiv)[1]
+
+    # -- persistence ("next" row 3 of SURVEY 8f) ---------------------------------------------
+    def save(self, path):
+        np.savez(path, ip_index=self.ip_index, ip_resid=self.ip_resid,
+                 W=self.W.cpu().numpy(), aoR_ip=self.aoR_ip.cpu().numpy(),
+                 mesh=np.asarray(self.mesh), n_ip=self.n_ip)
+
+    def load(self, path):
+        import torch
+        z = np.load(path)
+        if not np.array_equal(z['mesh'], np.asarray(self.mesh)):
+            raise ValueError('mesh of the saved ISDF object does not match the cell')
+        h = self.handle
+        self.ip_index, self.ip_resid, self.n_ip = z['ip_index'], z['ip_resid'], int(z['n_ip'])
+        self.W = torch.from_numpy(z['W']).to(h.torch_device)
+        self.aoR_ip = torch.from_numpy(z['aoR_ip']).to(h.torch_device)
+        self._jk_ws = None
+        return self

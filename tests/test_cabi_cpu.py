@@ -1,0 +1,102 @@
+"""CPU: the C-ABI library builds, loads and exports every declared symbol;
+the host-side plugin surface behaves like the reference's with_df objects."""
+import ctypes
+import os
+import re
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_header_symbol():
+    from pyscf_isdf_b200 import _lib
+    lib = _lib.load_library()
+    hdr = open(os.path.join(ROOT, 'include', 'isdf_b200.h')).read()
+    names = set(re.findall(r'\b(isdf_[a-z_A-Z0-9]+)\s*\(', hdr))
+    assert names, 'no prototypes parsed'
+    for n in sorted(names):
+        assert hasattr(lib, n), 'missing export %s' % n
+        assert n in _lib.SIGNATURES, 'no ctypes prototype for %s' % n
+    # workspace queries need no GPU
+    assert lib.isdf_get_jk_ws_bytes(104, 1560) > 8 * 1560 * 1560
+    mesh = (ctypes.c_int * 3)(35, 35, 35)
+    assert lib.isdf_build_W_ws_bytes(10, mesh) >= 16 * 10 * 35 * 35 * 18
+    assert lib.isdf_select_ip_ws_bytes(104, 42875, 1560) > 0
+    assert lib.isdf_fit_aux_ws_bytes(104, 42875, 1560) > 0
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip('GPU present')
+    from pyscf_isdf_b200._lib import Handle
+    with pytest.raises(RuntimeError):
+        Handle(0)
+    from util import diamond_c8
+    from pyscf_isdf_b200.isdf import ISDF
+    mydf = ISDF(diamond_c8([9, 9, 9], basis='gth-szv'), c=3)
+    with pytest.raises(RuntimeError):
+        mydf.get_jk(np.eye(mydf.cell.nao))
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, 'pyscf_isdf_b200')
+    for fn in os.listdir(pkg):
+        if fn.endswith('.py'):
+            src = open(os.path.join(pkg, fn)).read()
+            assert not re.search(r'^\s*(from|import)\s+oracle', src, re.M), fn
+
+
+def test_plugin_surface_errors():
+    from util import diamond_c8
+    from pyscf_isdf_b200.isdf import ISDF
+    cell = diamond_c8([9, 9, 9], basis='gth-szv')
+    mydf = ISDF(cell, c=3)
+    assert list(mydf.mesh) == [9, 9, 9]
+    assert mydf.kpts.shape == (1, 3)
+    dm = np.eye(cell.nao)
+    with pytest.raises(NotImplementedError):
+        mydf.get_jk(dm, omega=0.3)
+    with pytest.raises(NotImplementedError):
+        mydf.get_jk(dm, kpts_band=np.zeros(3))
+    with pytest.raises(NotImplementedError):
+        mydf.get_jk(dm, kpts=np.array([0.1, 0, 0]))
+    with pytest.raises(NotImplementedError):
+        mydf.get_jk(dm, exxdiv='vcut_sph')
+    with pytest.raises(NotImplementedError):
+        ISDF(cell, select='qr').check_sanity()
+
+    class FakeMF:
+        def __init__(self):
+            self._eri = 1
+            self.with_df = None
+
+        def copy(self):
+            import copy
+            return copy.copy(self)
+
+        def _is_mem_enough(self):
+            return True
+    mf = mydf.update_mf(FakeMF())
+    assert mf.with_df is mydf and mf._eri is None and mf._is_mem_enough() is False
+
+
+def test_cell_model_matches_reference_conventions():
+    from util import diamond_c8
+    from pyscf_isdf_b200.cell import madelung, super_cell
+    cell = diamond_c8([35, 35, 35])
+    assert cell.nao == 104 and cell.nelectron == 32 and cell.nbas == 24
+    # normalised contracted GTOs: self-overlap of every contraction is 1
+    from pyscf_isdf_b200.cell import gaussian_int
+    for ib in range(3):
+        l, es, cs = cell.bas_angular(ib), cell.bas_exp(ib), cell._libcint_ctr_coeff(ib)
+        ee = gaussian_int(2 * l + 2, es[:, None] + es[None, :])
+        assert abs(np.einsum('pi,pq,qi->i', cs, ee, cs) - 1).max() < 1e-12
+    # Madelung constant of a simple cubic lattice: 2.837297479 / L
+    L = cell.lattice_vectors()[0, 0]
+    assert abs(madelung(cell) - 2.837297479480619 / L) < 1e-7
+    sup = super_cell(cell, [2, 2, 2])
+    assert sup.natm == 64 and sup.nao == 832 and list(sup.mesh) == [71, 71, 71]
+    coords = cell.get_uniform_grids([4, 4, 4])
+    assert coords.shape == (64, 3) and abs(coords[1] - [0, 0, L / 4]).max() < 1e-12

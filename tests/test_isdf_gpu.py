@@ -1,0 +1,74 @@
+"""GPU: the ISDF plugin end to end (build + get_jk through host buffers)."""
+import numpy as np
+import pytest
+import oracle
+from oracle import c_oracle
+from util import diamond_c8, he_c_cell, oracle_phi, rand_dm
+from pyscf_isdf_b200.isdf import ISDF
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('fit', ['cholesky', 'pivot_factor'])
+def test_isdf_plugin_matches_cpu_isdf(fit):
+    """IP indices bit-exact; J/K within 1e-8 of the CPU ISDF oracle (north_star tolerance)."""
+    cell = diamond_c8([14, 14, 14], basis='gth-dzvp', jitter=0.15)
+    mydf = ISDF(cell, c=6, fit=fit)
+    dm = rand_dm(cell.nao)
+    vj, vk = mydf.get_jk(dm, exxdiv=None)                 # lazy build, like SCF would trigger it
+    phi = oracle_phi(cell)
+    assert abs(mydf.aoR_host() - phi).max() < 1e-12
+    ip, resid = c_oracle.select_ip_chain(mydf.aoR_host(), 6 * cell.nao)
+    assert np.array_equal(mydf.ip_index, ip)
+    assert np.array_equal(mydf.ip_resid, resid)
+    ref = oracle.isdf_build(phi, cell.lattice_vectors(), cell.mesh, 6 * cell.nao)
+    assert np.array_equal(ref['ip'], ip)
+    vj0, vk0 = oracle.isdf_get_jk(ref['X'], ref['W'], dm)
+    assert abs(vj - vj0).max() < 1e-8
+    assert abs(vk - vk0).max() < 1e-8
+    # J-only / K-only and shapes (pyscf/pbc/df/fft.py:298-315 convention)
+    j_only, none = mydf.get_jk(dm, with_k=False)
+    assert none is None and np.array_equal(j_only, vj)
+    dms = np.stack([dm, 2 * dm])
+    vj2, vk2 = mydf.get_jk(dms)
+    assert vj2.shape == dms.shape and abs(vk2[1] - 2 * vk).max() < 1e-9
+
+
+def test_isdf_exact_limit_reproduces_fftdf_goldens():
+    """Np = rank of the pair space -> ISDF equals exact FFTDF J/K: reproduces the
+    reference's golden fingerprints (pyscf/pbc/df/test/test_fft.py:642-645)."""
+    cell = he_c_cell()
+    mydf = ISDF(cell, n_ip=60)                       # pair space has dimension 21
+    dm = np.eye(cell.nao, dtype=int)                 # integer DM is cast (df_jk.py:1415-1416)
+    vj, vk = mydf.get_jk(dm, exxdiv=None)
+    assert mydf.n_ip <= 22
+    assert abs(oracle.fp(vj) - 3.7955873127283377) < 1e-7
+    assert abs(oracle.fp(vk) - 4.290076429522121) < 1e-7
+
+
+def test_isdf_ewald_and_convergence_with_c():
+    cell = diamond_c8([14, 14, 14], basis='gth-szv', jitter=0.15)
+    phi = oracle_phi(cell)
+    dm = rand_dm(cell.nao)
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    ovlp = (cell.vol / phi.shape[1]) * phi.dot(phi.T)
+    from pyscf_isdf_b200.cell import madelung
+    vj_x, vk_x = oracle.fftdf_get_jk(phi.T, dm, a, mesh, exxdiv='ewald', ovlp=ovlp, madelung=madelung(cell))
+    errs = []
+    for c in (4, 8, 16):
+        mydf = ISDF(cell, c=c)
+        vj, vk = mydf.get_jk(dm, exxdiv='ewald')
+        errs.append(max(abs(vj - vj_x).max(), abs(vk - vk_x).max()))
+    assert errs[0] > errs[1] > errs[2], errs          # tier C: error decreases with c
+    assert errs[2] < 1e-3 * abs(vk_x).max(), errs
+
+
+def test_isdf_save_load(tmp_path):
+    cell = diamond_c8([12, 12, 12], basis='gth-szv', jitter=0.1)
+    dm = rand_dm(cell.nao)
+    a = ISDF(cell, c=5).build()
+    vj, vk = a.get_jk(dm)
+    a.save(str(tmp_path / 'isdf.npz'))
+    b = ISDF(cell, c=5).load(str(tmp_path / 'isdf.npz'))
+    vj2, vk2 = b.get_jk(dm)
+    assert np.array_equal(vj, vj2) and np.array_equal(vk, vk2)

@@ -1,0 +1,91 @@
+"""CPU: pin the oracle to the reference's own known-answer tests."""
+import numpy as np
+import oracle
+from pyscf_isdf_b200.cell import Cell, cartesian_prod, madelung
+from util import he_c_cell, oracle_phi
+
+
+def test_fft_matches_numpy():
+    # pyscf/pbc/tools/test/test_pbc.py:185-217
+    rng = np.random.default_rng(0)
+    for mesh in ([31, 31, 31], [31, 31, 8], [8, 31, 8]):
+        f = rng.random((2, int(np.prod(mesh)))) + 0j
+        ref = np.fft.fftn(f.reshape(-1, *mesh), axes=(1, 2, 3)).reshape(2, -1)
+        assert abs(oracle.fft(f, mesh) - ref).max() < 1e-10
+        ref = np.fft.ifftn(f.reshape(-1, *mesh), axes=(1, 2, 3)).reshape(2, -1)
+        assert abs(oracle.ifft(f, mesh) - ref).max() < 1e-10
+
+
+def test_coulG_goldens():
+    # pyscf/pbc/tools/test/test_pbc.py:54-80
+    np.random.seed(19)
+    kpt = np.random.random(3)
+    a = (np.array(((0., 1.7834, 1.7834), (1.7834, 0., 1.7834), (1.7834, 1.7834, 0.)))
+         + np.random.random((3, 3)).T) / 0.52917721092
+    assert abs(oracle.fp(oracle.get_coulG(a, [11, 9, 7], kpt)) - 62.75448804333378) < 1e-9
+    a = np.eye(3)
+    k = np.array([0, np.pi, 0])
+    assert abs(oracle.fp(oracle.get_coulG(a, [11, 9, 7], k)) - 4.6737453679713905) < 1e-9
+    assert abs(oracle.fp(oracle.get_coulG(a, [11, 9, 7], k, wrap_around=False)) - 4.5757877990664744) < 1e-9
+    c2 = Cell(atom='C 0. 0. 0.; C 0.8917 0.8917 0.8917', a=np.eye(3), unit='B',
+              basis='gth-szv', pseudo='gth-pade', mesh=[11, 9, 7]).build()
+    g = oracle.get_coulG(a, [11, 9, 7], exx='ewald', madelung=madelung(c2))
+    assert abs(oracle.fp(g) - 4.888843468914021) < 1e-9
+
+
+def test_eval_ao_d_shell_golden():
+    # pyscf/pbc/gto/test/test_cell.py:500-504 (d shell, 27 k-points)
+    cell = Cell(a=np.eye(3) * 4, atom='He 1 1 1', basis=[[2, (1, .5), (.5, .5)]],
+                pseudo=None, precision=1e-10).build()
+    coords = cell.get_uniform_grids([10] * 3, wrap_around=False)
+    kpts = cartesian_prod([np.arange(3) / 3.] * 3).dot(cell.reciprocal_vectors())
+    rcut, Ls = cell.ao_eval_params()
+    ao = oracle.eval_ao(cell._atm, cell._bas, cell._env, coords, Ls, rcut, kpts=kpts)
+    assert abs(oracle.fp(ao) - (-0.27594803231989179 + 0.0064644591759109114j)) < 1e-9
+
+
+def test_fftdf_jk_golden():
+    # pyscf/pbc/df/test/test_fft.py:642-645 (dm = eye(int), exxdiv=None, Gamma point)
+    cell = he_c_cell()
+    ao = oracle_phi(cell).T
+    dm = np.eye(cell.nao, dtype=int)
+    vj, vk = oracle.fftdf_get_jk(ao, dm, cell.lattice_vectors(), cell.mesh)
+    assert abs(oracle.fp(vj) - 3.7955873127283377) < 1e-8
+    assert abs(oracle.fp(vk) - 4.290076429522121) < 1e-8
+
+
+def test_c2s_orthonormal():
+    """The restated libcint cart->sph matrices give orthonormal real harmonics."""
+    from oracle.eval_ao import C2S, cart_powers
+    x, w = np.polynomial.legendre.leggauss(24)
+    phi = (np.arange(48) + .5) * 2 * np.pi / 48
+    ct, ph = np.meshgrid(x, phi, indexing='ij')
+    st = np.sqrt(1 - ct**2)
+    xyz = np.stack([st * np.cos(ph), st * np.sin(ph), ct]).reshape(3, -1)
+    wt = (w[:, None] * np.ones_like(ph) * 2 * np.pi / 48).ravel()
+    for l, c2s in C2S.items():
+        cart = np.stack([xyz[0]**a * xyz[1]**b * xyz[2]**c for a, b, c in cart_powers(l)])
+        Y = c2s.dot(cart)
+        S = (Y * wt).dot(Y.T)
+        assert abs(S - np.eye(2 * l + 1)).max() < 1e-12
+
+
+def test_isdf_oracle_exact_limit():
+    """All grid points as interpolation points reproduce the FFTDF J/K."""
+    cell = Cell(atom='He 1. .5 .5; C .1 1.3 2.1',
+                basis={'He': [(0, (2.5, 1)), (0, (1., 1))], 'C': 'gth-szv'},
+                pseudo={'C': 'gth-pade'}, a=np.eye(3) * 2.5, mesh=[7] * 3).build()
+    phi = oracle_phi(cell)
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    nao, ng = phi.shape
+    rng = np.random.default_rng(1)
+    dm = rng.random((nao, nao)); dm = dm + dm.T
+    vj0, vk0 = oracle.fftdf_get_jk(phi.T, dm, a, mesh)
+    # rank of the pair-product space is nao(nao+1)/2 = 21 << ng: ISDF is exact once Np >= 21
+    ip, resid = oracle.select_ip(phi, 40)
+    assert len(ip) <= 21 + 1
+    zeta = oracle.fit_aux(phi, ip)
+    W = oracle.build_W(zeta, a, mesh)
+    vj, vk = oracle.isdf_get_jk(phi[:, ip], W, dm)
+    assert abs(vj - vj0).max() < 1e-9
+    assert abs(vk - vk0).max() < 1e-9
