@@ -168,16 +168,31 @@ struct CoulGeom {
     double scale;       // multiplies the kernel (1/ng for V)
 };
 
-__device__ __forceinline__ double coulG_at(const CoulGeom& g, int ix, int iy, int iz)
+__device__ __forceinline__ double coulG_raw(const CoulGeom& g, int fx, int fy, int fz)
 {
-    const int fx = ix < (g.mesh[0] + 1) / 2 ? ix : ix - g.mesh[0];
-    const int fy = iy < (g.mesh[1] + 1) / 2 ? iy : iy - g.mesh[1];
-    const int fz = iz < (g.mesh[2] + 1) / 2 ? iz : iz - g.mesh[2];
     const double gx = fx * g.b[0] + fy * g.b[3] + fz * g.b[6];
     const double gy = fx * g.b[1] + fy * g.b[4] + fz * g.b[7];
     const double gz = fx * g.b[2] + fy * g.b[5] + fz * g.b[8];
     const double g2 = gx * gx + gy * gy + gz * gz;
     return (fx == 0 && fy == 0 && fz == 0) ? 0.0 : 4.0 * 3.14159265358979323846 / g2;
+}
+
+__device__ __forceinline__ int freq_of(int i, int n) { return i < (n + 1) / 2 ? i : i - n; }
+
+// Coulomb kernel at FFT index (ix,iy,iz).  The reference multiplies the full
+// complex spectrum by coulG(G) and keeps the real part of the inverse FFT
+// (pyscf/pbc/df/fft_jk.py:72-74), which is the same as using the average of
+// coulG at G and at the index-negated -G.  The two differ only on the Nyquist
+// planes of even meshes in non-orthogonal cells.
+__device__ __forceinline__ double coulG_at(const CoulGeom& g, int ix, int iy, int iz)
+{
+    const int fx = freq_of(ix, g.mesh[0]), fy = freq_of(iy, g.mesh[1]), fz = freq_of(iz, g.mesh[2]);
+    const int mx = freq_of((g.mesh[0] - ix) % g.mesh[0], g.mesh[0]);
+    const int my = freq_of((g.mesh[1] - iy) % g.mesh[1], g.mesh[1]);
+    const int mz = freq_of((g.mesh[2] - iz) % g.mesh[2], g.mesh[2]);
+    const double c0 = coulG_raw(g, fx, fy, fz);
+    if (mx == -fx && my == -fy && mz == -fz) return c0;
+    return 0.5 * (c0 + coulG_raw(g, mx, my, mz));
 }
 
 // ---- z pass: real lines -> half spectrum ------------------------------------
