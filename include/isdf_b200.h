@@ -120,6 +120,13 @@ int isdf_dgemm(isdf_handle* h, int M, int N, int K,
                const double* E, long long lde,
                double alpha, int neg, int epi, int upper_only);
 
+/* Per-launch timing of the GEMM kernel (bench.py roofline): enable=1 resets and
+ * starts bracketing every GEMM launch with CUDA events on the handle's stream,
+ * enable=0 stops; read returns algorithmic flops (2*K per computed element),
+ * summed kernel milliseconds and the launch count since the last enable. */
+int isdf_gemm_profile(isdf_handle* h, int enable);
+int isdf_gemm_profile_read(isdf_handle* h, double* h_flops, double* h_ms, long long* h_count);
+
 /* gather columns: out[r, j] = in[r, idx[j]] (idx on host) */
 int isdf_gather_cols(isdf_handle* h, const double* in, long long ldin, int nrows,
                      const long long* h_idx, int ncols, double* out, long long ldout);

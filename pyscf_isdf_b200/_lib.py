@@ -41,6 +41,9 @@ SIGNATURES = {
                             c_vp, c_vp, c_vp, c_sz]),
     'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
                            c_vp, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_int, c_int]),
+    'isdf_gemm_profile': (c_int, [c_vp, c_int]),
+    'isdf_gemm_profile_read': (c_int, [c_vp, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl),
+                                       ctypes.POINTER(c_ll)]),
     'isdf_gather_cols': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_int, c_vp, c_ll]),
 }
 
@@ -125,6 +128,15 @@ class Handle:
         out = ctypes.c_float()
         check(self.lib.isdf_stage_time_ms(self.h, stage, ctypes.byref(out)))
         return out.value
+
+    def gemm_profile(self, enable):
+        check(self.lib.isdf_gemm_profile(self.h, int(enable)))
+
+    def gemm_profile_read(self):
+        """(algorithmic flops, summed kernel ms, launches) since gemm_profile(True)"""
+        fl, ms, n = c_dbl(), c_dbl(), c_ll()
+        check(self.lib.isdf_gemm_profile_read(self.h, ctypes.byref(fl), ctypes.byref(ms), ctypes.byref(n)))
+        return fl.value, ms.value, n.value
 
     def launches(self):
         return (self.lib.isdf_launch_count(self.h, 0), self.lib.isdf_launch_count(self.h, 1))

@@ -45,6 +45,10 @@ struct isdf_handle {
     void* h_pinned;      // 64 KiB pinned host mailbox
     long long gemm_launches;   // kernel-launch counter (bench reports it)
     long long other_launches;
+    // optional per-launch GEMM timing (bench.py roofline): event pairs + flop sum
+    int prof_on, prof_n, prof_cap;
+    cudaEvent_t* prof_ev;      // 2 * prof_cap events
+    double prof_flops;
 };
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

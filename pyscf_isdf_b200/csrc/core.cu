@@ -54,6 +54,8 @@ extern "C" int isdf_destroy(isdf_handle* h)
     }
     cudaFree(h->d_small);
     cudaFreeHost(h->h_pinned);
+    for (int i = 0; i < 2 * h->prof_cap; ++i) cudaEventDestroy(h->prof_ev[i]);
+    delete[] h->prof_ev;
     delete h;
     return ISDF_OK;
 }
@@ -79,6 +81,37 @@ extern "C" int isdf_stage_time_ms(isdf_handle* h, int stage, float* out)
     if (!h->ev_used[stage]) { *out = -1.f; return ISDF_OK; }
     CUDA_TRY(cudaEventSynchronize(h->ev1[stage]));
     CUDA_TRY(cudaEventElapsedTime(out, h->ev0[stage], h->ev1[stage]));
+    return ISDF_OK;
+}
+
+// Per-launch GEMM timing for bench.py's roofline: enable -> every GEMM launch is
+// bracketed by an event pair (up to 65536 launches); read -> total algorithmic
+// flops, summed kernel time and launch count since enable.
+extern "C" int isdf_gemm_profile(isdf_handle* h, int enable)
+{
+    ARG_CHECK(h != nullptr);
+    if (enable && h->prof_cap == 0) {
+        const int cap = 1 << 16;
+        h->prof_ev = new cudaEvent_t[2 * cap];
+        for (int i = 0; i < 2 * cap; ++i) CUDA_TRY(cudaEventCreate(&h->prof_ev[i]));
+        h->prof_cap = cap;
+    }
+    if (enable) { h->prof_n = 0; h->prof_flops = 0.0; }
+    h->prof_on = enable ? 1 : 0;
+    return ISDF_OK;
+}
+
+extern "C" int isdf_gemm_profile_read(isdf_handle* h, double* h_flops, double* h_ms, long long* h_count)
+{
+    ARG_CHECK(h && h_flops && h_ms && h_count);
+    double ms = 0.0;
+    for (int i = 0; i < h->prof_n; ++i) {
+        float t = 0.f;
+        CUDA_TRY(cudaEventSynchronize(h->prof_ev[2 * i + 1]));
+        CUDA_TRY(cudaEventElapsedTime(&t, h->prof_ev[2 * i], h->prof_ev[2 * i + 1]));
+        ms += t;
+    }
+    *h_flops = h->prof_flops; *h_ms = ms; *h_count = h->prof_n;
     return ISDF_OK;
 }
 

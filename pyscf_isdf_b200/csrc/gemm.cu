@@ -232,8 +232,24 @@ int launch_cfg(isdf_handle* h, const GemmParams& p)
         configured = true;
     }
     dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN);
+    const bool prof = h->prof_on && h->prof_n < h->prof_cap;
+    if (prof) CUDA_TRY(cudaEventRecord(h->prof_ev[2 * h->prof_n], h->stream));
     kern<<<grid, NTHREADS, smem, h->stream>>>(p);
     CUDA_TRY(cudaGetLastError());
+    if (prof) {
+        CUDA_TRY(cudaEventRecord(h->prof_ev[2 * h->prof_n + 1], h->stream));
+        h->prof_n++;
+        // algorithmic flops of this launch: 2*K per computed output element
+        double elems = (double)p.M * (double)p.N;
+        if (p.upper_only) {
+            long long tiles = 0;
+            for (unsigned bx = 0; bx < grid.x; ++bx)
+                for (unsigned by = 0; by < grid.y; ++by)
+                    if (!((long long)bx * BM >= (long long)by * BN + BN)) tiles++;
+            elems = (double)tiles * BM * BN;
+        }
+        h->prof_flops += 2.0 * elems * (double)p.K;
+    }
     h->gemm_launches++;
     return ISDF_OK;
 }

@@ -221,6 +221,19 @@ class ISDF:
         nset = dms.shape[0]
 
         d_dm = torch.from_numpy(dms).pin_memory().to(h.torch_device, non_blocking=True)
+        vj, vk = self.get_jk_device(d_dm, with_j, with_k, exxdiv)
+        out_j = vj.cpu().numpy().reshape(dm0.shape) if with_j else None
+        out_k = vk.cpu().numpy().reshape(dm0.shape) if with_k else None
+        return out_j, out_k
+
+    def get_jk_device(self, d_dm, with_j=True, with_k=True, exxdiv=None):
+        """Stage 5 on a device-resident density matrix [nset, nao, nao]; returns
+        device tensors (no host copies; asynchronous on the handle's stream)."""
+        if self.W is None:
+            self.build()
+        h = self.handle
+        nao, npts = self.aoR_ip.shape
+        nset = d_dm.shape[0]
         vj = h.empty((nset, nao, nao)) if with_j else None
         vk = h.empty((nset, nao, nao)) if with_k else None
         if self._jk_ws is None:
@@ -236,9 +249,7 @@ class ISDF:
                 h.dgemm(nao, nao, nao, S, nao, 0, d_dm[i], nao, 1, tmp, nao)            # S D
                 h.dgemm(nao, nao, nao, tmp, nao, 0, S, nao, 1, sds, nao, alpha=mad)    # mad (S D) S
                 vk[i] += sds
-        out_j = vj.cpu().numpy().reshape(dm0.shape) if with_j else None
-        out_k = vk.cpu().numpy().reshape(dm0.shape) if with_k else None
-        return out_j, out_k
+        return vj, vk
 
     def get_j(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None):
         return self.get_jk(dm, hermi, kpts, kpts_band, True, False, omega)[0]

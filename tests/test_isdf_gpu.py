@@ -72,3 +72,20 @@ def test_isdf_save_load(tmp_path):
     b = ISDF(cell, c=5).load(str(tmp_path / 'isdf.npz'))
     vj2, vk2 = b.get_jk(dm)
     assert np.array_equal(vj, vj2) and np.array_equal(vk, vk2)
+
+
+def test_isdf_matches_committed_golden_fixture():
+    """Pivots bit-exact and W/J/K within 1e-8 of tests/golden/isdf_small.npz
+    (made by tests/golden/make_golden.py; no oracle call here)."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'isdf_small.npz'))
+    cell = diamond_c8(list(z['mesh']), basis='gth-dzvp', jitter=float(z['jitter']))
+    for fit in ('cholesky', 'pivot_factor'):
+        mydf = ISDF(cell, c=int(z['c']), fit=fit).build()
+        assert np.array_equal(mydf.ip_index, z['ip'])
+        assert np.array_equal(mydf.ip_resid, z['resid'])
+        W = mydf.W.cpu().numpy()
+        assert abs(np.diag(W) - z['W_diag']).max() < 1e-8
+        assert abs(W[:16, :16] - z['W_block']).max() < 1e-8
+        vj, vk = mydf.get_jk(rand_dm(cell.nao))
+        assert abs(vj - z['vj']).max() < 1e-8 and abs(vk - z['vk']).max() < 1e-8

@@ -89,3 +89,21 @@ def test_isdf_oracle_exact_limit():
     vj, vk = oracle.isdf_get_jk(phi[:, ip], W, dm)
     assert abs(vj - vj0).max() < 1e-9
     assert abs(vk - vk0).max() < 1e-9
+
+
+def test_golden_files_consistent():
+    """tests/golden: the reference KAT table is the one this file checks, and the
+    self-generated ISDF fixture is reproduced by the oracle (regeneration check)."""
+    import json, os
+    from oracle import c_oracle
+    from util import diamond_c8
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+    kats = json.load(open(os.path.join(here, 'reference_kats.json')))
+    assert kats['fftdf_vj_eye']['value'] == 3.7955873127283377
+    assert kats['coulG_ewald']['value'] == 4.888843468914021
+    z = np.load(os.path.join(here, 'isdf_small.npz'))
+    cell = diamond_c8(list(z['mesh']), basis='gth-dzvp', jitter=float(z['jitter']))
+    phi = oracle_phi(cell)
+    assert abs(oracle.fp(phi) - float(z['phi_fp'])) < 1e-9
+    ip, resid = c_oracle.select_ip_chain(phi, int(z['c']) * cell.nao)
+    assert np.array_equal(ip, z['ip']) and np.array_equal(resid, z['resid'])
