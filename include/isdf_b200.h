@@ -120,6 +120,10 @@ int isdf_dgemm(isdf_handle* h, int M, int N, int K,
                const double* E, long long lde,
                double alpha, int neg, int epi, int upper_only);
 
+/* Tuning knob: CTA tile of the GEMM kernel, 0 = automatic (default),
+ * 2 = 64x128, 3 = 64x64. */
+int isdf_set_gemm_tile(isdf_handle* h, int which);
+
 /* Per-launch timing of the GEMM kernel (bench.py roofline): enable=1 resets and
  * starts bracketing every GEMM launch with CUDA events on the handle's stream,
  * enable=0 stops; read returns algorithmic flops (2*K per computed element),

@@ -41,6 +41,7 @@ SIGNATURES = {
                             c_vp, c_vp, c_vp, c_sz]),
     'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
                            c_vp, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_int, c_int]),
+    'isdf_set_gemm_tile': (c_int, [c_vp, c_int]),
     'isdf_gemm_profile': (c_int, [c_vp, c_int]),
     'isdf_gemm_profile_read': (c_int, [c_vp, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl),
                                        ctypes.POINTER(c_ll)]),
@@ -106,6 +107,8 @@ class Handle:
         with torch.cuda.device(self.device):
             self.stream = torch.cuda.current_stream()
         check(self.lib.isdf_set_stream(self.h, c_vp(self.stream.cuda_stream)))
+        if os.environ.get('ISDF_GEMM_TILE'):          # tuning knob, see include/isdf_b200.h
+            self.set_gemm_tile(int(os.environ['ISDF_GEMM_TILE']))
 
     def __del__(self):
         try:
@@ -128,6 +131,9 @@ class Handle:
         out = ctypes.c_float()
         check(self.lib.isdf_stage_time_ms(self.h, stage, ctypes.byref(out)))
         return out.value
+
+    def set_gemm_tile(self, which):
+        check(self.lib.isdf_set_gemm_tile(self.h, int(which)))
 
     def gemm_profile(self, enable):
         check(self.lib.isdf_gemm_profile(self.h, int(enable)))

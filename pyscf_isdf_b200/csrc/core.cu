@@ -84,6 +84,13 @@ extern "C" int isdf_stage_time_ms(isdf_handle* h, int stage, float* out)
     return ISDF_OK;
 }
 
+extern "C" int isdf_set_gemm_tile(isdf_handle* h, int which)
+{
+    ARG_CHECK(h != nullptr && (which == 0 || which == 2 || which == 3));
+    h->gemm_force = which;
+    return ISDF_OK;
+}
+
 // Per-launch GEMM timing for bench.py's roofline: enable -> every GEMM launch is
 // bracketed by an event pair (up to 65536 launches); read -> total algorithmic
 // flops, summed kernel time and launch count since enable.

@@ -26,10 +26,25 @@ constexpr int FFT_THREADS = 256;
 constexpr int MAX_RAD = 16;
 constexpr int BIG_RADIX_MAX = 256;
 
-struct FftPlan {
+struct Radix {
     int n, nrad;
     int rad[MAX_RAD];
     const double2* tw;      // exp(-2 pi i k / n), k < n
+};
+
+// A prime length n > 7 is transformed with Rader's algorithm: the n-1 non-zero
+// indices, permuted by powers of a generator of (Z/n)*, turn the DFT into a
+// cyclic convolution of length n-1 (composite), done with two sub-FFTs.
+struct FftPlan {
+    Radix main;
+    int rader;              // 1: main.n is prime, use sub / perm / bhat
+    Radix sub;              // length n-1
+    const int* perm;        // g^p mod n,      p < n-1
+    const int* iperm;       // g^-q mod n,     q < n-1
+    const double2* bhat_f;  // FFT_{n-1}(w^(g^-m)) / (n-1) for the forward transform (w = e^{-2 pi i/n})
+    const double2* bhat_b;  // same for the inverse transform (w = e^{+2 pi i/n})
+    __host__ __device__ int n() const { return main.n; }
+    __host__ __device__ int lalloc() const { return main.n + (rader ? 2 : 0); }   // smem slots per line
 };
 
 __device__ __forceinline__ double2 cmul(double2 a, double2 b)
@@ -85,7 +100,7 @@ __device__ __forceinline__ void dft_small(double2* u, const double2* tw, int n)
 
 template <int R, int SIGN>
 __device__ __forceinline__ void stage_small(const double2* __restrict__ in, double2* __restrict__ out,
-                                            const FftPlan& pl, int p, int nlines, int line_stride,
+                                            const Radix& pl, int p, int nlines, int line_stride,
                                             int elem_stride, bool line_fast)
 {
     const int n = pl.n, t = n / R;
@@ -112,7 +127,7 @@ __device__ __forceinline__ void stage_small(const double2* __restrict__ in, doub
 }
 
 template <int SIGN>
-__device__ void stage_big(const double2* __restrict__ in, double2* __restrict__ out, const FftPlan& pl,
+__device__ void stage_big(const double2* __restrict__ in, double2* __restrict__ out, const Radix& pl,
                           int r, int p, int nlines, int line_stride, int elem_stride, bool line_fast)
 {
     const int n = pl.n, t = n / r;
@@ -140,8 +155,8 @@ __device__ void stage_big(const double2* __restrict__ in, double2* __restrict__ 
 
 // FFT of `nlines` lines living in shared memory; returns the buffer holding the result.
 template <int SIGN>
-__device__ double2* fft_smem(double2* a, double2* b, const FftPlan& pl, int nlines,
-                             int line_stride, int elem_stride, bool line_fast)
+__device__ double2* fft_radix_smem(double2* a, double2* b, const Radix& pl, int nlines,
+                                   int line_stride, int elem_stride, bool line_fast)
 {
     int p = 1;
     for (int s = 0; s < pl.nrad; ++s) {
@@ -159,6 +174,57 @@ __device__ double2* fft_smem(double2* a, double2* b, const FftPlan& pl, int nlin
         p *= r;
     }
     return a;
+}
+
+// Rader transform of prime-length lines (slots n and n+1 of buffer `a` hold x[0] and X[0]).
+template <int SIGN>
+__device__ double2* rader_smem(double2* a, double2* b, const FftPlan& pl, int nlines,
+                               int ls, int es, bool line_fast)
+{
+    const int n = pl.main.n, m = n - 1;
+    const double2* bhat = SIGN < 0 ? pl.bhat_f : pl.bhat_b;
+    for (int idx = threadIdx.x; idx < nlines * m; idx += blockDim.x) {
+        int line, q;
+        if (line_fast) { q = idx / nlines; line = idx - q * nlines; }
+        else { line = idx / m; q = idx - line * m; }
+        b[(long long)line * ls + q * es] = a[(long long)line * ls + pl.perm[q] * es];
+    }
+    __syncthreads();
+    for (int line = threadIdx.x; line < nlines; line += blockDim.x)
+        a[(long long)line * ls + n * es] = a[(long long)line * ls];
+    __syncthreads();
+    double2* r = fft_radix_smem<-1>(b, a, pl.sub, nlines, ls, es, line_fast);
+    double2* o = (r == a) ? b : a;
+    for (int idx = threadIdx.x; idx < nlines * m; idx += blockDim.x) {
+        int line, q;
+        if (line_fast) { q = idx / nlines; line = idx - q * nlines; }
+        else { line = idx / m; q = idx - line * m; }
+        const double2 v = r[(long long)line * ls + q * es];
+        if (q == 0) a[(long long)line * ls + (n + 1) * es] = cadd(a[(long long)line * ls + n * es], v);
+        r[(long long)line * ls + q * es] = cmul(v, bhat[q]);
+    }
+    __syncthreads();
+    double2* r2 = fft_radix_smem<+1>(r, o, pl.sub, nlines, ls, es, line_fast);
+    double2* o2 = (r2 == a) ? b : a;
+    for (int idx = threadIdx.x; idx < nlines * m; idx += blockDim.x) {
+        int line, q;
+        if (line_fast) { q = idx / nlines; line = idx - q * nlines; }
+        else { line = idx / m; q = idx - line * m; }
+        o2[(long long)line * ls + pl.iperm[q] * es] =
+            cadd(a[(long long)line * ls + n * es], r2[(long long)line * ls + q * es]);
+    }
+    for (int line = threadIdx.x; line < nlines; line += blockDim.x)
+        o2[(long long)line * ls] = a[(long long)line * ls + (n + 1) * es];
+    __syncthreads();
+    return o2;
+}
+
+template <int SIGN>
+__device__ __forceinline__ double2* fft_smem(double2* a, double2* b, const FftPlan& pl, int nlines,
+                                             int line_stride, int elem_stride, bool line_fast)
+{
+    if (pl.rader) return rader_smem<SIGN>(a, b, pl, nlines, line_stride, elem_stride, line_fast);
+    return fft_radix_smem<SIGN>(a, b, pl.main, nlines, line_stride, elem_stride, line_fast);
 }
 
 struct CoulGeom {
@@ -201,18 +267,21 @@ fft_z_r2c_kernel(const double* __restrict__ in, long long ldin, double2* __restr
                  FftPlan pl, int nlines, int LB)
 {
     extern __shared__ double2 sm[];
-    const int nz = pl.n, nzh = nz / 2 + 1;
-    double2* a = sm; double2* b = sm + LB * nz;
+    const int nz = pl.n(), nzh = nz / 2 + 1, LS = pl.lalloc();
+    double2* a = sm; double2* b = sm + LB * LS;
     const int line0 = blockIdx.x * LB;
     const int nl = min(LB, nlines - line0);
     const double* src = in + (long long)blockIdx.y * ldin + (long long)line0 * nz;
-    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) a[idx] = make_double2(src[idx], 0.0);
+    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) {
+        const int line = idx / nz, e = idx - line * nz;
+        a[line * LS + e] = make_double2(src[idx], 0.0);
+    }
     __syncthreads();
-    double2* r = fft_smem<-1>(a, b, pl, nl, nz, 1, false);
+    double2* r = fft_smem<-1>(a, b, pl, nl, LS, 1, false);
     double2* dst = out + (long long)blockIdx.y * ldout + (long long)line0 * nzh;
     for (int idx = threadIdx.x; idx < nl * nzh; idx += blockDim.x) {
         const int line = idx / nzh, e = idx - line * nzh;
-        dst[idx] = r[line * nz + e];
+        dst[idx] = r[line * LS + e];
     }
 }
 
@@ -222,8 +291,8 @@ fft_z_c2r_kernel(const double2* __restrict__ in, long long ldin, double* __restr
                  FftPlan pl, int nlines, int LB)
 {
     extern __shared__ double2 sm[];
-    const int nz = pl.n, nzh = nz / 2 + 1;
-    double2* a = sm; double2* b = sm + LB * nz;
+    const int nz = pl.n(), nzh = nz / 2 + 1, LS = pl.lalloc();
+    double2* a = sm; double2* b = sm + LB * LS;
     const int line0 = blockIdx.x * LB;
     const int nl = min(LB, nlines - line0);
     const double2* src = in + (long long)blockIdx.y * ldin + (long long)line0 * nzh;
@@ -232,12 +301,15 @@ fft_z_c2r_kernel(const double2* __restrict__ in, long long ldin, double* __restr
         double2 v;
         if (e < nzh) v = src[line * nzh + e];
         else { v = src[line * nzh + (nz - e)]; v.y = -v.y; }
-        a[idx] = v;
+        a[line * LS + e] = v;
     }
     __syncthreads();
-    double2* r = fft_smem<+1>(a, b, pl, nl, nz, 1, false);
+    double2* r = fft_smem<+1>(a, b, pl, nl, LS, 1, false);
     double* dst = out + (long long)blockIdx.y * ldout + (long long)line0 * nz;
-    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) dst[idx] = r[idx].x;
+    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) {
+        const int line = idx / nz, e = idx - line * nz;
+        dst[idx] = r[line * LS + e].x;
+    }
 }
 
 // ---- column pass over a row-major [n, ncols] complex matrix --------------------
@@ -250,8 +322,8 @@ fft_cols_kernel(double2* __restrict__ data, long long vec_stride, long long oute
                 FftPlan pl, int ncols, int CH, CoulGeom geo)
 {
     extern __shared__ double2 sm[];
-    const int n = pl.n;
-    double2* a = sm; double2* b = sm + n * CH;
+    const int n = pl.n();
+    double2* a = sm; double2* b = sm + pl.lalloc() * CH;
     const int c0 = blockIdx.x * CH;
     const int nc = min(CH, ncols - c0);
     double2* base = data + (long long)blockIdx.z * vec_stride + (long long)blockIdx.y * outer_stride + c0;
@@ -308,29 +380,111 @@ int factorize(int n, int* rad)
 
 struct Plans {
     FftPlan ax[3];
-    double2* d_tw;
+    double2* d_tw;      // one allocation: twiddles, Rader kernels, permutations
 };
+
+bool is_prime(int n)
+{
+    if (n < 2) return false;
+    for (int p = 2; p * p <= n; ++p) if (n % p == 0) return false;
+    return true;
+}
+
+int powmod(long long b, int e, int n)
+{
+    long long r = 1; b %= n;
+    for (; e > 0; e >>= 1) { if (e & 1) r = r * b % n; b = b * b % n; }
+    return (int)r;
+}
+
+int primitive_root(int n)
+{
+    std::vector<int> fac;
+    int m = n - 1;
+    for (int p = 2; p * p <= m; ++p) if (m % p == 0) { fac.push_back(p); while (m % p == 0) m /= p; }
+    if (m > 1) fac.push_back(m);
+    for (int g = 2; g < n; ++g) {
+        bool ok = true;
+        for (int f : fac) if (powmod(g, (n - 1) / f, n) == 1) { ok = false; break; }
+        if (ok) return g;
+    }
+    return -1;
+}
+
+void push_twiddles(std::vector<double2>& tw, int n)
+{
+    for (int k = 0; k < n; ++k) {
+        const long double ang = -2.0L * 3.141592653589793238462643383279502884L * k / n;
+        tw.push_back(make_double2((double)cosl(ang), (double)sinl(ang)));
+    }
+}
 
 int make_plans(isdf_handle* h, const int* mesh, Plans& P)
 {
-    std::vector<double2> tw;
-    size_t off[3];
+    std::vector<double2> tw;          // complex tables, offsets in double2 units
+    std::vector<int> iv;              // integer tables
+    size_t off_tw[3], off_sub[3] = {0, 0, 0}, off_bf[3] = {0, 0, 0}, off_bb[3] = {0, 0, 0};
+    size_t off_perm[3] = {0, 0, 0}, off_iperm[3] = {0, 0, 0};
     for (int d = 0; d < 3; ++d) {
         const int n = mesh[d];
         ARG_CHECK(n >= 1 && n <= 1024);
-        P.ax[d].n = n;
-        P.ax[d].nrad = factorize(n, P.ax[d].rad);
-        if (P.ax[d].nrad < 0) { isdf_set_error("mesh size %d has an unsupported prime factor", n); return ISDF_ERR_ARG; }
-        off[d] = tw.size();
-        for (int k = 0; k < n; ++k) {
-            const long double ang = -2.0L * 3.141592653589793238462643383279502884L * k / n;
-            tw.push_back(make_double2((double)cosl(ang), (double)sinl(ang)));
+        FftPlan& pl = P.ax[d];
+        memset(&pl, 0, sizeof(pl));
+        pl.main.n = n;
+        off_tw[d] = tw.size();
+        push_twiddles(tw, n);
+        int sub_rad[MAX_RAD];
+        const int sub_nrad = (n > 7 && is_prime(n)) ? factorize(n - 1, sub_rad) : -1;
+        if (sub_nrad >= 0) {
+            // Rader: DFT_n as a cyclic convolution of length m = n-1
+            const int m = n - 1, g = primitive_root(n), ginv = powmod(g, n - 2, n);
+            pl.rader = 1;
+            pl.main.nrad = 0;
+            pl.sub.n = m; pl.sub.nrad = sub_nrad;
+            for (int i = 0; i < sub_nrad; ++i) pl.sub.rad[i] = sub_rad[i];
+            off_sub[d] = tw.size();
+            push_twiddles(tw, m);
+            off_perm[d] = iv.size();
+            for (int q = 0; q < m; ++q) iv.push_back(powmod(g, q, n));
+            off_iperm[d] = iv.size();
+            for (int q = 0; q < m; ++q) iv.push_back(powmod(ginv, q, n));
+            const long double PI2 = 2.0L * 3.141592653589793238462643383279502884L;
+            for (int sgn = -1; sgn <= 1; sgn += 2) {
+                (sgn < 0 ? off_bf[d] : off_bb[d]) = tw.size();
+                for (int k = 0; k < m; ++k) {
+                    // bhat[k] = (1/m) sum_j w^(ginv^j) e^{-2 pi i j k / m},  w = e^{sgn 2 pi i / n}
+                    long double re = 0, im = 0;
+                    for (int j = 0; j < m; ++j) {
+                        const long double ang = sgn * PI2 * powmod(ginv, j, n) / n - PI2 * ((long long)j * k % m) / m;
+                        re += cosl(ang); im += sinl(ang);
+                    }
+                    tw.push_back(make_double2((double)(re / m), (double)(im / m)));
+                }
+            }
+        } else {
+            pl.main.nrad = factorize(n, pl.main.rad);
+            if (pl.main.nrad < 0) { isdf_set_error("mesh size %d has an unsupported prime factor", n); return ISDF_ERR_ARG; }
         }
     }
-    CUDA_TRY(cudaMallocAsync((void**)&P.d_tw, sizeof(double2) * tw.size(), h->stream));
+    const size_t bytes_tw = align_up(sizeof(double2) * tw.size(), 256);
+    const size_t bytes_iv = sizeof(int) * std::max<size_t>(iv.size(), 1);
+    CUDA_TRY(cudaMallocAsync((void**)&P.d_tw, bytes_tw + bytes_iv, h->stream));
+    int* d_iv = (int*)((char*)P.d_tw + bytes_tw);
     CUDA_TRY(cudaMemcpyAsync(P.d_tw, tw.data(), sizeof(double2) * tw.size(), cudaMemcpyHostToDevice, h->stream));
+    if (!iv.empty())
+        CUDA_TRY(cudaMemcpyAsync(d_iv, iv.data(), sizeof(int) * iv.size(), cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));
-    for (int d = 0; d < 3; ++d) P.ax[d].tw = P.d_tw + off[d];
+    for (int d = 0; d < 3; ++d) {
+        FftPlan& pl = P.ax[d];
+        pl.main.tw = P.d_tw + off_tw[d];
+        if (pl.rader) {
+            pl.sub.tw = P.d_tw + off_sub[d];
+            pl.bhat_f = P.d_tw + off_bf[d];
+            pl.bhat_b = P.d_tw + off_bb[d];
+            pl.perm = d_iv + off_perm[d];
+            pl.iperm = d_iv + off_iperm[d];
+        }
+    }
     return ISDF_OK;
 }
 
@@ -356,7 +510,8 @@ void fill_geom(CoulGeom& g, const int* mesh, const double* a, double scale)
     g.scale = scale;
 }
 
-int pick_lb(int n, size_t budget) { return (int)std::max<size_t>(1, std::min<size_t>(64, budget / (2 * sizeof(double2) * n))); }
+// lines (or columns) per CTA such that two ping-pong buffers of `nalloc` slots per line fit the budget
+int pick_lb(int nalloc, size_t budget) { return (int)std::max<size_t>(1, std::min<size_t>(64, budget / (2 * sizeof(double2) * nalloc))); }
 
 // forward 3-D transform of nvec real vectors into half spectra (spec[vec*lds + ...]);
 // xmode selects what the x pass fuses (0 plain, 1 sqrt(w coulG), 2 coulG*scale + inverse x)
@@ -367,16 +522,16 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
     cudaStream_t s = h->stream;
     const size_t budget = 96 * 1024;
     {
-        const int LB = pick_lb(nz, budget);
-        const size_t smem = 2 * sizeof(double2) * LB * nz;
+        const int LB = pick_lb(P.ax[2].lalloc(), budget);
+        const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         int rc; if ((rc = set_smem(fft_z_r2c_kernel, smem))) return rc;
         dim3 grid((nx * ny + LB - 1) / LB, nvec);
         fft_z_r2c_kernel<<<grid, FFT_THREADS, smem, s>>>(in, ldin, spec, lds, P.ax[2], nx * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
     {
-        const int CH = std::min(pick_lb(ny, budget), nzh);
-        const size_t smem = 2 * sizeof(double2) * CH * ny;
+        const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
+        const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
         int rc; if ((rc = set_smem(fft_cols_kernel<0>, smem))) return rc;
         dim3 grid((nzh + CH - 1) / CH, nx, nvec);
         fft_cols_kernel<0><<<grid, FFT_THREADS, smem, s>>>(spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
@@ -384,8 +539,8 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
     }
     {
         const int ncols = ny * nzh;
-        const int CH = std::min(pick_lb(nx, budget), ncols);
-        const size_t smem = 2 * sizeof(double2) * CH * nx;
+        const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncols);
+        const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
         dim3 grid((ncols + CH - 1) / CH, 1, nvec);
         int rc;
         if (xmode == 1) {
@@ -412,16 +567,16 @@ int inverse_yz(isdf_handle* h, const Plans& P, const int* mesh, double2* spec, l
     cudaStream_t s = h->stream;
     const size_t budget = 96 * 1024;
     {
-        const int CH = std::min(pick_lb(ny, budget), nzh);
-        const size_t smem = 2 * sizeof(double2) * CH * ny;
+        const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
+        const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
         int rc; if ((rc = set_smem(fft_cols_kernel<3>, smem))) return rc;
         dim3 grid((nzh + CH - 1) / CH, nx, nvec);
         fft_cols_kernel<3><<<grid, FFT_THREADS, smem, s>>>(spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
         CUDA_TRY(cudaGetLastError());
     }
     {
-        const int LB = pick_lb(nz, budget);
-        const size_t smem = 2 * sizeof(double2) * LB * nz;
+        const int LB = pick_lb(P.ax[2].lalloc(), budget);
+        const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         int rc; if ((rc = set_smem(fft_z_c2r_kernel, smem))) return rc;
         dim3 grid((nx * ny + LB - 1) / LB, nvec);
         fft_z_c2r_kernel<<<grid, FFT_THREADS, smem, s>>>(spec, lds, out, ldout, P.ax[2], nx * ny, LB);

@@ -1,4 +1,4 @@
-// FP64 GEMM for the ISDF hot path (sm_100a).
+// FP64 GEMM for the ISDF hot path on the B200 FP64 tensor pipe (sm_100a).
 //
 // One kernel family covers every dense contraction of stages 2-5:
 //   * both operand layouts (k-major rows, or k-contiguous rows),
@@ -6,226 +6,241 @@
 //   * fused epilogues: scale, Hadamard square ((Phi_IP^T Phi)^2 pair densities),
 //     Hadamard multiply (M o W of the exchange build).
 //
-// Arithmetic contract: every C element is one FMA chain over ascending k
-// (no split-K, no re-association), which the C oracle reproduces bit for bit.
+// Inner product: mma.sync.aligned.m8n8k4.f64 (SASS DMMA).  Measured on B200
+// (tools/fp64_probe.cu, profiles/r01_fp64_probe.txt): the instruction
+// accumulates c + a0 b0 + a1 b1 + a2 b2 + a3 b3 as ONE ascending-k FMA chain
+// (bit-identical to fma() over 1.28 M random cases), and its peak equals the
+// DFMA peak (37.0 vs 36.7 TFLOP/s).  So the arithmetic contract of this
+// library -- every C element is one FMA chain over ascending k starting from
+// Cin, no split-K, no re-association, which the C oracle reproduces bit for
+// bit -- holds on the tensor pipe, with 1/32 of the issue slots of DFMA.
 //
-// Tiling: BM x BN CTA tile, 256 threads as a 16 x 16 grid, TM x TN register
-// micro-tile per thread (8x8 -> 128x128 tile, 4x4 -> 64x64 tile), BK = 16,
-// double-buffered shared memory, register-staged global prefetch.
+// Operand feed: a 3-stage shared-memory ring filled with 16-byte cp.async
+// (SASS LDGSTS) copies whose src-size operand zero-fills everything out of
+// range (ragged M/N edges and the K tail); padded row strides (== 4 mod 16
+// doubles) make the DMMA fragment loads bank-conflict free (ncu: 0 conflicts).
+// Operands that are not 16-byte aligned go through a synchronous loader.
+// A TMA variant (per-row cp.async.bulk + mbarrier complete_tx, SASS UBLKCP)
+// was built and measured first (profiles/r01_gemm_loaders.md): equal speed
+// for k-major operands (31.4 vs 30.9 TFLOP/s on the 128x128 tile) but 2-4x
+// slower for k-contiguous ones (a 16-double row is a 128-byte bulk copy, 256
+// of them per stage), and ncu shows the kernel is DMMA-pipe bound either way
+// (tensor pipe 84 % active, no operand-feed stalls) -- so LDGSTS is the loader.
+//
+// Tiling: warp tile 64x32 (8x4 DMMA tiles, 64 FP64 accumulators per lane);
+// CTA tiles 64x128 (4 warps, 2 CTAs/SM; 4 warps/SM already saturate the DMMA
+// pipe, measured) and 64x64 (2 warps) for problems with few tiles.
 #include "common.cuh"
 
 namespace {
 
 constexpr int BK = 16;
-constexpr int NTHREADS = 256;
+constexpr int NSTAGE = 3;
+constexpr int WTM = 64, WTN = 32;          // warp tile
+constexpr int KPAD = BK + 4;               // k-contiguous rows: stride == 4 (mod 16) doubles
 
-template <int BX>
-struct Tile {
-    static constexpr int LD = BX + 2;          // 2-way-conflict-free transposed stores, 16B-aligned rows
-    static constexpr int NJ = BX / 32;         // double2 loads per thread per k-tile
+__device__ __forceinline__ uint32_t smem_u32(const void* p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c[0]), "+d"(c[1])
+                 : "d"(a), "d"(b));
+}
+
+// shared-memory footprint (doubles) of one operand tile of BX rows/cols
+template <int BX, bool KMAJOR>
+struct OpTile {
+    static constexpr int LD = KMAJOR ? BX + 4 : KPAD;       // row stride, == 4 (mod 16)
+    static constexpr int ROWS = KMAJOR ? BK : BX;
+    static constexpr int SIZE = ROWS * LD;
 };
 
-// ---- global -> registers -------------------------------------------------
-// k-major operand: elem(k, x) = p[k*ld + x].  thread t: k = t/16, x = (t%16)*2 + 32*j
-// k-contig operand: elem(k, x) = p[x*ld + k]. thread t: k = 2*(t%8) (+1), x = t/8 + 32*j
-template <int BX, bool KMAJOR>
-__device__ __forceinline__ void load_tile(const double* __restrict__ p, long long ld,
-                                          int dimX, int K, int x0, int k0,
-                                          double2 (&r)[Tile<BX>::NJ], bool fast, int tid)
+// ---- synchronous zero-filling loader (operands that are not 16-byte aligned) -------------------------
+template <int BX, bool KMAJOR, int NT>
+__device__ __forceinline__ void load_slow(double* S, const double* __restrict__ g, long long ld,
+                                          int dimX, int K, int x0, int k0, int tid)
 {
-    constexpr int NJ = Tile<BX>::NJ;
+    using T = OpTile<BX, KMAJOR>;
+    for (int idx = tid; idx < BX * BK; idx += NT) {
+        int x, k;
+        if (KMAJOR) { k = idx / BX; x = idx - k * BX; }
+        else { x = idx / BK; k = idx - x * BK; }
+        double v = 0.0;
+        if (x0 + x < dimX && k0 + k < K)
+            v = KMAJOR ? g[(long long)(k0 + k) * ld + x0 + x] : g[(long long)(x0 + x) * ld + k0 + k];
+        S[KMAJOR ? k * T::LD + x : x * T::LD + k] = v;
+    }
+}
+
+// ---- LDGSTS producer (cp.async, 16-byte chunks, zero-fill of the out-of-range part) --------
+__device__ __forceinline__ void cp_async16(void* dst, const void* src, int src_bytes)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem_u32(dst)), "l"(src), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+template <int BX, bool KMAJOR, int NT>
+__device__ __forceinline__ void load_async(double* S, const double* __restrict__ g, long long ld,
+                                           int dimX, int K, int x0, int k0, int tid)
+{
+    using T = OpTile<BX, KMAJOR>;
     if (KMAJOR) {
-        const int k = k0 + (tid >> 4);
-        const int xb = x0 + ((tid & 15) << 1);
-        if (fast) {
-            const double* q = p + (long long)k * ld + xb;
+        constexpr int CPR = BX / 2;                     // 16-byte chunks per k row
 #pragma unroll
-            for (int j = 0; j < NJ; ++j) r[j] = *reinterpret_cast<const double2*>(q + 32 * j);
-        } else {
-#pragma unroll
-            for (int j = 0; j < NJ; ++j) {
-                const int x = xb + 32 * j;
-                double2 v = make_double2(0.0, 0.0);
-                if (k < K) {
-                    const double* q = p + (long long)k * ld + x;
-                    if (x < dimX) v.x = q[0];
-                    if (x + 1 < dimX) v.y = q[1];
-                }
-                r[j] = v;
-            }
+        for (int idx = tid; idx < BK * CPR; idx += NT) {
+            const int r = idx / CPR, c = (idx - r * CPR) * 2;
+            const int x = x0 + c, k = k0 + r;
+            int bytes = 0;
+            if (k < K) bytes = (x + 1 < dimX) ? 16 : (x < dimX ? 8 : 0);
+            const double* src = bytes ? g + (long long)k * ld + x : g;
+            cp_async16(S + r * T::LD + c, src, bytes);
         }
     } else {
-        const int k = k0 + ((tid & 7) << 1);
-        const int xb = x0 + (tid >> 3);
-        if (fast) {
+        constexpr int CPR = BK / 2;                     // 16-byte chunks per x row
 #pragma unroll
-            for (int j = 0; j < NJ; ++j)
-                r[j] = *reinterpret_cast<const double2*>(p + (long long)(xb + 32 * j) * ld + k);
-        } else {
-#pragma unroll
-            for (int j = 0; j < NJ; ++j) {
-                const int x = xb + 32 * j;
-                double2 v = make_double2(0.0, 0.0);
-                if (x < dimX) {
-                    const double* q = p + (long long)x * ld + k;
-                    if (k < K) v.x = q[0];
-                    if (k + 1 < K) v.y = q[1];
-                }
-                r[j] = v;
-            }
+        for (int idx = tid; idx < BX * CPR; idx += NT) {
+            const int r = idx / CPR, c = (idx - r * CPR) * 2;
+            const int x = x0 + r, k = k0 + c;
+            int bytes = 0;
+            if (x < dimX) bytes = (k + 1 < K) ? 16 : (k < K ? 8 : 0);
+            const double* src = bytes ? g + (long long)x * ld + k : g;
+            cp_async16(S + r * T::LD + c, src, bytes);
         }
     }
 }
 
-// ---- registers -> shared (always stored as S[k][x]) ------------------------
-template <int BX, bool KMAJOR, bool NEG>
-__device__ __forceinline__ void store_tile(double* __restrict__ S,
-                                           const double2 (&r)[Tile<BX>::NJ], int tid)
+// ---- one k-tile of DMMAs on a resident stage ------------------------------------------------
+template <bool AK, bool BKM, bool NEG, int LDA, int LDB>
+__device__ __forceinline__ void compute_stage(const double* __restrict__ As, const double* __restrict__ Bs,
+                                              double (&acc)[8][4][2], int wm, int wn, int g, int t)
 {
-    constexpr int NJ = Tile<BX>::NJ;
-    constexpr int LD = Tile<BX>::LD;
-    if (KMAJOR) {
-        double* s = S + (tid >> 4) * LD + ((tid & 15) << 1);
 #pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-            double2 v = r[j];
-            if (NEG) { v.x = -v.x; v.y = -v.y; }
-            *reinterpret_cast<double2*>(s + 32 * j) = v;
-        }
-    } else {
-        double* s = S + ((tid & 7) << 1) * LD + (tid >> 3);
+    for (int kk = 0; kk < BK; kk += 4) {
+        double a[8], b[4];
 #pragma unroll
-        for (int j = 0; j < NJ; ++j) {
-            double2 v = r[j];
-            if (NEG) { v.x = -v.x; v.y = -v.y; }
-            s[32 * j] = v.x;
-            s[LD + 32 * j] = v.y;
+        for (int i = 0; i < 8; ++i) {
+            const double v = AK ? As[(kk + t) * LDA + wm + 8 * i + g] : As[(wm + 8 * i + g) * LDA + kk + t];
+            a[i] = NEG ? -v : v;
         }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            b[j] = BKM ? Bs[(kk + t) * LDB + wn + 8 * j + g] : Bs[(wn + 8 * j + g) * LDB + kk + t];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma884(acc[i][j], a[i], b[j]);
     }
 }
 
-template <int TM, int TN, bool AK, bool BKM, bool NEG>
-__global__ void __launch_bounds__(NTHREADS, 1)
+template <int WM, int WN, bool AK, bool BKM, bool NEG>
+__global__ void __launch_bounds__(32 * WM * WN, (WM * WN <= 4) ? 2 : 1)
 dgemm_kernel(GemmParams p)
 {
-    constexpr int BM = 16 * TM, BN = 16 * TN;
-    constexpr int LDA = Tile<BM>::LD, LDB = Tile<BN>::LD;
-    extern __shared__ __align__(16) double smem[];
-    double* As = smem;                       // [2][BK][LDA]
-    double* Bs = smem + 2 * BK * LDA;        // [2][BK][LDB]
+    constexpr int BM = WTM * WM, BN = WTN * WN, NT = 32 * WM * WN;
+    using TA = OpTile<BM, AK>;
+    using TB = OpTile<BN, BKM>;
+    constexpr int STAGE = TA::SIZE + TB::SIZE;
+    extern __shared__ __align__(128) double smem[];
 
-    const int tid = threadIdx.x;
-    const int m0 = blockIdx.x * BM;
-    const int n0 = blockIdx.y * BN;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = (warp / WN) * WTM, wn = (warp % WN) * WTN;
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
     if (p.upper_only && m0 >= n0 + BN) return;
     const int M = p.M, N = p.N, K = p.K;
 
-    const int tx = tid & 15, ty = tid >> 4;
+    // fast path needs 16-byte aligned rows in both operands
+    const bool fast = ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) && ((p.lda & 1) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(p.B) & 15) == 0) && ((p.ldb & 1) == 0);
+    const int nfull = fast ? (K + BK - 1) / BK : 0;
+    auto issue = [&](int kt) {
+        double* As = smem + (kt % NSTAGE) * STAGE;
+        load_async<BM, AK, NT>(As, p.A, p.lda, M, K, m0, kt * BK, tid);
+        load_async<BN, BKM, NT>(As + TA::SIZE, p.B, p.ldb, N, K, n0, kt * BK, tid);
+    };
+    for (int kt = 0; kt < NSTAGE - 1; ++kt) {
+        if (kt < nfull) issue(kt);
+        cp_async_commit();
+    }
 
-    double acc[TM][TN];
     // accumulator init (the FMA chain starts here)
+    double acc[8][4][2];
 #pragma unroll
-    for (int i = 0; i < TM; ++i) {
-        const int m = m0 + (i >> 2) * 64 + ty * 4 + (i & 3);
+    for (int i = 0; i < 8; ++i) {
+        const int m = m0 + wm + 8 * i + g;
 #pragma unroll
-        for (int j = 0; j < TN; ++j) {
-            const int n = n0 + (j >> 2) * 64 + tx * 4 + (j & 3);
-            double v = 0.0;
-            if (p.Cin != nullptr && m < M && n < N) v = p.Cin[(long long)m * p.ldcin + n];
-            acc[i][j] = v;
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + wn + 8 * j + 2 * t;
+            double v0 = 0.0, v1 = 0.0;
+            if (p.Cin != nullptr && m < M) {
+                const double* c = p.Cin + (long long)m * p.ldcin + n;
+                if (n < N) v0 = c[0];
+                if (n + 1 < N) v1 = c[1];
+            }
+            acc[i][j][0] = v0; acc[i][j][1] = v1;
         }
     }
 
-    const bool alignedA = ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) && ((p.lda & 1) == 0);
-    const bool alignedB = ((reinterpret_cast<uintptr_t>(p.B) & 15) == 0) && ((p.ldb & 1) == 0);
-    const bool fullM = alignedA && (m0 + BM <= M);
-    const bool fullN = alignedB && (n0 + BN <= N);
-
-    double2 ra[Tile<BM>::NJ], rb[Tile<BN>::NJ];
-    const int nk = (K + BK - 1) / BK;
-    if (nk > 0) {
-        const bool fk = (BK <= K);
-        load_tile<BM, AK>(p.A, p.lda, M, K, m0, 0, ra, fullM && fk, tid);
-        load_tile<BN, BKM>(p.B, p.ldb, N, K, n0, 0, rb, fullN && fk, tid);
-        store_tile<BM, AK, NEG>(As, ra, tid);
-        store_tile<BN, BKM, false>(Bs, rb, tid);
+    for (int kt = 0; kt < nfull; ++kt) {
+        const int s = kt % NSTAGE;
+        cp_async_wait<NSTAGE - 2>();
+        __syncthreads();                       // tile kt landed; every warp is done with the stage refilled below
+        if (kt + NSTAGE - 1 < nfull) issue(kt + NSTAGE - 1);
+        cp_async_commit();
+        const double* As = smem + s * STAGE;
+        compute_stage<AK, BKM, NEG, TA::LD, TB::LD>(As, As + TA::SIZE, acc, wm, wn, g, t);
     }
-    __syncthreads();
-
-    for (int kt = 0; kt < nk; ++kt) {
-        const int cur = kt & 1;
-        if (kt + 1 < nk) {
-            const int k0 = (kt + 1) * BK;
-            const bool fk = (k0 + BK <= K);
-            load_tile<BM, AK>(p.A, p.lda, M, K, m0, k0, ra, fullM && fk, tid);
-            load_tile<BN, BKM>(p.B, p.ldb, N, K, n0, k0, rb, fullN && fk, tid);
-        }
-        const double* as = As + cur * BK * LDA + ty * 4;
-        const double* bs = Bs + cur * BK * LDB + tx * 4;
-#pragma unroll
-        for (int k = 0; k < BK; ++k) {
-            double a[TM], b[TN];
-#pragma unroll
-            for (int g = 0; g < TM / 4; ++g) {
-                const double2 v0 = *reinterpret_cast<const double2*>(as + k * LDA + g * 64);
-                const double2 v1 = *reinterpret_cast<const double2*>(as + k * LDA + g * 64 + 2);
-                a[g * 4 + 0] = v0.x; a[g * 4 + 1] = v0.y; a[g * 4 + 2] = v1.x; a[g * 4 + 3] = v1.y;
-            }
-#pragma unroll
-            for (int g = 0; g < TN / 4; ++g) {
-                const double2 v0 = *reinterpret_cast<const double2*>(bs + k * LDB + g * 64);
-                const double2 v1 = *reinterpret_cast<const double2*>(bs + k * LDB + g * 64 + 2);
-                b[g * 4 + 0] = v0.x; b[g * 4 + 1] = v0.y; b[g * 4 + 2] = v1.x; b[g * 4 + 3] = v1.y;
-            }
-#pragma unroll
-            for (int i = 0; i < TM; ++i)
-#pragma unroll
-                for (int j = 0; j < TN; ++j)
-                    acc[i][j] = fma(a[i], b[j], acc[i][j]);
-        }
-        if (kt + 1 < nk) {
-            store_tile<BM, AK, NEG>(As + (cur ^ 1) * BK * LDA, ra, tid);
-            store_tile<BN, BKM, false>(Bs + (cur ^ 1) * BK * LDB, rb, tid);
-        }
+    // unaligned operands: synchronous zero-filling loads
+    for (int k0 = nfull * BK; k0 < K; k0 += BK) {
         __syncthreads();
+        double* As = smem;
+        double* Bs = As + TA::SIZE;
+        load_slow<BM, AK, NT>(As, p.A, p.lda, M, K, m0, k0, tid);
+        load_slow<BN, BKM, NT>(Bs, p.B, p.ldb, N, K, n0, k0, tid);
+        __syncthreads();
+        compute_stage<AK, BKM, NEG, TA::LD, TB::LD>(As, Bs, acc, wm, wn, g, t);
     }
 
-    // epilogue
+    // epilogue: lane holds C[m][n], C[m][n+1] of every 8x8 tile
 #pragma unroll
-    for (int i = 0; i < TM; ++i) {
-        const int m = m0 + (i >> 2) * 64 + ty * 4 + (i & 3);
+    for (int i = 0; i < 8; ++i) {
+        const int m = m0 + wm + 8 * i + g;
         if (m >= M) continue;
 #pragma unroll
-        for (int jg = 0; jg < TN / 4; ++jg) {
-            const int n = n0 + jg * 64 + tx * 4;
-            double v[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                double x = acc[i][jg * 4 + q];
-                if (p.epi == EPI_SQUARE) x = x * x;
-                else if (p.epi == EPI_MUL) {
-                    if (n + q < N) x = x * p.E[(long long)m * p.lde + n + q];
-                } else x = p.alpha * x;
-                v[q] = x;
-            }
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + wn + 8 * j + 2 * t;
+            if (n >= N) continue;
+            double v0 = acc[i][j][0], v1 = acc[i][j][1];
+            if (p.epi == EPI_SQUARE) { v0 = v0 * v0; v1 = v1 * v1; }
+            else if (p.epi == EPI_MUL) {
+                const double* e = p.E + (long long)m * p.lde + n;
+                v0 = v0 * e[0];
+                if (n + 1 < N) v1 = v1 * e[1];
+            } else { v0 = p.alpha * v0; v1 = p.alpha * v1; }
             double* c = p.C + (long long)m * p.ldc + n;
-            if (n + 3 < N && ((reinterpret_cast<uintptr_t>(c) & 15) == 0)) {
-                *reinterpret_cast<double2*>(c) = make_double2(v[0], v[1]);
-                *reinterpret_cast<double2*>(c + 2) = make_double2(v[2], v[3]);
+            if (n + 1 < N && ((reinterpret_cast<uintptr_t>(c) & 15) == 0)) {
+                *reinterpret_cast<double2*>(c) = make_double2(v0, v1);
             } else {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) if (n + q < N) c[q] = v[q];
+                c[0] = v0;
+                if (n + 1 < N) c[1] = v1;
             }
         }
     }
 }
 
-template <int TM, int TN, bool AK, bool BKM, bool NEG>
+template <int WM, int WN, bool AK, bool BKM, bool NEG>
 int launch_cfg(isdf_handle* h, const GemmParams& p)
 {
-    constexpr int BM = 16 * TM, BN = 16 * TN;
-    const size_t smem = sizeof(double) * 2 * BK * (Tile<BM>::LD + Tile<BN>::LD);
-    auto kern = dgemm_kernel<TM, TN, AK, BKM, NEG>;
+    constexpr int BM = WTM * WM, BN = WTN * WN, NT = 32 * WM * WN;
+    const size_t smem = sizeof(double) * NSTAGE * (OpTile<BM, AK>::SIZE + OpTile<BN, BKM>::SIZE);
+    auto kern = dgemm_kernel<WM, WN, AK, BKM, NEG>;
     static bool configured = false;
     if (!configured) {
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -234,7 +249,7 @@ int launch_cfg(isdf_handle* h, const GemmParams& p)
     dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN);
     const bool prof = h->prof_on && h->prof_n < h->prof_cap;
     if (prof) CUDA_TRY(cudaEventRecord(h->prof_ev[2 * h->prof_n], h->stream));
-    kern<<<grid, NTHREADS, smem, h->stream>>>(p);
+    kern<<<grid, NT, smem, h->stream>>>(p);
     CUDA_TRY(cudaGetLastError());
     if (prof) {
         CUDA_TRY(cudaEventRecord(h->prof_ev[2 * h->prof_n + 1], h->stream));
@@ -254,19 +269,19 @@ int launch_cfg(isdf_handle* h, const GemmParams& p)
     return ISDF_OK;
 }
 
-template <int TM, int TN>
+template <int WM, int WN>
 int dispatch_layout(isdf_handle* h, const GemmParams& p)
 {
     const int key = (p.a_kmajor ? 4 : 0) | (p.b_kmajor ? 2 : 0) | (p.neg ? 1 : 0);
     switch (key) {
-    case 0: return launch_cfg<TM, TN, false, false, false>(h, p);
-    case 1: return launch_cfg<TM, TN, false, false, true>(h, p);
-    case 2: return launch_cfg<TM, TN, false, true, false>(h, p);
-    case 3: return launch_cfg<TM, TN, false, true, true>(h, p);
-    case 4: return launch_cfg<TM, TN, true, false, false>(h, p);
-    case 5: return launch_cfg<TM, TN, true, false, true>(h, p);
-    case 6: return launch_cfg<TM, TN, true, true, false>(h, p);
-    default: return launch_cfg<TM, TN, true, true, true>(h, p);
+    case 0: return launch_cfg<WM, WN, false, false, false>(h, p);
+    case 1: return launch_cfg<WM, WN, false, false, true>(h, p);
+    case 2: return launch_cfg<WM, WN, false, true, false>(h, p);
+    case 3: return launch_cfg<WM, WN, false, true, true>(h, p);
+    case 4: return launch_cfg<WM, WN, true, false, false>(h, p);
+    case 5: return launch_cfg<WM, WN, true, false, true>(h, p);
+    case 6: return launch_cfg<WM, WN, true, true, false>(h, p);
+    default: return launch_cfg<WM, WN, true, true, true>(h, p);
     }
 }
 
@@ -277,8 +292,9 @@ int gemm_launch(isdf_handle* h, const GemmParams& p)
     if (p.M <= 0 || p.N <= 0) return ISDF_OK;
     ARG_CHECK(p.A && p.B && p.C && p.K >= 0);
     ARG_CHECK(p.epi != EPI_MUL || p.E != nullptr);
-    // 128x128 tiles when they fill the machine, else 64x64
-    const long long big_tiles = (long long)((p.M + 127) / 128) * ((p.N + 127) / 128);
-    if (big_tiles >= h->num_sms) return dispatch_layout<8, 8>(h, p);
-    return dispatch_layout<4, 4>(h, p);
+    auto tiles = [&](int bm, int bn) { return (long long)((p.M + bm - 1) / bm) * ((p.N + bn - 1) / bn); };
+    // 64x128 CTAs (2 per SM) once they cover the SMs; 64x64 for problems with few tiles
+    if (h->gemm_force == 2 || (h->gemm_force == 0 && tiles(64, 128) >= (long long)h->num_sms))
+        return dispatch_layout<1, 4>(h, p);
+    return dispatch_layout<1, 2>(h, p);
 }

@@ -177,9 +177,11 @@ def test_fit_aux_matches_oracle(handle):
     assert abs(pair(got2) - pair(zeta_ref)).max() < 1e-9 * scale
 
 
-@pytest.mark.parametrize('mesh', [[12, 10, 9], [7, 11, 13], [16, 8, 5], [35, 6, 4]])
+@pytest.mark.parametrize('mesh', [[12, 10, 9], [7, 11, 13], [16, 8, 5], [35, 6, 4],
+                                  [71, 5, 4], [6, 23, 47], [4, 22, 71]])
 def test_coulomb_apply_matches_numpy_fft(handle, mesh):
-    """Stage 4 FFT + fused 4 pi/G^2 on even/odd/prime meshes, triclinic lattice."""
+    """Stage 4 FFT + fused 4 pi/G^2 on even/odd/prime meshes (primes > 7 go through
+    Rader's algorithm, 22 = 2*11 through the direct large-radix stage), triclinic lattice."""
     import torch
     rng = np.random.default_rng(11)
     a = np.array([[5.0, 0.3, 0.1], [0.2, 4.5, -0.4], [0.0, 0.6, 6.0]])

@@ -126,6 +126,17 @@ int main()
             if (rep) printf("DMMA  %d CTA/SM x 512 thr: %.2f TFLOP/s (%.3f ms)\n", bpsm, fl / ms / 1e9, ms);
         }
     }
+    // DMMA rate vs resident warps and independent accumulators (GEMM-like: 32 accumulators)
+    for (int thr = 64; thr <= 1024; thr *= 2) {
+        float ms;
+        dmma_tput<32><<<prop.multiProcessorCount, thr>>>(out, 4000);
+        cudaEventRecord(e0);
+        dmma_tput<32><<<prop.multiProcessorCount, thr>>>(out, 4000);
+        cudaEventRecord(e1); cudaEventSynchronize(e1);
+        cudaEventElapsedTime(&ms, e0, e1);
+        double fl = 2.0 * 256 * 32.0 * 4000 * (thr / 32) * prop.multiProcessorCount;
+        printf("DMMA  ILP32, %4d thr/SM (%2d warps): %.2f TFLOP/s\n", thr, thr / 32, fl / ms / 1e9);
+    }
     printf("last error: %s\n", cudaGetErrorString(cudaGetLastError()));
     return 0;
 }
