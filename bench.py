@@ -244,7 +244,11 @@ def run_b200(args):
     from pyscf_isdf_b200 import workloads
     from pyscf_isdf_b200.isdf import ISDF
     name, cell, nao, ng, npts = target_dims(args)
-    mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=False)
+    comm = None
+    if world > 1:
+        from pyscf_isdf_b200.dist import Comm
+        comm = Comm()                 # grid sharded by x-planes, one rank per GPU (pyscf_isdf_b200/dist.py)
+    mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=False, comm=comm)
     h = mydf.handle
     dm_host = workloads.synthetic_dm(nao)[None]
     dm_pinned = torch.from_numpy(dm_host).pin_memory()
@@ -341,7 +345,7 @@ def run_b200(args):
         'data': 'synthetic',
         'config': {'workload': workloads.describe(name), 'c': args.c, 'nao': nao, 'ngrids': ng,
                    'n_ip': int(mydf.n_ip), 'fit': args.fit, 'l2': 'inputs_exceed_l2' if 8.0 * ng * nao > 126e6 else 'inputs_fit_l2',
-                   'parallelism': 'single' if world == 1 else 'replicas%d' % world},
+                   'parallelism': 'single' if world == 1 else 'grid-slab x%d (all-gather/all-to-all/all-reduce over NCCL)' % world},
         'build_s': build_s, 'jk_s': jk_ms / 1e3, 'stages_ms': stages_ms,
         'flop_model': fm,
         'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},

@@ -72,6 +72,37 @@ int isdf_select_ip(isdf_handle* h, const double* phi, int nao, long long ng, lon
                    long long* h_ip, double* h_resid, int* h_rank,
                    void* ws, size_t ws_bytes);
 
+/* Stage 2, stepwise form used when the grid is sharded over several GPUs (one
+ * process per GPU, each owning the slab [g_offset, g_offset+ngl) of grid points,
+ * its columns of phi and of the factor Lt).  Per panel of <= isdf_select_panel_width()
+ * pivots:  candidates (local: the `quota` largest residuals, packed with their phi
+ * and factor columns into rows of isdf_select_row_len(nao,k0) doubles, quota+1 rows)
+ * -> [all-gather of the blocks, done by the caller] -> panel (every rank factors the
+ * gathered candidate set redundantly; pivots are exact while the largest candidate
+ * residual exceeds the largest residual outside the set) -> flush (local: new factor
+ * rows for the slab).  isdf_select_ip is this loop with one rank.  U (nullable,
+ * [npts, ldu]) receives U[j,i] = L[ip_i, j], the transposed pivot factor that
+ * isdf_fit_aux_from_U solves with. */
+typedef struct isdf_select_plan isdf_select_plan;
+int isdf_select_max_rows(void);
+int isdf_select_panel_width(void);
+int isdf_select_row_len(int nao, int k0);
+int isdf_select_first_quota(int nranks);
+int isdf_select_next_quota(int quota, int nb, int nbmax, int nranks);
+int isdf_select_create(isdf_handle* h, int nao, long long ngl, long long g_offset,
+                       long long ng_total, int npts, void* ws, size_t ws_bytes,
+                       isdf_select_plan** out);
+int isdf_select_destroy(isdf_select_plan* pl);
+int isdf_select_begin(isdf_select_plan* pl, const double* phi, long long ldphi, double* h_dmax);
+int isdf_select_set_tol(isdf_select_plan* pl, double tol);
+int isdf_select_candidates(isdf_select_plan* pl, const double* phi, long long ldphi,
+                           const double* Lt, long long ldl, int k0, int quota, double* block);
+int isdf_select_panel(isdf_select_plan* pl, const double* blocks, int nranks, int quota,
+                      int k0, int nbmax, double* U, long long ldu, int* h_nb, int* h_stop);
+int isdf_select_flush(isdf_select_plan* pl, const double* phi, long long ldphi,
+                      double* Lt, long long ldl, int k0, int nb);
+int isdf_select_finish(isdf_select_plan* pl, int rank, long long* h_ip, double* h_resid);
+
 /* Stage 3 [spec].  A = (X^T X)^2, B = (X^T phi)^2 with X = phi[:, ip];
  * zeta[np, ldz] = A^-1 B by Cholesky (A = U^T U) and two triangular solves. */
 size_t isdf_fit_aux_ws_bytes(int nao, long long ng, int np);
@@ -82,6 +113,12 @@ int isdf_fit_aux(isdf_handle* h, const double* phi, int nao, long long ng, long 
  * (in place on Lt); mathematically identical to isdf_fit_aux. */
 int isdf_fit_aux_from_factor(isdf_handle* h, double* Lt, long long ldl, long long ng,
                              const long long* h_ip, int np, void* ws, size_t ws_bytes);
+
+/* Same solve on one slab of grid points, with the transposed pivot factor U
+ * from isdf_select_panel: Z[np, ngl] <- U^-1 Z.  No communication between slabs. */
+size_t isdf_fit_from_U_ws_bytes(long long ngl, int np);
+int isdf_fit_aux_from_U(isdf_handle* h, double* U, long long ldu, int np,
+                        double* Z, long long ldz, long long ngl, void* ws, size_t ws_bytes);
 
 /* Stage 4.  Conventions of pyscf/pbc/tools/pbc.py:149-211 (fft/ifft) and
  * :269-356 (coulG = 4 pi/|G|^2, G=0 -> 0), normalisation of
@@ -99,6 +136,22 @@ int isdf_coulomb_apply(isdf_handle* h, const double* in, long long ldin, int nve
                        const int* h_mesh, const double* h_a,
                        double* out, long long ldout, void* ws, size_t ws_bytes);
 
+/* Stage 4 with the grid sharded by x-planes over ranks: local z/y passes, pack for the
+ * all-to-all that re-shards the half spectra to (y,z)-column slabs (the exchange itself
+ * is the caller's NCCL all_to_all), unpack, x pass fused with sqrt(weight*coulG).
+ * The rank's partial W is then isdf_dgemm over its spectral slab (K = 2*nx*ncl,
+ * alpha = vol/ng^2, upper_only) + isdf_symmetrize_upper, summed over ranks by the caller.
+ * spec/send/recv/Y are complex128 buffers; lds/ldy count complex elements. */
+int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int nvec, int nxl,
+                const int* h_mesh, void* spec, long long lds);
+int isdf_fft_pack(isdf_handle* h, const void* spec, long long lds, int nvec, int nxl, int ncols,
+                  const int* h_col_off, int nranks, void* send);
+int isdf_fft_unpack(isdf_handle* h, const void* recv, int nvec, const int* h_x_off, int nranks,
+                    int ncl, void* Y, long long ldy);
+int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nvec,
+                       const int* h_mesh, const double* h_a, int col0, int ncl);
+int isdf_symmetrize_upper(isdf_handle* h, double* W, long long ld, int n);
+
 /* Stage 5 [spec; exact limit pyscf/pbc/df/fft_jk.py:33-109,177-302].
  * X[nao, np] = phi[:, ip];  J = X diag(W rho) X^T, rho_P = (X^T D X)_PP;
  * K = X ((X^T D X) o W) X^T.  dm/vj/vk: [nset, nao, nao]. */
@@ -107,6 +160,15 @@ int isdf_get_jk(isdf_handle* h, const double* X, const double* W,
                 const double* dm, int nset, int nao, int np,
                 int with_j, int with_k, double* vj, double* vk,
                 void* ws, size_t ws_bytes);
+
+/* Contribution of the interpolation points [p0, p0+npl) to J and K, given the row
+ * block Wrows[npl, ldw] = W[p0:p0+npl, :]; the full J/K is the sum over disjoint
+ * blocks (one block per rank, all-reduced by the caller).  p0 must be even. */
+size_t isdf_get_jk_block_ws_bytes(int nao, int np, int npl);
+int isdf_get_jk_block(isdf_handle* h, const double* X, const double* Wrows, long long ldw,
+                      int p0, int npl, const double* dm, int nset, int nao, int np,
+                      int with_j, int with_k, double* vj, double* vk,
+                      void* ws, size_t ws_bytes);
 
 /* Generic FP64 GEMM used by every stage (exposed for tests / bench):
  * C[m,n] = epi( Cin[m,n] -/+ sum_k opA(k,m) opB(k,n) ), one FMA chain per

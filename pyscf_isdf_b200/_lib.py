@@ -30,6 +30,30 @@ SIGNATURES = {
     'isdf_select_ip_ws_bytes': (c_sz, [c_int, c_ll, c_int]),
     'isdf_select_ip': (c_int, [c_vp, c_vp, c_int, c_ll, c_ll, c_int, c_dbl, c_vp, c_ll,
                                c_vp, c_vp, c_vp, c_vp, c_sz]),
+    'isdf_select_max_rows': (c_int, []),
+    'isdf_select_panel_width': (c_int, []),
+    'isdf_select_row_len': (c_int, [c_int, c_int]),
+    'isdf_select_first_quota': (c_int, [c_int]),
+    'isdf_select_next_quota': (c_int, [c_int, c_int, c_int, c_int]),
+    'isdf_select_create': (c_int, [c_vp, c_int, c_ll, c_ll, c_ll, c_int, c_vp, c_sz, ctypes.POINTER(c_vp)]),
+    'isdf_select_destroy': (c_int, [c_vp]),
+    'isdf_select_begin': (c_int, [c_vp, c_vp, c_ll, ctypes.POINTER(c_dbl)]),
+    'isdf_select_set_tol': (c_int, [c_vp, c_dbl]),
+    'isdf_select_candidates': (c_int, [c_vp, c_vp, c_ll, c_vp, c_ll, c_int, c_int, c_vp]),
+    'isdf_select_panel': (c_int, [c_vp, c_vp, c_int, c_int, c_int, c_int, c_vp, c_ll,
+                                  ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
+    'isdf_select_flush': (c_int, [c_vp, c_vp, c_ll, c_vp, c_ll, c_int, c_int]),
+    'isdf_select_finish': (c_int, [c_vp, c_int, c_vp, c_vp]),
+    'isdf_fit_from_U_ws_bytes': (c_sz, [c_ll, c_int]),
+    'isdf_fit_aux_from_U': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_ll, c_ll, c_vp, c_sz]),
+    'isdf_fft_zy': (c_int, [c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_vp, c_ll]),
+    'isdf_fft_pack': (c_int, [c_vp, c_vp, c_ll, c_int, c_int, c_int, c_vp, c_int, c_vp]),
+    'isdf_fft_unpack': (c_int, [c_vp, c_vp, c_int, c_vp, c_int, c_int, c_vp, c_ll]),
+    'isdf_fft_x_coulomb': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_vp, c_int, c_int]),
+    'isdf_symmetrize_upper': (c_int, [c_vp, c_vp, c_ll, c_int]),
+    'isdf_get_jk_block_ws_bytes': (c_sz, [c_int, c_int, c_int]),
+    'isdf_get_jk_block': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_int, c_int, c_int,
+                                  c_int, c_int, c_vp, c_vp, c_vp, c_sz]),
     'isdf_fit_aux_ws_bytes': (c_sz, [c_int, c_ll, c_int]),
     'isdf_fit_aux': (c_int, [c_vp, c_vp, c_int, c_ll, c_ll, c_vp, c_int, c_vp, c_ll, c_vp, c_sz]),
     'isdf_fit_aux_from_factor': (c_int, [c_vp, c_vp, c_ll, c_ll, c_vp, c_int, c_vp, c_sz]),
@@ -122,6 +146,32 @@ class Handle:
     def empty(self, *shape, dtype=None):
         import torch
         return torch.empty(*shape, dtype=dtype or torch.float64, device=self.torch_device)
+
+    def zeros(self, *shape, dtype=None):
+        import torch
+        return torch.zeros(*shape, dtype=dtype or torch.float64, device=self.torch_device)
+
+    def empty_complex(self, *shape):
+        import torch
+        return torch.empty(*shape, dtype=torch.complex128, device=self.torch_device)
+
+    @staticmethod
+    def as_real(t):
+        """complex128 [.., n] -> float64 view [.., 2n] (same memory)"""
+        import torch
+        v = torch.view_as_real(t)
+        return v.reshape(*t.shape[:-1], 2 * t.shape[-1])
+
+    def index(self, idx):
+        import torch
+        return torch.as_tensor(np.asarray(idx, dtype=np.int64), device=self.torch_device)
+
+    def synchronize(self):
+        import torch
+        torch.cuda.synchronize(self.torch_device)
+
+    def timer(self):
+        return StageTimer(self)
 
     def workspace(self, nbytes):
         import torch
@@ -227,3 +277,121 @@ class Handle:
         idx = np.ascontiguousarray(idx, dtype=np.int64)
         check(self.lib.isdf_gather_cols(self.h, c_vp(src.data_ptr()), ldin, nrows, hptr(idx), len(idx),
                                         c_vp(out.data_ptr()), ldout))
+
+
+    # -- stepwise stage 2-5 pieces used by the multi-GPU driver (pyscf_isdf_b200/dist.py) ---------
+    def select_create(self, nao, ngl, g_offset, ng_total, npts):
+        nbytes = self.lib.isdf_select_ip_ws_bytes(nao, ngl, npts)
+        ws = self.workspace(nbytes)
+        plan = c_vp()
+        check(self.lib.isdf_select_create(self.h, nao, ngl, g_offset, ng_total, npts,
+                                          c_vp(ws.data_ptr()), nbytes, ctypes.byref(plan)))
+        return SelectPlan(self, plan, ws)
+
+    def fit_aux_from_U(self, U, ldu, npts, Z, ldz, ngl):
+        nbytes = self.lib.isdf_fit_from_U_ws_bytes(ngl, npts)
+        ws = self.workspace(nbytes)
+        check(self.lib.isdf_fit_aux_from_U(self.h, c_vp(U.data_ptr()), ldu, npts, c_vp(Z.data_ptr()), ldz, ngl,
+                                           c_vp(ws.data_ptr()), nbytes))
+
+    def fft_zy(self, vin, ldin, nvec, nxl, mesh, spec, lds):
+        mesh = np.ascontiguousarray(mesh, dtype=np.int32)
+        check(self.lib.isdf_fft_zy(self.h, c_vp(vin.data_ptr()), ldin, nvec, nxl, hptr(mesh),
+                                   c_vp(spec.data_ptr()), lds))
+
+    def fft_pack(self, spec, lds, nvec, nxl, ncols, col_off, send):
+        col_off = np.ascontiguousarray(col_off, dtype=np.int32)
+        check(self.lib.isdf_fft_pack(self.h, c_vp(spec.data_ptr()), lds, nvec, nxl, ncols, hptr(col_off),
+                                     len(col_off) - 1, c_vp(send.data_ptr())))
+
+    def fft_unpack(self, recv, nvec, x_off, ncl, Y, ldy):
+        x_off = np.ascontiguousarray(x_off, dtype=np.int32)
+        check(self.lib.isdf_fft_unpack(self.h, c_vp(recv.data_ptr()), nvec, hptr(x_off), len(x_off) - 1, ncl,
+                                       c_vp(Y.data_ptr()), ldy))
+
+    def fft_x_coulomb(self, Y, ldy, nvec, mesh, a, col0, ncl):
+        mesh = np.ascontiguousarray(mesh, dtype=np.int32)
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        check(self.lib.isdf_fft_x_coulomb(self.h, c_vp(Y.data_ptr()), ldy, nvec, hptr(mesh), hptr(a), col0, ncl))
+
+    def symmetrize_upper(self, W, ld, n):
+        check(self.lib.isdf_symmetrize_upper(self.h, c_vp(W.data_ptr()), ld, n))
+
+    def get_jk_block(self, X, Wrows, ldw, p0, npl, dm, nset, nao, npts, with_j, with_k, vj, vk, ws=None):
+        nbytes = self.lib.isdf_get_jk_block_ws_bytes(nao, npts, npl)
+        if ws is None:
+            ws = self.workspace(nbytes)
+        check(self.lib.isdf_get_jk_block(self.h, c_vp(X.data_ptr()), c_vp(Wrows.data_ptr()), ldw, p0, npl,
+                                         c_vp(dm.data_ptr()), nset, nao, npts, int(with_j), int(with_k),
+                                         c_vp(vj.data_ptr()) if vj is not None else None,
+                                         c_vp(vk.data_ptr()) if vk is not None else None,
+                                         c_vp(ws.data_ptr()), ws.numel()))
+        return ws
+
+
+class StageTimer:
+    """CUDA-event stopwatch on the handle's stream: mark(name) closes the interval since the previous mark."""
+
+    def __init__(self, handle):
+        import torch
+        self._torch = torch
+        self._dev = handle.torch_device
+        self._marks = []
+        self._last = torch.cuda.Event(enable_timing=True)
+        self._last.record()
+        self._times = None
+
+    def mark(self, name):
+        e = self._torch.cuda.Event(enable_timing=True)
+        e.record()
+        self._marks.append((name, self._last, e))
+        self._last = e
+        self._times = None
+
+    @property
+    def times(self):
+        if self._times is None:
+            self._torch.cuda.synchronize(self._dev)
+            self._times = {n: a.elapsed_time(b) for n, a, b in self._marks}
+        return self._times
+
+
+class SelectPlan:
+    """One stage-2 run on one slab of grid points (include/isdf_b200.h, isdf_select_*)."""
+
+    def __init__(self, handle, plan, ws):
+        self.handle, self.plan, self.ws = handle, plan, ws
+        self.lib = handle.lib
+
+    def close(self):
+        if self.plan:
+            self.lib.isdf_select_destroy(self.plan)
+            self.plan = None
+
+    def begin(self, phi, ldphi):
+        dmax = c_dbl()
+        check(self.lib.isdf_select_begin(self.plan, c_vp(phi.data_ptr()), ldphi, ctypes.byref(dmax)))
+        return dmax.value
+
+    def set_tol(self, tol):
+        check(self.lib.isdf_select_set_tol(self.plan, float(tol)))
+
+    def candidates(self, phi, ldphi, Lt, ldl, k0, quota, block):
+        check(self.lib.isdf_select_candidates(self.plan, c_vp(phi.data_ptr()), ldphi, c_vp(Lt.data_ptr()), ldl,
+                                              k0, quota, c_vp(block.data_ptr())))
+
+    def panel(self, blocks, nranks, quota, k0, nbmax, U, ldu):
+        nb, stop = c_int(), c_int()
+        check(self.lib.isdf_select_panel(self.plan, c_vp(blocks.data_ptr()), nranks, quota, k0, nbmax,
+                                         c_vp(U.data_ptr()) if U is not None else None, ldu,
+                                         ctypes.byref(nb), ctypes.byref(stop)))
+        return nb.value, bool(stop.value)
+
+    def flush(self, phi, ldphi, Lt, ldl, k0, nb):
+        check(self.lib.isdf_select_flush(self.plan, c_vp(phi.data_ptr()), ldphi, c_vp(Lt.data_ptr()), ldl, k0, nb))
+
+    def finish(self, rank):
+        ip = np.zeros(max(rank, 1), dtype=np.int64)
+        resid = np.zeros(max(rank, 1), dtype=np.float64)
+        check(self.lib.isdf_select_finish(self.plan, rank, hptr(ip), hptr(resid)))
+        return ip[:rank].copy(), resid[:rank].copy()

@@ -232,6 +232,7 @@ struct CoulGeom {
     int nzh;
     double b[9];        // reciprocal vectors (rows)
     double scale;       // multiplies the kernel (1/ng for V)
+    int col0;           // first (y,z)-column of this rank's slab in the x pass (0 when not sharded)
 };
 
 __device__ __forceinline__ double coulG_raw(const CoulGeom& g, int fx, int fy, int fz)
@@ -338,7 +339,7 @@ fft_cols_kernel(double2* __restrict__ data, long long vec_stride, long long oute
     if (MODE == 1 || MODE == 2) {
         for (int idx = threadIdx.x; idx < n * nc; idx += blockDim.x) {
             const int i = idx / nc, c = idx - i * nc;
-            const int col = c0 + c;
+            const int col = geo.col0 + c0 + c;
             const int iy = col / geo.nzh, iz = col - iy * geo.nzh;
             double f = coulG_at(geo, i, iy, iz);
             if (MODE == 1) {
@@ -508,6 +509,7 @@ void fill_geom(CoulGeom& g, const int* mesh, const double* a, double scale)
     for (int d = 0; d < 3; ++d) g.mesh[d] = mesh[d];
     g.nzh = mesh[2] / 2 + 1;
     g.scale = scale;
+    g.col0 = 0;
 }
 
 // lines (or columns) per CTA such that two ping-pong buffers of `nalloc` slots per line fit the budget
@@ -664,5 +666,133 @@ extern "C" int isdf_build_W(isdf_handle* h, const double* zeta, int np, long lon
     CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_COULOMB], s));
     h->ev_used[ISDF_STAGE_COULOMB] = true;
     CUDA_TRY(cudaFreeAsync(P.d_tw, s));
+    return ISDF_OK;
+}
+
+// ---- slab-decomposed 3-D transform (grid sharded over ranks by x-planes) --------------------
+// Each rank holds x-planes [x_off[r], x_off[r+1]) of every vector.  z and y passes are local;
+// one all-to-all (done by the caller, NCCL) re-shards the half spectra from x-planes to
+// (y,z)-column slabs; the x pass with the fused Coulomb weight then runs on whole x lines.
+namespace {
+
+__global__ void fft_pack_kernel(const double2* __restrict__ spec, long long lds, int nxl, int ncols,
+                                int c0, int ncl, double2* __restrict__ send)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncl) return;
+    const int x = blockIdx.y, v = blockIdx.z;
+    send[((long long)v * nxl + x) * ncl + c] = spec[(long long)v * lds + (long long)x * ncols + c0 + c];
+}
+
+__global__ void fft_unpack_kernel(const double2* __restrict__ recv, int nxl, int x0, int ncl,
+                                  double2* __restrict__ Y, long long ldy)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncl) return;
+    const int x = blockIdx.y, v = blockIdx.z;
+    Y[(long long)v * ldy + (long long)(x0 + x) * ncl + c] = recv[((long long)v * nxl + x) * ncl + c];
+}
+
+}  // namespace
+
+// local z (R2C) and y passes: in[nvec, ldin] real, x-planes of this rank -> spec[nvec][nxl][ny*nzh] complex
+extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int nvec, int nxl,
+                           const int* h_mesh, void* spec, long long lds)
+{
+    ARG_CHECK(h && in && h_mesh && spec && nvec > 0 && nxl > 0 && nxl <= h_mesh[0]);
+    const int ny = h_mesh[1], nz = h_mesh[2], nzh = nz / 2 + 1;
+    ARG_CHECK(ldin >= (long long)nxl * ny * nz && lds >= (long long)nxl * ny * nzh);
+    Plans P; int rc;
+    if ((rc = make_plans(h, h_mesh, P))) return rc;
+    cudaStream_t s = h->stream;
+    const size_t budget = 96 * 1024;
+    CoulGeom geo; memset(&geo, 0, sizeof(geo));
+    {
+        const int LB = pick_lb(P.ax[2].lalloc(), budget);
+        const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
+        if ((rc = set_smem(fft_z_r2c_kernel, smem))) return rc;
+        dim3 grid((nxl * ny + LB - 1) / LB, nvec);
+        fft_z_r2c_kernel<<<grid, FFT_THREADS, smem, s>>>(in, ldin, (double2*)spec, lds, P.ax[2], nxl * ny, LB);
+        CUDA_TRY(cudaGetLastError());
+    }
+    {
+        const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
+        const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
+        if ((rc = set_smem(fft_cols_kernel<0>, smem))) return rc;
+        dim3 grid((nzh + CH - 1) / CH, nxl, nvec);
+        fft_cols_kernel<0><<<grid, FFT_THREADS, smem, s>>>((double2*)spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
+        CUDA_TRY(cudaGetLastError());
+    }
+    h->other_launches += 2;
+    CUDA_TRY(cudaFreeAsync(P.d_tw, s));
+    return ISDF_OK;
+}
+
+// send buffer for the all-to-all: block of rank r = [nvec][nxl][h_col_off[r+1]-h_col_off[r]], blocks in rank order
+extern "C" int isdf_fft_pack(isdf_handle* h, const void* spec, long long lds, int nvec, int nxl, int ncols,
+                             const int* h_col_off, int nranks, void* send)
+{
+    ARG_CHECK(h && spec && h_col_off && send && nranks >= 1 && h_col_off[0] == 0 && h_col_off[nranks] == ncols);
+    for (int r = 0; r < nranks; ++r) {
+        const int c0 = h_col_off[r], ncl = h_col_off[r + 1] - c0;
+        if (ncl <= 0) continue;
+        double2* dst = (double2*)send + (long long)nvec * nxl * c0;
+        dim3 grid((ncl + 127) / 128, nxl, nvec);
+        fft_pack_kernel<<<grid, 128, 0, h->stream>>>((const double2*)spec, lds, nxl, ncols, c0, ncl, dst);
+        h->other_launches++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return ISDF_OK;
+}
+
+// receive buffer (block of rank r = [nvec][nx_r][ncl]) -> Y[nvec][nx][ncl] (row stride ldy, complex units)
+extern "C" int isdf_fft_unpack(isdf_handle* h, const void* recv, int nvec, const int* h_x_off, int nranks,
+                               int ncl, void* Y, long long ldy)
+{
+    ARG_CHECK(h && recv && h_x_off && Y && nranks >= 1 && ncl > 0 && h_x_off[0] == 0);
+    ARG_CHECK(ldy >= (long long)h_x_off[nranks] * ncl);
+    for (int r = 0; r < nranks; ++r) {
+        const int x0 = h_x_off[r], nxl = h_x_off[r + 1] - x0;
+        if (nxl <= 0) continue;
+        const double2* src = (const double2*)recv + (long long)nvec * ncl * x0;
+        dim3 grid((ncl + 127) / 128, nxl, nvec);
+        fft_unpack_kernel<<<grid, 128, 0, h->stream>>>(src, nxl, x0, ncl, (double2*)Y, ldy);
+        h->other_launches++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return ISDF_OK;
+}
+
+// x pass over the column slab [col0, col0+ncl) of the (y,z) plane, fused with the
+// sqrt(weight * coulG) factor of the W build: Y[nvec][nx][ncl] in place.
+extern "C" int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nvec,
+                                  const int* h_mesh, const double* h_a, int col0, int ncl)
+{
+    ARG_CHECK(h && Y && h_mesh && h_a && nvec > 0 && ncl > 0 && col0 >= 0);
+    const int nx = h_mesh[0];
+    ARG_CHECK(col0 + ncl <= h_mesh[1] * (h_mesh[2] / 2 + 1) && ldy >= (long long)nx * ncl);
+    Plans P; int rc;
+    if ((rc = make_plans(h, h_mesh, P))) return rc;
+    CoulGeom geo; fill_geom(geo, h_mesh, h_a, 1.0);
+    geo.col0 = col0;
+    const size_t budget = 96 * 1024;
+    const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncl);
+    const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
+    if ((rc = set_smem(fft_cols_kernel<1>, smem))) return rc;
+    dim3 grid((ncl + CH - 1) / CH, 1, nvec);
+    fft_cols_kernel<1><<<grid, FFT_THREADS, smem, h->stream>>>((double2*)Y, ldy, 0, P.ax[0], ncl, CH, geo);
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches++;
+    CUDA_TRY(cudaFreeAsync(P.d_tw, h->stream));
+    return ISDF_OK;
+}
+
+extern "C" int isdf_symmetrize_upper(isdf_handle* h, double* W, long long ld, int n)
+{
+    ARG_CHECK(h && W && n > 0 && ld >= n);
+    dim3 blk(32, 8), grd((n + 31) / 32, (n + 7) / 8);
+    symmetrize_upper_kernel<<<grd, blk, 0, h->stream>>>(W, ld, n);
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches++;
     return ISDF_OK;
 }

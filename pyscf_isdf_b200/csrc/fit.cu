@@ -258,3 +258,41 @@ extern "C" int isdf_fit_aux_from_factor(isdf_handle* h, double* Lt, long long ld
     h->ev_used[ISDF_STAGE_FIT] = true;
     return ISDF_OK;
 }
+
+// zeta = U^-1 Z for the local slab Z[np, ngl] (in place), U[j,i] = L[ip_i, j] the transposed
+// pivot factor assembled by isdf_select_panel.  Columns (grid points) are independent, so a
+// grid-sharded run needs no communication here.
+extern "C" size_t isdf_fit_from_U_ws_bytes(long long ngl, int np)
+{
+    FitWs w;
+    WsAlloc a(nullptr, 0);
+    const size_t nblk = (np + CB - 1) / CB;
+    w.Vinv = a.get<double>(nblk * CB * CB);
+    w.tmp = a.get<double>((size_t)CB * pad8(ngl));
+    w.info = a.get<int>(4);
+    return a.off + 256;
+}
+
+extern "C" int isdf_fit_aux_from_U(isdf_handle* h, double* U, long long ldu, int np,
+                                   double* Z, long long ldz, long long ngl, void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && U && Z && ws && np > 0 && ngl > 0 && ldu >= np && ldz >= ngl);
+    if (isdf_fit_from_U_ws_bytes(ngl, np) > ws_bytes) {
+        isdf_set_error("fit_aux_from_U workspace too small: need %zu have %zu", isdf_fit_from_U_ws_bytes(ngl, np), ws_bytes);
+        return ISDF_ERR_WS;
+    }
+    WsAlloc a(ws, ws_bytes);
+    const size_t nblk = (np + CB - 1) / CB;
+    double* Vinv = a.get<double>(nblk * CB * CB);
+    double* tmp = a.get<double>((size_t)CB * pad8(ngl));
+    int* info = a.get<int>(4);
+    int rc;
+    cudaStream_t s = h->stream;
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FIT], s));
+    CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int) * 4, s));
+    if ((rc = invert_diag_blocks(h, U, ldu, np, Vinv, info))) return rc;
+    if ((rc = solve_upper(h, U, ldu, np, Vinv, Z, ldz, ngl, tmp))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FIT], s));
+    h->ev_used[ISDF_STAGE_FIT] = true;
+    return ISDF_OK;
+}

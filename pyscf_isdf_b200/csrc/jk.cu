@@ -20,13 +20,13 @@ __global__ void coldot_kernel(const double* __restrict__ X, const double* __rest
     rho[P] = s;
 }
 
-// v = W rho, one warp per row
-__global__ void gemv_rows_kernel(const double* __restrict__ W, long long ld, int n,
+// v = W rho for a block of rows, one warp per row
+__global__ void gemv_rows_kernel(const double* __restrict__ W, long long ld, int nrows, int n,
                                  const double* __restrict__ x, double* __restrict__ y)
 {
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
-    if (row >= n) return;
+    if (row >= nrows) return;
     const double* w = W + (long long)row * ld;
     double s = 0.0;
     for (int j = lane; j < n; j += 32) s = fma(w[j], x[j], s);
@@ -36,12 +36,12 @@ __global__ void gemv_rows_kernel(const double* __restrict__ W, long long ld, int
 
 // Y[mu,P] = X[mu,P] * v[P]
 __global__ void scale_cols_kernel(const double* __restrict__ X, const double* __restrict__ v,
-                                  int nao, int np, long long ld, double* __restrict__ Y)
+                                  int nao, int np, long long ldx, long long ldy, double* __restrict__ Y)
 {
     const int P = blockIdx.x * blockDim.x + threadIdx.x;
     if (P >= np) return;
     const double f = v[P];
-    for (int mu = blockIdx.y; mu < nao; mu += gridDim.y) Y[(long long)mu * ld + P] = X[(long long)mu * ld + P] * f;
+    for (int mu = blockIdx.y; mu < nao; mu += gridDim.y) Y[(long long)mu * ldy + P] = X[(long long)mu * ldx + P] * f;
 }
 
 int gemm6(isdf_handle* h, int M, int N, int K, const double* A, long long lda, int ak,
@@ -57,28 +57,36 @@ int gemm6(isdf_handle* h, int M, int N, int K, const double* A, long long lda, i
 
 }  // namespace
 
-extern "C" size_t isdf_get_jk_ws_bytes(int nao, int np)
+extern "C" size_t isdf_get_jk_block_ws_bytes(int nao, int np, int npl)
 {
-    return sizeof(double) * ((size_t)2 * nao * np + (size_t)np * np + 2 * (size_t)np) + 8192;
+    return sizeof(double) * ((size_t)nao * np + 2 * (size_t)nao * npl + (size_t)npl * np + (size_t)np + npl) + 8192;
 }
 
-extern "C" int isdf_get_jk(isdf_handle* h, const double* X, const double* W,
-                           const double* dm, int nset, int nao, int np,
-                           int with_j, int with_k, double* vj, double* vk,
-                           void* ws, size_t ws_bytes)
+extern "C" size_t isdf_get_jk_ws_bytes(int nao, int np) { return isdf_get_jk_block_ws_bytes(nao, np, np); }
+
+// Contribution of the interpolation points [p0, p0+npl) (a row block of W) to J and K:
+//   J_part = X_b diag(W_b rho) X_b^T ,  K_part = X_b ((X_b^T D X) o W_b) X^T
+// Summed over disjoint blocks this is the full J/K (the caller all-reduces).
+extern "C" int isdf_get_jk_block(isdf_handle* h, const double* X, const double* Wrows, long long ldw,
+                                 int p0, int npl, const double* dm, int nset, int nao, int np,
+                                 int with_j, int with_k, double* vj, double* vk,
+                                 void* ws, size_t ws_bytes)
 {
-    ARG_CHECK(h && X && W && dm && ws && nset > 0 && nao > 0 && np > 0);
+    ARG_CHECK(h && X && Wrows && dm && ws && nset > 0 && nao > 0 && np > 0);
+    ARG_CHECK(p0 >= 0 && npl > 0 && p0 + npl <= np && ldw >= np);
     ARG_CHECK((!with_j || vj) && (!with_k || vk));
-    if (isdf_get_jk_ws_bytes(nao, np) > ws_bytes) {
-        isdf_set_error("get_jk workspace too small: need %zu have %zu", isdf_get_jk_ws_bytes(nao, np), ws_bytes);
+    if (isdf_get_jk_block_ws_bytes(nao, np, npl) > ws_bytes) {
+        isdf_set_error("get_jk workspace too small: need %zu have %zu", isdf_get_jk_block_ws_bytes(nao, np, npl), ws_bytes);
         return ISDF_ERR_WS;
     }
     WsAlloc a(ws, ws_bytes);
-    double* T = a.get<double>((size_t)nao * np);
-    double* U = a.get<double>((size_t)nao * np);
-    double* Nm = a.get<double>((size_t)np * np);
+    double* T = a.get<double>((size_t)nao * np);       // D X
+    double* Ub = a.get<double>((size_t)nao * npl);     // X_b diag(v)
+    double* Vb = a.get<double>((size_t)npl * nao);     // N_b X^T
+    double* Nm = a.get<double>((size_t)npl * np);      // (X_b^T T) o W_b
     double* rho = a.get<double>(np);
-    double* v = a.get<double>(np);
+    double* v = a.get<double>(npl);
+    const double* Xb = X + p0;                         // columns p0.. of X (row stride np)
     cudaStream_t s = h->stream;
     int rc;
     CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_JK], s));
@@ -88,21 +96,30 @@ extern "C" int isdf_get_jk(isdf_handle* h, const double* X, const double* W,
         if ((rc = gemm6(h, nao, np, nao, D, nao, 0, X, np, 1, T, np, nullptr, 0, EPI_STORE))) return rc;
         if (with_j) {
             coldot_kernel<<<(np + 255) / 256, 256, 0, s>>>(X, T, nao, np, np, rho);
-            gemv_rows_kernel<<<(np + 7) / 8, 256, 0, s>>>(W, np, np, rho, v);
-            dim3 g((np + 255) / 256, std::min(nao, 1024));
-            scale_cols_kernel<<<g, 256, 0, s>>>(X, v, nao, np, np, U);
+            gemv_rows_kernel<<<(npl + 7) / 8, 256, 0, s>>>(Wrows, ldw, npl, np, rho, v);
+            dim3 g((npl + 255) / 256, std::min(nao, 1024));
+            scale_cols_kernel<<<g, 256, 0, s>>>(Xb, v, nao, npl, np, npl, Ub);
             CUDA_TRY(cudaGetLastError());
             h->other_launches += 3;
-            if ((rc = gemm6(h, nao, nao, np, U, np, 0, X, np, 0, vj + (size_t)i * nao * nao, nao, nullptr, 0, EPI_STORE))) return rc;
+            // J_part = Ub X_b^T
+            if ((rc = gemm6(h, nao, nao, npl, Ub, npl, 0, Xb, np, 0, vj + (size_t)i * nao * nao, nao, nullptr, 0, EPI_STORE))) return rc;
         }
         if (with_k) {
-            // N = (X^T T) o W ; U = X N ; K = U X^T
-            if ((rc = gemm6(h, np, np, nao, X, np, 1, T, np, 1, Nm, np, W, np, EPI_MUL))) return rc;
-            if ((rc = gemm6(h, nao, np, np, X, np, 0, Nm, np, 1, U, np, nullptr, 0, EPI_STORE))) return rc;
-            if ((rc = gemm6(h, nao, nao, np, U, np, 0, X, np, 0, vk + (size_t)i * nao * nao, nao, nullptr, 0, EPI_STORE))) return rc;
+            // N_b = (X_b^T T) o W_b ; V_b = N_b X^T ; K_part = X_b V_b
+            if ((rc = gemm6(h, npl, np, nao, Xb, np, 1, T, np, 1, Nm, np, Wrows, ldw, EPI_MUL))) return rc;
+            if ((rc = gemm6(h, npl, nao, np, Nm, np, 0, X, np, 0, Vb, nao, nullptr, 0, EPI_STORE))) return rc;
+            if ((rc = gemm6(h, nao, nao, npl, Xb, np, 0, Vb, nao, 1, vk + (size_t)i * nao * nao, nao, nullptr, 0, EPI_STORE))) return rc;
         }
     }
     CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_JK], s));
     h->ev_used[ISDF_STAGE_JK] = true;
     return ISDF_OK;
+}
+
+extern "C" int isdf_get_jk(isdf_handle* h, const double* X, const double* W,
+                           const double* dm, int nset, int nao, int np,
+                           int with_j, int with_k, double* vj, double* vk,
+                           void* ws, size_t ws_bytes)
+{
+    return isdf_get_jk_block(h, X, W, np, 0, np, dm, nset, nao, np, with_j, with_k, vj, vk, ws, ws_bytes);
 }

@@ -113,28 +113,49 @@ __global__ void radix_hist_kernel(const double* __restrict__ d, long long ng, co
         if (sh[i]) atomicAdd(&hist[i], sh[i]);
 }
 
-__global__ void radix_scan_kernel(SelState* st, int shift, int bits, unsigned int* hist, int last)
+// one CTA of 1024 threads: suffix sums over <= 2048 bins, then the owning bin is located in parallel
+__global__ void __launch_bounds__(1024) radix_scan_kernel(SelState* st, int shift, int bits, unsigned int* hist, int last)
 {
-    if (threadIdx.x != 0) return;
+    __shared__ long long suf[2049];      // suf[b] = sum_{b' >= b} hist[b']
+    __shared__ int s_ob;
     const int nbins = 1 << bits;
-    if (!st->all_fit) {
-        long long cum = 0;
-        int ob = -1;
-        for (int b = nbins - 1; b >= 0; --b) {
-            if (cum + (long long)hist[b] > st->remaining) { ob = b; break; }
-            cum += hist[b];
+    const int tid = threadIdx.x;
+    if (st->all_fit) {
+        for (int b = tid; b < nbins; b += blockDim.x) hist[b] = 0;
+        return;
+    }
+    for (int b = tid; b < 2049; b += blockDim.x) suf[b] = (b < nbins) ? (long long)hist[b] : 0;
+    if (tid == 0) s_ob = -1;
+    __syncthreads();
+    for (int off = 1; off < nbins; off <<= 1) {
+        long long v[2];
+        for (int i = 0; i < 2; ++i) {
+            const int b = tid + i * 1024;
+            v[i] = (b < nbins) ? suf[b] + ((b + off < nbins) ? suf[b + off] : 0) : 0;
         }
+        __syncthreads();
+        for (int i = 0; i < 2; ++i) { const int b = tid + i * 1024; if (b < nbins) suf[b] = v[i]; }
+        __syncthreads();
+    }
+    const long long remaining = st->remaining;
+    // ob = largest b with suf[b] > remaining (the bin where the quota is crossed)
+    for (int b = tid; b < nbins; b += blockDim.x)
+        if (suf[b] > remaining && suf[b + 1] <= remaining) s_ob = b;
+    __syncthreads();
+    if (tid == 0) {
+        const int ob = s_ob;
         if (ob < 0) {
             // everything under this prefix fits (can only happen on the first pass)
             st->all_fit = 1;
             st->tie_key = 0; st->tie_take = 0;
         } else {
-            st->remaining -= cum;
+            st->remaining -= suf[ob + 1];
             st->prefix = (st->prefix << bits) | (unsigned long long)ob;
             if (last) { st->tie_key = st->prefix; st->tie_take = st->remaining; }
         }
     }
-    for (int b = 0; b < nbins; ++b) hist[b] = 0;
+    __syncthreads();
+    for (int b = tid; b < nbins; b += blockDim.x) hist[b] = 0;
 }
 
 // ---- ordered compaction of the candidate set (single CTA, ascending g) --------
@@ -335,17 +356,99 @@ __global__ void gather_lpp_kernel(const double* __restrict__ LppT, const int* __
     if (k < nb && j < nb) LppP[k * NB + j] = (j < k) ? LppT[(long long)j * MCAP + piv_local[k]] : 0.0;
 }
 
-__global__ void record_pivots_kernel(const int* __restrict__ cand, const int* __restrict__ piv_local,
-                                     int nb, int k0, long long* __restrict__ ip_dev)
+// Candidate block row (doubles): [0] global grid index, [1] residual d, [2],[3] aux,
+// [4 .. 4+nao) phi[:, g], [4+naop .. 4+naop+k0) Lt[:k0, g].  Row `nrows` (trailer):
+// [0] = [1] = -1, [2] = number of real candidates, [3] = largest residual outside the set.
+constexpr int META = 4;
+
+__global__ void pack_candidates_kernel(const double* __restrict__ phi, long long ldphi, int nao, int naop,
+                                       const double* __restrict__ Lt, long long ldl, int k0,
+                                       const int* __restrict__ cand, const double* __restrict__ dC,
+                                       const SelState* __restrict__ st, long long g_offset,
+                                       int nrows, int rl, double* __restrict__ block)
 {
-    const int k = threadIdx.x;
-    if (k < nb) ip_dev[k0 + k] = cand[piv_local[k]];
+    const int i = blockIdx.y;                       // row
+    const int count = min(st->m, nrows);
+    double* row = block + (long long)i * rl;
+    const int ncol = rl - META;
+    if (i >= count) {
+        for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < rl; c += gridDim.x * blockDim.x) {
+            double v = 0.0;
+            if (c < 2) v = -1.0;
+            if (i == nrows && c == 2) v = (double)count;
+            if (i == nrows && c == 3) v = st->theta_key ? __longlong_as_double((long long)st->theta_key) : 0.0;
+            row[c] = v;
+        }
+        return;
+    }
+    const long long g = cand[i];
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < ncol; c += gridDim.x * blockDim.x) {
+        double v = 0.0;
+        if (c < nao) v = phi[(long long)c * ldphi + g];
+        else if (c >= naop && c - naop < k0) v = Lt[(long long)(c - naop) * ldl + g];
+        row[META + c] = v;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < META) {
+        const int c = threadIdx.x;
+        row[c] = c == 0 ? (double)(g + g_offset) : (c == 1 ? dC[i] : 0.0);
+    }
 }
 
-__global__ void mark_selected_kernel(const long long* __restrict__ ip_dev, int k0, int nb, double* __restrict__ d)
+// gathered blocks of all ranks -> candidate index / residual arrays, theta = max over ranks
+__global__ void panel_prepare_kernel(const double* __restrict__ blocks, int nranks, int nrows, int rl,
+                                     int* __restrict__ cand, double* __restrict__ dC, SelState* st)
+{
+    const int m = nranks * (nrows + 1);
+    for (int c = threadIdx.x; c < m; c += blockDim.x) {
+        const double* row = blocks + (long long)c * rl;
+        cand[c] = (int)row[0];
+        dC[c] = row[1];
+    }
+    if (threadIdx.x == 0) {
+        double theta = 0.0;
+        for (int r = 0; r < nranks; ++r)
+            theta = fmax(theta, blocks[((long long)r * (nrows + 1) + nrows) * rl + 3]);
+        st->theta_key = dkey(theta);
+        st->m = m;
+        st->barrier = 0;
+    }
+}
+
+// PivRows[k][:] = blocks[piv_local[k]][:]; pivots' global indices recorded
+__global__ void gather_rows_kernel(const double* __restrict__ blocks, int rl, const int* __restrict__ piv_local,
+                                   int nb, int k0, double* __restrict__ PivRows, long long* __restrict__ ip_dev)
+{
+    const int k = blockIdx.y;
+    if (k >= nb) return;
+    const double* src = blocks + (long long)piv_local[k] * rl;
+    double* dst = PivRows + (long long)k * rl;
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < rl; c += gridDim.x * blockDim.x) dst[c] = src[c];
+    if (blockIdx.x == 0 && threadIdx.x == 0) ip_dev[k0 + k] = (long long)src[0];
+}
+
+// U[j, k0+k] = L[ip_(k0+k), j]: the pivot rows of the factor, transposed (upper triangular)
+__global__ void assemble_U_kernel(const double* __restrict__ PivRows, int rl, int off_l,
+                                  const double* __restrict__ LppT, const int* __restrict__ piv_local,
+                                  int nb, int k0, int npts, double* __restrict__ U, long long ldu)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;      // pivot within the panel (fast index)
+    if (k >= nb) return;
+    for (int j = blockIdx.y; j < npts; j += gridDim.y) {
+        double v = 0.0;
+        if (j < k0) v = PivRows[(long long)k * rl + off_l + j];
+        else if (j - k0 <= k) v = LppT[(long long)(j - k0) * MCAP + piv_local[k]];
+        U[(long long)j * ldu + k0 + k] = v;
+    }
+}
+
+__global__ void mark_selected_kernel(const long long* __restrict__ ip_dev, int k0, int nb,
+                                     long long g_offset, long long ngl, double* __restrict__ d)
 {
     const int k = threadIdx.x;
-    if (k < nb) d[ip_dev[k0 + k]] = -1.0;
+    if (k < nb) {
+        const long long g = ip_dev[k0 + k] - g_offset;
+        if (g >= 0 && g < ngl) d[g] = -1.0;
+    }
 }
 
 // Per-grid-point triangular sweep over the panel columns + residual update.
@@ -393,45 +496,44 @@ panel_sweep_kernel(double* __restrict__ Ltp, long long ldl, long long ng, int nb
 }
 
 struct SelWs {
-    double* d; unsigned int* hist; int* cand; double* dC; double* PhiC; double* LcOld; double* T;
-    double* LppT; int* piv_local; double* PhiP; double* LtP; double* LppP; double* resid_dev;
-    long long* ip_dev; Partial* partials; SelState* st;
+    double* d; unsigned int* hist; int* cand; double* dC; double* T;
+    double* LppT; int* piv_local; double* PivRows; double* LppP; double* resid_dev;
+    long long* ip_dev; Partial* partials; SelState* st; double* block;
 };
 
-size_t carve(SelWs& w, void* ws, size_t bytes, int nao, long long ng, int npts)
+inline int pad2(int n) { return (n + 1) & ~1; }
+inline int row_len(int nao, int k0) { return META + pad2(nao) + pad2(k0); }
+
+size_t carve(SelWs& w, void* ws, size_t bytes, int nao, long long ngl, int npts)
 {
     WsAlloc a(ws, bytes);
-    w.d = a.get<double>(ng);
+    const size_t rl = row_len(nao, npts);
+    w.d = a.get<double>(ngl);
     w.hist = a.get<unsigned int>(2048);
     w.cand = a.get<int>(MCAP);
     w.dC = a.get<double>(MCAP);
-    w.PhiC = a.get<double>((size_t)nao * MCAP);
-    w.LcOld = a.get<double>((size_t)npts * MCAP);
     w.T = a.get<double>((size_t)MCAP * MCAP);
     w.LppT = a.get<double>((size_t)NB * MCAP);
     w.piv_local = a.get<int>(NB);
-    w.PhiP = a.get<double>((size_t)nao * NB);
-    w.LtP = a.get<double>((size_t)npts * NB);
+    w.PivRows = a.get<double>((size_t)NB * rl);
     w.LppP = a.get<double>((size_t)NB * NB);
     w.resid_dev = a.get<double>(npts);
     w.ip_dev = a.get<long long>(npts);
     w.partials = a.get<Partial>(2 * PANEL_CTAS);
     w.st = a.get<SelState>(1);
+    w.block = a.get<double>((size_t)MCAP * rl);       // local candidate block (quota+1 <= MCAP rows)
     return a.off + 256;
 }
 
 }  // namespace
 
-static int gather_dev(isdf_handle* h, const double* in, long long ldin, int nrows,
-                      const int* idx, int ncols, double* out, long long ldout)
-{
-    if (nrows <= 0 || ncols <= 0) return ISDF_OK;
-    dim3 grid((ncols + 127) / 128, std::min(nrows, 4096));
-    gather_cols_kernel<<<grid, 128, 0, h->stream>>>(in, ldin, nrows, idx, ncols, out, ldout);
-    CUDA_TRY(cudaGetLastError());
-    h->other_launches++;
-    return ISDF_OK;
-}
+// Host-side plan of one selection run (dimensions + carved workspace pointers).
+struct isdf_select_plan {
+    isdf_handle* h;
+    int nao, npts;
+    long long ngl, g_offset, ng_total;
+    SelWs w;
+};
 
 extern "C" int isdf_gather_cols(isdf_handle* h, const double* in, long long ldin, int nrows,
                                 const long long* h_idx, int ncols, double* out, long long ldout)
@@ -456,19 +558,214 @@ extern "C" size_t isdf_select_ip_ws_bytes(int nao, long long ng, int npts)
     return carve(w, nullptr, 0, nao, ng, npts);
 }
 
-static int gemm_simple(isdf_handle* h, int M, int N, int K, const double* A, long long lda,
-                       const double* B, long long ldb, double* C, long long ldc,
-                       const double* Cin, int neg, int epi)
+extern "C" int isdf_select_max_rows(void) { return MCAP; }
+extern "C" int isdf_select_panel_width(void) { return NB; }
+extern "C" int isdf_select_row_len(int nao, int k0) { return row_len(nao, k0); }
+
+// ---- stepwise interface (one slab of grid points per rank) -----------------------------------
+extern "C" int isdf_select_create(isdf_handle* h, int nao, long long ngl, long long g_offset,
+                                  long long ng_total, int npts, void* ws, size_t ws_bytes,
+                                  isdf_select_plan** out)
+{
+    ARG_CHECK(h && ws && out && nao > 0 && ngl > 0 && npts > 0 && g_offset >= 0);
+    ARG_CHECK(ng_total >= g_offset + ngl && ng_total < 0x7fffffffLL && npts <= ng_total);
+    isdf_select_plan* pl = new isdf_select_plan();
+    pl->h = h; pl->nao = nao; pl->npts = npts; pl->ngl = ngl; pl->g_offset = g_offset; pl->ng_total = ng_total;
+    const size_t need = carve(pl->w, ws, ws_bytes, nao, ngl, npts);
+    if (need > ws_bytes) {
+        isdf_set_error("select_ip workspace too small: need %zu have %zu", need, ws_bytes);
+        delete pl;
+        return ISDF_ERR_WS;
+    }
+    *out = pl;
+    return ISDF_OK;
+}
+
+extern "C" int isdf_select_destroy(isdf_select_plan* pl)
+{
+    delete pl;
+    return ISDF_OK;
+}
+
+// d_g = (sum_mu phi^2)^2 on the local slab; *h_dmax = its maximum (host sync)
+extern "C" int isdf_select_begin(isdf_select_plan* pl, const double* phi, long long ldphi, double* h_dmax)
+{
+    ARG_CHECK(pl && phi && h_dmax && ldphi >= pl->ngl);
+    isdf_handle* h = pl->h;
+    cudaStream_t s = h->stream;
+    SelWs& w = pl->w;
+    init_diag_kernel<<<(unsigned)((pl->ngl + 255) / 256), 256, 0, s>>>(phi, ldphi, pl->nao, pl->ngl, w.d);
+    state_init_kernel<<<1, 1024, 0, s>>>(w.d, pl->ngl, 0.0, w.st);
+    CUDA_TRY(cudaMemsetAsync(w.hist, 0, 2048 * sizeof(unsigned int), s));
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches += 2;
+    SelState* hst = (SelState*)h->h_pinned;
+    CUDA_TRY(cudaMemcpyAsync(hst, w.st, sizeof(SelState), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    *h_dmax = hst->dmax0;
+    return ISDF_OK;
+}
+
+// stop threshold on the residual diagonal (absolute); the default rule is
+// tol = ng_total * eps * max_g d_g (pyscf/lib/scipy_helper.py:88-90)
+extern "C" int isdf_select_set_tol(isdf_select_plan* pl, double tol)
+{
+    ARG_CHECK(pl != nullptr);
+    CUDA_TRY(cudaMemcpyAsync(&pl->w.st->tol, &tol, sizeof(double), cudaMemcpyHostToDevice, pl->h->stream));
+    CUDA_TRY(cudaStreamSynchronize(pl->h->stream));
+    return ISDF_OK;
+}
+
+// The `quota` largest local residuals -> block[(quota+1)][row_len(nao,k0)] (see pack_candidates_kernel).
+// block == nullptr packs into the plan's own buffer.
+extern "C" int isdf_select_candidates(isdf_select_plan* pl, const double* phi, long long ldphi,
+                                      const double* Lt, long long ldl, int k0, int quota, double* block)
+{
+    ARG_CHECK(pl && phi && Lt && k0 >= 0 && quota >= 1 && quota < MCAP);
+    isdf_handle* h = pl->h;
+    cudaStream_t s = h->stream;
+    SelWs& w = pl->w;
+    if (!block) block = w.block;
+    const int shifts[6] = {52, 41, 30, 20, 10, 0};
+    const int bitsv[6] = {11, 11, 11, 10, 10, 10};
+    const int hist_blocks = (int)std::min<long long>((pl->ngl + 255) / 256, 2 * h->num_sms);
+    radix_begin_kernel<<<1, 1, 0, s>>>(w.st, (long long)quota);
+    for (int pass = 0; pass < 6; ++pass) {
+        radix_hist_kernel<<<hist_blocks, 256, 0, s>>>(w.d, pl->ngl, w.st, shifts[pass], bitsv[pass], w.hist);
+        radix_scan_kernel<<<1, 1024, 0, s>>>(w.st, shifts[pass], bitsv[pass], w.hist, pass == 5);
+    }
+    compact_kernel<<<1, 1024, 0, s>>>(w.d, pl->ngl, w.st, w.cand, w.dC);
+    const int rl = row_len(pl->nao, k0);
+    dim3 grid((rl + 255) / 256, quota + 1);
+    pack_candidates_kernel<<<grid, 256, 0, s>>>(phi, ldphi, pl->nao, pad2(pl->nao), Lt, ldl, k0, w.cand, w.dC,
+                                               w.st, pl->g_offset, quota, rl, block);
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches += 15;
+    return ISDF_OK;
+}
+
+static int gemm_kc(isdf_handle* h, int M, int N, int K, const double* A, long long lda,
+                   const double* B, long long ldb, int b_kmajor, double* C, long long ldc,
+                   const double* Cin, int neg, int epi)
 {
     GemmParams p;
     p.M = M; p.N = N; p.K = K;
-    p.A = A; p.lda = lda; p.a_kmajor = 1;
-    p.B = B; p.ldb = ldb; p.b_kmajor = 1;
+    p.A = A; p.lda = lda; p.a_kmajor = 0;
+    p.B = B; p.ldb = ldb; p.b_kmajor = b_kmajor;
     p.C = C; p.ldc = ldc; p.Cin = Cin; p.ldcin = ldc;
     p.E = nullptr; p.lde = 0; p.alpha = 1.0; p.neg = neg; p.epi = epi; p.upper_only = 0;
     return gemm_launch(h, p);
 }
 
+// Panel factorisation on the gathered candidate blocks of all ranks
+// (blocks: [nranks * (quota+1)][row_len]); every rank runs it redundantly on
+// identical data and gets identical pivots.  U (nullable) receives the new
+// columns of the transposed pivot factor.  Host sync: returns nb, stop.
+extern "C" int isdf_select_panel(isdf_select_plan* pl, const double* blocks, int nranks, int quota,
+                                 int k0, int nbmax, double* U, long long ldu, int* h_nb, int* h_stop)
+{
+    ARG_CHECK(pl && h_nb && h_stop && nranks >= 1 && quota >= 1 && k0 >= 0 && nbmax >= 1 && nbmax <= NB);
+    isdf_handle* h = pl->h;
+    cudaStream_t s = h->stream;
+    SelWs& w = pl->w;
+    if (!blocks) blocks = w.block;
+    const int m = nranks * (quota + 1);
+    ARG_CHECK(m <= MCAP);
+    const int rl = row_len(pl->nao, k0), naop = pad2(pl->nao);
+    int rc;
+    panel_prepare_kernel<<<1, 1024, 0, s>>>(blocks, nranks, quota, rl, w.cand, w.dC, w.st);
+    h->other_launches++;
+    // T = G[C,C] - Lc Lc^T  (same FMA chains as the flush GEMMs)
+    if ((rc = gemm_kc(h, m, m, pl->nao, blocks + META, rl, blocks + META, rl, 0, w.T, MCAP, nullptr, 0, EPI_SQUARE))) return rc;
+    if (k0 > 0)
+        if ((rc = gemm_kc(h, m, m, k0, blocks + META + naop, rl, blocks + META + naop, rl, 0, w.T, MCAP, w.T, 1, EPI_STORE))) return rc;
+    {
+        SelState* st = w.st; const double* T = w.T; long long ldT = MCAP; const int* cand = w.cand;
+        double* dC = w.dC; double* LppT = w.LppT; int* pvl = w.piv_local; double* rs = w.resid_dev;
+        Partial* pa = w.partials; int k0a = k0, nbm = nbmax;
+        void* args[] = {&st, &T, &ldT, &cand, &dC, &LppT, &pvl, &rs, &pa, &k0a, &nbm};
+        CUDA_TRY(cudaLaunchCooperativeKernel((void*)panel_kernel, dim3(PANEL_CTAS), dim3(PANEL_THREADS), args, 0, s));
+        h->other_launches++;
+    }
+    SelState* hst = (SelState*)h->h_pinned;
+    CUDA_TRY(cudaMemcpyAsync(hst, w.st, sizeof(SelState), cudaMemcpyDeviceToHost, s));
+    CUDA_TRY(cudaStreamSynchronize(s));
+    const int nb = hst->nb_eff;
+    *h_nb = nb; *h_stop = hst->stop;
+    if (nb > 0) {
+        dim3 g1((rl + 255) / 256, nb);
+        gather_rows_kernel<<<g1, 256, 0, s>>>(blocks, rl, w.piv_local, nb, k0, w.PivRows, w.ip_dev);
+        gather_lpp_kernel<<<nb, NB, 0, s>>>(w.LppT, w.piv_local, nb, w.LppP);
+        h->other_launches += 2;
+        if (U) {
+            dim3 g2((nb + 127) / 128, std::min(pl->npts, 2048));
+            assemble_U_kernel<<<g2, 128, 0, s>>>(w.PivRows, rl, META + naop, w.LppT, w.piv_local, nb, k0,
+                                                 pl->npts, U, ldu);
+            h->other_launches++;
+        }
+        CUDA_TRY(cudaGetLastError());
+    }
+    return ISDF_OK;
+}
+
+// New factor rows k0 .. k0+nb for the local slab, residual update, pivots masked.
+extern "C" int isdf_select_flush(isdf_select_plan* pl, const double* phi, long long ldphi,
+                                 double* Lt, long long ldl, int k0, int nb)
+{
+    ARG_CHECK(pl && phi && Lt && k0 >= 0 && nb >= 0 && nb <= NB && k0 + nb <= pl->npts);
+    if (nb == 0) return ISDF_OK;
+    isdf_handle* h = pl->h;
+    cudaStream_t s = h->stream;
+    SelWs& w = pl->w;
+    const int rl = row_len(pl->nao, k0), naop = pad2(pl->nao);
+    const long long ngl = pl->ngl;
+    static bool sweep_cfg = false;
+    const size_t sweep_smem = sizeof(double) * (NB * (NB + 1) / 2 + NB);
+    if (!sweep_cfg) {
+        CUDA_TRY(cudaFuncSetAttribute(panel_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem));
+        sweep_cfg = true;
+    }
+    int rc;
+    double* Ltp = Lt + (long long)k0 * ldl;
+    if ((rc = gemm_kc(h, nb, (int)ngl, pl->nao, w.PivRows + META, rl, phi, ldphi, 1, Ltp, ldl, nullptr, 0, EPI_SQUARE))) return rc;
+    if (k0 > 0)
+        if ((rc = gemm_kc(h, nb, (int)ngl, k0, w.PivRows + META + naop, rl, Lt, ldl, 1, Ltp, ldl, Ltp, 1, EPI_STORE))) return rc;
+    panel_sweep_kernel<<<(unsigned)((ngl + 127) / 128), 128, sweep_smem, s>>>(
+        Ltp, ldl, ngl, nb, w.LppP, w.resid_dev + k0, w.d);
+    mark_selected_kernel<<<1, NB, 0, s>>>(w.ip_dev, k0, nb, pl->g_offset, ngl, w.d);
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches += 2;
+    return ISDF_OK;
+}
+
+extern "C" int isdf_select_finish(isdf_select_plan* pl, int rank, long long* h_ip, double* h_resid)
+{
+    ARG_CHECK(pl && h_ip && rank >= 0 && rank <= pl->npts);
+    cudaStream_t s = pl->h->stream;
+    if (rank > 0) {
+        CUDA_TRY(cudaMemcpyAsync(h_ip, pl->w.ip_dev, sizeof(long long) * rank, cudaMemcpyDeviceToHost, s));
+        if (h_resid) CUDA_TRY(cudaMemcpyAsync(h_resid, pl->w.resid_dev, sizeof(double) * rank, cudaMemcpyDeviceToHost, s));
+    }
+    CUDA_TRY(cudaStreamSynchronize(s));
+    return ISDF_OK;
+}
+
+// Quota policy shared by the single-GPU driver below and the multi-rank host
+// driver (pyscf_isdf_b200/dist.py): grow the candidate set when the exactness
+// certificate ends panels early.
+extern "C" int isdf_select_next_quota(int quota, int nb, int nbmax, int nranks)
+{
+    const int cap = MCAP / nranks - 1;
+    if (nb < nbmax / 2 && quota * 2 <= cap) return quota * 2;
+    return quota;
+}
+
+extern "C" int isdf_select_first_quota(int nranks)
+{
+    return std::max(NB, 1024 / nranks);
+}
+
+// ---- single-GPU driver ----------------------------------------------------------------
 extern "C" int isdf_select_ip(isdf_handle* h, const double* phi, int nao, long long ng, long long ldphi,
                               int npts, double tol, double* Lt, long long ldl,
                               long long* h_ip, double* h_resid, int* h_rank,
@@ -476,95 +773,32 @@ extern "C" int isdf_select_ip(isdf_handle* h, const double* phi, int nao, long l
 {
     ARG_CHECK(h && phi && Lt && h_ip && h_rank && ws);
     ARG_CHECK(nao > 0 && ng > 0 && ng < 0x7fffffffLL && npts > 0 && npts <= ng && ldphi >= ng && ldl >= ng);
-    SelWs w;
-    const size_t need = carve(w, ws, ws_bytes, nao, ng, npts);
-    if (need > ws_bytes) { isdf_set_error("select_ip workspace too small: need %zu have %zu", need, ws_bytes); return ISDF_ERR_WS; }
+    isdf_select_plan* pl = nullptr;
+    int rc;
+    if ((rc = isdf_select_create(h, nao, ng, 0, ng, npts, ws, ws_bytes, &pl))) return rc;
     cudaStream_t s = h->stream;
     CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_SELECT], s));
-
-    init_diag_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(phi, ldphi, nao, ng, w.d);
-    state_init_kernel<<<1, 1024, 0, s>>>(w.d, ng, tol, w.st);
-    CUDA_TRY(cudaMemsetAsync(w.hist, 0, 2048 * sizeof(unsigned int), s));
-    CUDA_TRY(cudaGetLastError());
-    h->other_launches += 2;
-
-    static bool sweep_cfg = false;
-    const size_t sweep_smem = sizeof(double) * (NB * (NB + 1) / 2 + NB);
-    if (!sweep_cfg) {
-        CUDA_TRY(cudaFuncSetAttribute(panel_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem));
-        sweep_cfg = true;
-    }
-
-    SelState* hst = (SelState*)h->h_pinned;
-    const int shifts[6] = {52, 41, 30, 20, 10, 0};
-    const int bitsv[6] = {11, 11, 11, 10, 10, 10};
-    long long quota = 1024;
+    double dmax = 0.0;
+    rc = isdf_select_begin(pl, phi, ldphi, &dmax);
+    if (!rc) rc = isdf_select_set_tol(pl, tol < 0.0 ? (double)ng * 2.220446049250313e-16 * dmax : tol);
+    int quota = std::min(isdf_select_first_quota(1), (int)std::min<long long>(ng, MCAP - 1));
     int k0 = 0;
-    const int hist_blocks = std::min<long long>((ng + 255) / 256, 2 * h->num_sms);
-    while (k0 < npts) {
+    while (!rc && k0 < npts) {
         const int nbmax = std::min(NB, npts - k0);
-        // ---- candidate set ----
-        radix_begin_kernel<<<1, 1, 0, s>>>(w.st, quota);
-        for (int pass = 0; pass < 6; ++pass) {
-            radix_hist_kernel<<<hist_blocks, 256, 0, s>>>(w.d, ng, w.st, shifts[pass], bitsv[pass], w.hist);
-            radix_scan_kernel<<<1, 32, 0, s>>>(w.st, shifts[pass], bitsv[pass], w.hist, pass == 5);
-        }
-        compact_kernel<<<1, 1024, 0, s>>>(w.d, ng, w.st, w.cand, w.dC);
-        CUDA_TRY(cudaGetLastError());
-        h->other_launches += 14;
-        CUDA_TRY(cudaMemcpyAsync(hst, w.st, sizeof(SelState), cudaMemcpyDeviceToHost, s));
-        CUDA_TRY(cudaStreamSynchronize(s));
-        const int m = hst->m;
-        if (m <= 0) break;                       // no positive residual left
-        // ---- T = G[C,C] - Lc^T Lc ----
-        int rc;
-        if ((rc = gather_dev(h, phi, ldphi, nao, w.cand, m, w.PhiC, MCAP))) return rc;
-        if ((rc = gather_dev(h, Lt, ldl, k0, w.cand, m, w.LcOld, MCAP))) return rc;
-        if ((rc = gemm_simple(h, m, m, nao, w.PhiC, MCAP, w.PhiC, MCAP, w.T, MCAP, nullptr, 0, EPI_SQUARE))) return rc;
-        if (k0 > 0)
-            if ((rc = gemm_simple(h, m, m, k0, w.LcOld, MCAP, w.LcOld, MCAP, w.T, MCAP, w.T, 1, EPI_STORE))) return rc;
-        // ---- panel factorisation on the candidates ----
-        {
-            SelState* st = w.st; const double* T = w.T; long long ldT = MCAP; const int* cand = w.cand;
-            double* dC = w.dC; double* LppT = w.LppT; int* pl = w.piv_local; double* rs = w.resid_dev;
-            Partial* pa = w.partials; int k0a = k0, nbm = nbmax;
-            void* args[] = {&st, &T, &ldT, &cand, &dC, &LppT, &pl, &rs, &pa, &k0a, &nbm};
-            CUDA_TRY(cudaMemsetAsync(&w.st->barrier, 0, sizeof(unsigned int), s));
-            CUDA_TRY(cudaLaunchCooperativeKernel((void*)panel_kernel, dim3(PANEL_CTAS), dim3(PANEL_THREADS), args, 0, s));
-            h->other_launches++;
-        }
-        CUDA_TRY(cudaMemcpyAsync(hst, w.st, sizeof(SelState), cudaMemcpyDeviceToHost, s));
-        CUDA_TRY(cudaStreamSynchronize(s));
-        const int nb = hst->nb_eff;
-        const int stop = hst->stop;
-        if (nb > 0) {
-            // ---- flush: new factor rows for every grid point ----
-            record_pivots_kernel<<<1, NB, 0, s>>>(w.cand, w.piv_local, nb, k0, w.ip_dev);
-            gather_lpp_kernel<<<nb, NB, 0, s>>>(w.LppT, w.piv_local, nb, w.LppP);
-            h->other_launches += 2;
-            if ((rc = gather_dev(h, w.PhiC, MCAP, nao, w.piv_local, nb, w.PhiP, NB))) return rc;
-            if ((rc = gather_dev(h, w.LcOld, MCAP, k0, w.piv_local, nb, w.LtP, NB))) return rc;
-            double* Ltp = Lt + (long long)k0 * ldl;
-            if ((rc = gemm_simple(h, nb, (int)ng, nao, w.PhiP, NB, phi, ldphi, Ltp, ldl, nullptr, 0, EPI_SQUARE))) return rc;
-            if (k0 > 0)
-                if ((rc = gemm_simple(h, nb, (int)ng, k0, w.LtP, NB, Lt, ldl, Ltp, ldl, Ltp, 1, EPI_STORE))) return rc;
-            panel_sweep_kernel<<<(unsigned)((ng + 127) / 128), 128, sweep_smem, s>>>(
-                Ltp, ldl, ng, nb, w.LppP, w.resid_dev + k0, w.d);
-            mark_selected_kernel<<<1, NB, 0, s>>>(w.ip_dev, k0, nb, w.d);
-            CUDA_TRY(cudaGetLastError());
-            h->other_launches += 2;
-            k0 += nb;
-        }
-        if (stop) break;
-        // adapt the candidate quota: grow when the certificate ends panels early
-        if (nb < nbmax / 2 && quota < MCAP) quota *= 2;
-        else if (nb == nbmax && quota > 1024 && m > 8 * nbmax) quota = quota;   // keep
+        int nb = 0, stop = 0;
+        if ((rc = isdf_select_candidates(pl, phi, ldphi, Lt, ldl, k0, quota, nullptr))) break;
+        if ((rc = isdf_select_panel(pl, nullptr, 1, quota, k0, nbmax, nullptr, 0, &nb, &stop))) break;
+        if ((rc = isdf_select_flush(pl, phi, ldphi, Lt, ldl, k0, nb))) break;
+        k0 += nb;
+        if (stop || nb == 0) break;
+        quota = isdf_select_next_quota(quota, nb, nbmax, 1);
     }
-    CUDA_TRY(cudaMemcpyAsync(h_ip, w.ip_dev, sizeof(long long) * k0, cudaMemcpyDeviceToHost, s));
-    if (h_resid) CUDA_TRY(cudaMemcpyAsync(h_resid, w.resid_dev, sizeof(double) * k0, cudaMemcpyDeviceToHost, s));
-    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_SELECT], s));
-    h->ev_used[ISDF_STAGE_SELECT] = true;
-    CUDA_TRY(cudaStreamSynchronize(s));
-    *h_rank = k0;
-    return ISDF_OK;
+    if (!rc) {
+        CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_SELECT], s));
+        h->ev_used[ISDF_STAGE_SELECT] = true;
+        rc = isdf_select_finish(pl, k0, h_ip, h_resid);
+        *h_rank = k0;
+    }
+    isdf_select_destroy(pl);
+    return rc;
 }

@@ -25,10 +25,10 @@ from .cell import madelung as _madelung
 class ISDF:
     _keys = {'cell', 'kpts', 'mesh', 'c', 'n_ip', 'select', 'fit', 'tol', 'exxdiv',
              'ip_index', 'ip_resid', 'W', 'aoR', 'aoR_ip', 'stdout', 'verbose', 'max_memory',
-             'keep_aoR', 'timings'}
+             'keep_aoR', 'timings', 'comm'}
 
     def __init__(self, cell, kpts=np.zeros((1, 3)), c=15, n_ip=None, select='cholesky',
-                 fit='cholesky', tol=-1.0, device=None, keep_aoR=True):
+                 fit='cholesky', tol=-1.0, device=None, keep_aoR=True, comm=None):
         self.cell = cell
         self.stdout = sys.stdout
         self.verbose = getattr(cell, 'verbose', 0)
@@ -43,6 +43,8 @@ class ISDF:
         self.keep_aoR = keep_aoR
         self._device = device
         self._handle = None
+        # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
+        self.comm = comm
         self._rsh_df = {}
         self.timings = {}
         self.reset()
@@ -70,6 +72,8 @@ class ISDF:
         self._ovlp = None
         self._madelung = None
         self._jk_ws = None
+        self._part = None
+        self._slab = None
         return self
 
     def dump_flags(self, verbose=None):
@@ -111,6 +115,9 @@ class ISDF:
     def build(self):
         import torch
         self.check_sanity()
+        if self.comm is not None:
+            from . import dist
+            return dist.build(self, self.comm)
         h = self.handle
         cell = self.cell
         mesh = np.asarray(cell.mesh, dtype=np.int32)
@@ -170,6 +177,8 @@ class ISDF:
         if self.aoR is None:
             raise RuntimeError('aoR was not kept (keep_aoR=False)')
         ng = int(np.prod(self.mesh))
+        if self.comm is not None:
+            ng = self._slab[1] - self._slab[0]        # this rank's slab only
         return self.aoR[:, :ng].cpu().numpy()
 
     # -- overlap / Madelung for exxdiv='ewald' ---------------------------------------
@@ -185,8 +194,12 @@ class ISDF:
             nao = self.aoR.shape[0]
             ng = int(np.prod(self.mesh))
             S = h.empty((nao, nao))
-            h.dgemm(nao, nao, ng, self.aoR, self._ld, 0, self.aoR, self._ld, 0, S, nao,
+            # with a sharded grid every rank sums its slab, then the partial overlaps are added
+            g0, g1 = self._slab if self.comm is not None else (0, ng)
+            h.dgemm(nao, nao, g1 - g0, self.aoR, self._ld, 0, self.aoR, self._ld, 0, S, nao,
                     alpha=self.cell.vol / ng)
+            if self.comm is not None:
+                self.comm.all_reduce_sum(S)
             self._ovlp = S
         return self._ovlp
 
@@ -234,11 +247,15 @@ class ISDF:
         h = self.handle
         nao, npts = self.aoR_ip.shape
         nset = d_dm.shape[0]
-        vj = h.empty((nset, nao, nao)) if with_j else None
-        vk = h.empty((nset, nao, nao)) if with_k else None
-        if self._jk_ws is None:
-            self._jk_ws = h.workspace(h.lib.isdf_get_jk_ws_bytes(nao, npts))
-        h.get_jk(self.aoR_ip, self.W, d_dm, nset, nao, npts, with_j, with_k, vj, vk, ws=self._jk_ws)
+        if self.comm is not None:
+            from . import dist
+            vj, vk = dist.get_jk_device(self, self.comm, d_dm, with_j, with_k)
+        else:
+            vj = h.empty((nset, nao, nao)) if with_j else None
+            vk = h.empty((nset, nao, nao)) if with_k else None
+            if self._jk_ws is None:
+                self._jk_ws = h.workspace(h.lib.isdf_get_jk_ws_bytes(nao, npts))
+            h.get_jk(self.aoR_ip, self.W, d_dm, nset, nao, npts, with_j, with_k, vj, vk, ws=self._jk_ws)
         if with_k and exxdiv == 'ewald':
             # vk += madelung * S D S   (pyscf/pbc/df/df_jk.py:1446-1455)
             S = self.get_ovlp()

@@ -1,0 +1,121 @@
+"""CPU: the multi-rank host logic of pyscf_isdf_b200/dist.py under gloo with
+world_size 2 (and in-process with one rank), driven through the NumPy test
+double tests/fake_ops.py, checked against the CPU ISDF oracle."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+for p in (ROOT, HERE):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def _cell():
+    from util import diamond_c8
+    return diamond_c8([9, 9, 9], basis='gth-szv', jitter=0.2)
+
+
+def _reference(cell, npts, dm):
+    import oracle
+    from util import oracle_phi
+    phi = oracle_phi(cell)
+    ref = oracle.isdf_build(phi, cell.lattice_vectors(), cell.mesh, npts)
+    vj, vk = oracle.isdf_get_jk(ref['X'], ref['W'], dm)
+    return ref, vj, vk
+
+
+def _run_rank(comm, out=None):
+    from fake_ops import FakeOps
+    from pyscf_isdf_b200 import dist
+    from pyscf_isdf_b200.isdf import ISDF
+    from util import rand_dm
+    cell = _cell()
+    mydf = ISDF(cell, c=5, comm=comm)
+    mydf._handle = FakeOps()
+    mydf.build()
+    dm = rand_dm(cell.nao)
+    vj, vk = dist.get_jk_device(mydf, comm, torch.from_numpy(dm[None].copy()))
+    res = dict(ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(),
+               vj=vj.numpy()[0].copy(), vk=vk.numpy()[0].copy(), slab=mydf._slab,
+               panels=mydf.timings['select_panels'])
+    if out is not None:
+        out.put((comm.rank, res))
+    return res
+
+
+def _check(res, tol=1e-9):
+    from util import rand_dm
+    cell = _cell()
+    ref, vj, vk = _reference(cell, 5 * cell.nao, rand_dm(cell.nao))
+    assert np.array_equal(res['ip'], ref['ip'])
+    assert abs(res['X'] - ref['X']).max() < 1e-12
+    assert abs(res['W'] - ref['W']).max() < tol * abs(ref['W']).max()
+    assert abs(res['vj'] - vj).max() < tol * abs(vj).max()
+    assert abs(res['vk'] - vk).max() < tol * abs(vk).max()
+
+
+def test_partition():
+    from pyscf_isdf_b200.dist import SlabPartition
+    p = SlabPartition([71, 71, 71], 8, 12480)
+    assert p.x_off[0] == 0 and p.x_off[-1] == 71 and (np.diff(p.x_off) >= 8).all()
+    assert p.col_off[-1] == 71 * 36 and p.ip_off[-1] == 12480
+    assert all(o % 8 == 0 for o in p.ip_off[:-1])
+    assert p.grid_range(0)[0] == 0 and p.grid_range(7)[1] == 71 ** 3
+    assert sum(p.nx_local(r) for r in range(8)) == 71
+    p = SlabPartition([9, 9, 9], 3, 50)           # ragged: 50 points over 3 ranks
+    assert list(p.ip_off) == [0, 16, 32, 50]
+    with pytest.raises(ValueError):
+        SlabPartition([4, 4, 4], 8, 10)
+
+
+def test_single_rank_driver_matches_oracle():
+    from pyscf_isdf_b200.dist import SerialComm
+    _check(_run_rank(SerialComm()))
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        from pyscf_isdf_b200.dist import Comm
+        _run_rank(Comm(), q)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('world', [2, 3])
+def test_gloo_ranks_match_oracle(world):
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(('127.0.0.1', 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = {}
+    for _ in range(world):
+        r, res = q.get(timeout=300)
+        got[r] = res
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    # every rank ends with the same replicated ip / X / W / J / K
+    for r in range(1, world):
+        assert np.array_equal(got[r]['ip'], got[0]['ip'])
+        assert np.array_equal(got[r]['W'], got[0]['W'])
+        assert np.array_equal(got[r]['vk'], got[0]['vk'])
+    slabs = [got[r]['slab'] for r in range(world)]
+    assert slabs[0][0] == 0 and slabs[-1][1] == 9 ** 3
+    assert all(slabs[r][1] == slabs[r + 1][0] for r in range(world - 1))
+    _check(got[0])
