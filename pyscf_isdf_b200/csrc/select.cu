@@ -470,18 +470,19 @@ panel_sweep_kernel(double* __restrict__ Ltp, long long ldl, long long ng, int nb
     if (g >= ng) return;
     double dd = d[g];
     double* col = Ltp + g;
-    for (int kb = 0; kb < nb; kb += 8) {
-        double acc[8], res[8];
+    constexpr int SB = 16;      // rows per register block: earlier rows are re-read nb/(2*SB) times
+    for (int kb = 0; kb < nb; kb += SB) {
+        double acc[SB], res[SB];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[i] = (kb + i < nb) ? col[(long long)(kb + i) * ldl] : 0.0;
+        for (int i = 0; i < SB; ++i) acc[i] = (kb + i < nb) ? col[(long long)(kb + i) * ldl] : 0.0;
         for (int j = 0; j < kb; ++j) {
             const double x = -col[(long long)j * ldl];
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
+            for (int i = 0; i < SB; ++i)
                 if (kb + i < nb) acc[i] = fma(x, s_l[(kb + i) * (kb + i + 1) / 2 + j], acc[i]);
         }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < SB; ++i) {
             if (kb + i < nb) {
 #pragma unroll
                 for (int jj = 0; jj < i; ++jj)
