@@ -36,7 +36,7 @@ def parse_args():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--workload', default=None, help='c8 | c64 | h2o32 | si216 | c8-small')
     ap.add_argument('--c', type=float, default=15.0, help='ISDF rank parameter: N_IP = c * nao')
-    ap.add_argument('--fit', default='pivot_factor', choices=['pivot_factor', 'cholesky'])
+    ap.add_argument('--fit', default='implicit', choices=['implicit', 'pivot_factor', 'cholesky'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--jk-reps', type=int, default=5)
     return ap.parse_args()

@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "../../include/isdf_b200.h"
 #include <vector>
+#include <cstdlib>
 #include <cmath>
 #include <algorithm>
 
@@ -512,6 +513,19 @@ void fill_geom(CoulGeom& g, const int* mesh, const double* a, double scale)
     g.col0 = 0;
 }
 
+// shared memory per CTA of the FFT kernels (two ping-pong line buffers); smaller = more CTAs per SM.
+// Tuning knob: environment ISDF_FFT_SMEM_KB.
+size_t fft_smem_budget()
+{
+    static size_t v = 0;
+    if (v == 0) {
+        const char* e = getenv("ISDF_FFT_SMEM_KB");
+        const long kb = e ? atol(e) : 96;
+        v = (size_t)std::min(200L, std::max(8L, kb)) * 1024;
+    }
+    return v;
+}
+
 // lines (or columns) per CTA such that two ping-pong buffers of `nalloc` slots per line fit the budget
 int pick_lb(int nalloc, size_t budget) { return (int)std::max<size_t>(1, std::min<size_t>(64, budget / (2 * sizeof(double2) * nalloc))); }
 
@@ -522,7 +536,7 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
 {
     const int nx = mesh[0], ny = mesh[1], nz = mesh[2], nzh = nz / 2 + 1;
     cudaStream_t s = h->stream;
-    const size_t budget = 96 * 1024;
+    const size_t budget = fft_smem_budget();
     {
         const int LB = pick_lb(P.ax[2].lalloc(), budget);
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
@@ -567,7 +581,7 @@ int inverse_yz(isdf_handle* h, const Plans& P, const int* mesh, double2* spec, l
 {
     const int nx = mesh[0], ny = mesh[1], nz = mesh[2], nzh = nz / 2 + 1;
     cudaStream_t s = h->stream;
-    const size_t budget = 96 * 1024;
+    const size_t budget = fft_smem_budget();
     {
         const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
@@ -705,7 +719,7 @@ extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int
     Plans P; int rc;
     if ((rc = make_plans(h, h_mesh, P))) return rc;
     cudaStream_t s = h->stream;
-    const size_t budget = 96 * 1024;
+    const size_t budget = fft_smem_budget();
     CoulGeom geo; memset(&geo, 0, sizeof(geo));
     {
         const int LB = pick_lb(P.ax[2].lalloc(), budget);
@@ -775,7 +789,7 @@ extern "C" int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nv
     if ((rc = make_plans(h, h_mesh, P))) return rc;
     CoulGeom geo; fill_geom(geo, h_mesh, h_a, 1.0);
     geo.col0 = col0;
-    const size_t budget = 96 * 1024;
+    const size_t budget = fft_smem_budget();
     const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncl);
     const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
     if ((rc = set_smem(fft_cols_kernel<1>, smem))) return rc;

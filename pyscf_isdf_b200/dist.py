@@ -13,11 +13,17 @@ the partitioning below is this repository's design:
                              the same candidate set redundantly (pivots are
                              exact: certificate max_C d > max_notC d) and
                              updates its own slab                          all-gather
-  stage 3  aux fit           zeta = U^-1 Lt, columns independent           no exchange
+  stage 3  aux fit           fit='pivot_factor': zeta = U^-1 Lt, columns
+                             independent.  fit='implicit' (default): zeta is
+                             never formed, see stage 4                     no exchange
   stage 4  Coulomb metric W  slab FFT: local z,y passes, ONE all-to-all to
                              (y,z)-column slabs, x pass fused with the
-                             Coulomb weight, partial W over the rank's
-                             spectral slab, summed                         all-to-all + all-reduce
+                             Coulomb weight, partial metric over the rank's
+                             spectral slab, summed.  'implicit': the metric
+                             M = Lt K Lt^T of the factor rows is formed and
+                             W = U^-1 M U^-T follows from two triangular
+                             solves sharded by columns (one small all-to-all
+                             transposes between them)                      all-to-all + all-reduce
   stage 5  J/K               rank r contracts its row block of W           all-reduce of J,K
 
 Results are bit-identical for any number of ranks in stages 1-3 (same FMA
@@ -176,8 +182,11 @@ def build(mydf, comm, ops=None):
     part.set_npts(npts)
     ev.mark('select_ms')
 
-    # stage 3: zeta = U^-1 Lt on the local slab (in place)
-    ops.fit_aux_from_U(U, ldu, npts, Lt, ldl, ngl)
+    # stage 3: zeta = U^-1 Lt on the local slab (in place) -- skipped by fit='implicit',
+    # which transforms the metric of the factor rows afterwards: W = U^-1 (Lt K Lt^T) U^-T
+    implicit = (mydf.fit == 'implicit')
+    if not implicit:
+        ops.fit_aux_from_U(U, ldu, npts, Lt, ldl, ngl)
     ev.mark('fit_ms')
 
     # X = Phi[:, ip]: every rank contributes the pivots that live in its slab
@@ -220,11 +229,19 @@ def build(mydf, comm, ops=None):
     ops.symmetrize_upper(W, npts, npts)
     comm.all_reduce_sum(W)
     ev.mark('wgemm_ms')
+    del Y, Yr
+    p0, p1 = int(part.ip_off[r]), int(part.ip_off[r + 1])
+    if implicit:
+        W = _congruence_solve(ops, comm, part, U, ldu, W, npts)
+        ev.mark('wsolve_ms')
+    else:
+        W = W[p0:p1]
     ops.synchronize()
-    del Y, Lt, U
+    del Lt, U
 
     mydf.timings = dict(ev.times)
-    mydf.timings['coulomb_ms'] = ev.times.get('fft_ms', 0.0) + ev.times.get('wgemm_ms', 0.0)
+    mydf.timings['coulomb_ms'] = (ev.times.get('fft_ms', 0.0) + ev.times.get('wgemm_ms', 0.0) +
+                                  ev.times.get('wsolve_ms', 0.0))
     mydf.timings['build_wall_s'] = time.perf_counter() - t0
     mydf.timings['select_panels'] = npanels
     mydf.n_ip = npts
@@ -240,6 +257,38 @@ def build(mydf, comm, ops=None):
     return mydf
 
 
+def _congruence_solve(ops, comm, part, U, ldu, M, npts):
+    """Rows [p0, p1) of W = U^-1 M U^-T for this rank (M symmetric, replicated; U upper
+    triangular, replicated).  Both solves act on independent columns, so rank r takes the
+    column block [p0, p1); the transposition between them is one all-to-all of Np*Np/N doubles."""
+    N, r = comm.size, comm.rank
+    off = [int(x) for x in part.ip_off]
+    p0, p1 = off[r], off[r + 1]
+    ncr = p1 - p0
+    if ncr == 0:
+        return M[p0:p1]
+    Z1 = M[:, p0:p1].contiguous()                       # [Np, ncr]
+    del M
+    ops.fit_aux_from_U(U, ldu, npts, Z1, ncr, ncr)      # Z1 = U^-1 M[:, cols]
+    R = ops.empty((npts, ncr))
+    if N == 1:
+        R.copy_(Z1.t())
+    else:
+        recv = ops.empty((npts * ncr,))
+        splits = [(off[s + 1] - off[s]) * ncr for s in range(N)]
+        comm.all_to_all(recv, Z1.reshape(-1), splits, splits)
+        o = 0
+        for s in range(N):
+            ncs = off[s + 1] - off[s]
+            if ncs:
+                R[off[s]:off[s + 1]] = recv[o:o + ncr * ncs].view(ncr, ncs).t()
+            o += ncr * ncs
+        del recv
+    del Z1
+    ops.fit_aux_from_U(U, ldu, npts, R, ncr, ncr)       # R = U^-1 (U^-1 M)^T[:, cols] = W[:, cols]
+    return R.t().contiguous()                           # W[cols, :] by symmetry
+
+
 def get_jk_device(mydf, comm, d_dm, with_j=True, with_k=True, ops=None):
     """Stage 5: every rank contracts its row block of W, then J and K are all-reduced."""
     ops = ops or mydf.handle
@@ -252,7 +301,8 @@ def get_jk_device(mydf, comm, d_dm, with_j=True, with_k=True, ops=None):
     vj = out[0] if with_j else None
     vk = out[1] if with_k else None
     if p1 > p0:
-        mydf._jk_ws = ops.get_jk_block(mydf.aoR_ip, mydf.W[p0:], npts, p0, p1 - p0, d_dm, nset, nao, npts,
+        # mydf.W holds this rank's row block W[p0:p1, :] (the whole matrix on one rank)
+        mydf._jk_ws = ops.get_jk_block(mydf.aoR_ip, mydf.W, npts, p0, p1 - p0, d_dm, nset, nao, npts,
                                        with_j, with_k, vj, vk, ws=mydf._jk_ws)
     comm.all_reduce_sum(out)
     return vj, vk

@@ -13,6 +13,11 @@ Stages (all on the GPU, no CPU fallback):
   get_jk(): 5 J/K contraction per SCF iteration.
 The mounted reference has no ISDF class; the constructor follows SURVEY.md
 section 8b (``ISDF(cell, kpts, c=15, n_ip=None, select='cholesky')``).
+
+``fit`` selects how stages 3+4 are organised (all give the same J/K to 1e-8):
+  'cholesky'      zeta = A^-1 B by Cholesky of A = (X^T X)^2 (the oracle's route)
+  'pivot_factor'  zeta = U^-1 Lt from the selection factor (A = U^T U, B = U^T Lt exactly)
+  'implicit'      zeta is never formed: M = Lt K Lt^T, W = U^-1 M U^-T   (default, fewest flops)
 """
 import sys
 import time
@@ -28,7 +33,7 @@ class ISDF:
              'keep_aoR', 'timings', 'comm'}
 
     def __init__(self, cell, kpts=np.zeros((1, 3)), c=15, n_ip=None, select='cholesky',
-                 fit='cholesky', tol=-1.0, device=None, keep_aoR=True, comm=None):
+                 fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None):
         self.cell = cell
         self.stdout = sys.stdout
         self.verbose = getattr(cell, 'verbose', 0)
@@ -88,8 +93,10 @@ class ISDF:
     def check_sanity(self):
         if self.select != 'cholesky':
             raise NotImplementedError("select=%r (only 'cholesky' pivoting is implemented)" % self.select)
-        if self.fit not in ('cholesky', 'pivot_factor'):
-            raise ValueError("fit must be 'cholesky' or 'pivot_factor'")
+        if self.fit not in ('implicit', 'cholesky', 'pivot_factor'):
+            raise ValueError("fit must be 'implicit', 'cholesky' or 'pivot_factor'")
+        if self.comm is not None and self.fit == 'cholesky':
+            raise NotImplementedError("fit='cholesky' is single-GPU only; use 'implicit' or 'pivot_factor'")
         if getattr(self.cell, 'dimension', 3) != 3:
             raise RuntimeError('ISDF supports 3-D periodic cells only')   # cf. fft.py:216-220
         if abs(self.kpts).sum() > 1e-9:
@@ -115,9 +122,9 @@ class ISDF:
     def build(self):
         import torch
         self.check_sanity()
-        if self.comm is not None:
+        if self.comm is not None or self.fit == 'implicit':
             from . import dist
-            return dist.build(self, self.comm)
+            return dist.build(self, self.comm if self.comm is not None else dist.SerialComm())
         h = self.handle
         cell = self.cell
         mesh = np.asarray(cell.mesh, dtype=np.int32)
@@ -177,7 +184,7 @@ class ISDF:
         if self.aoR is None:
             raise RuntimeError('aoR was not kept (keep_aoR=False)')
         ng = int(np.prod(self.mesh))
-        if self.comm is not None:
+        if self._slab is not None:
             ng = self._slab[1] - self._slab[0]        # this rank's slab only
         return self.aoR[:, :ng].cpu().numpy()
 
@@ -195,7 +202,7 @@ class ISDF:
             ng = int(np.prod(self.mesh))
             S = h.empty((nao, nao))
             # with a sharded grid every rank sums its slab, then the partial overlaps are added
-            g0, g1 = self._slab if self.comm is not None else (0, ng)
+            g0, g1 = self._slab if self._slab is not None else (0, ng)
             h.dgemm(nao, nao, g1 - g0, self.aoR, self._ld, 0, self.aoR, self._ld, 0, S, nao,
                     alpha=self.cell.vol / ng)
             if self.comm is not None:
@@ -248,7 +255,7 @@ class ISDF:
         nao, npts = self.aoR_ip.shape
         nset = d_dm.shape[0]
         if self.comm is not None:
-            from . import dist
+            from . import dist                  # self.W is this rank's row block of W
             vj, vk = dist.get_jk_device(self, self.comm, d_dm, with_j, with_k)
         else:
             vj = h.empty((nset, nao, nao)) if with_j else None
@@ -276,6 +283,8 @@ class ISDF:
 
     # -- persistence ("next" row 3 of SURVEY 8f) ---------------------------------------------
     def save(self, path):
+        if self.comm is not None and self.comm.size > 1:
+            raise NotImplementedError('save() of a sharded ISDF object (W is distributed over ranks)')
         np.savez(path, ip_index=self.ip_index, ip_resid=self.ip_resid,
                  W=self.W.cpu().numpy(), aoR_ip=self.aoR_ip.cpu().numpy(),
                  mesh=np.asarray(self.mesh), n_ip=self.n_ip)

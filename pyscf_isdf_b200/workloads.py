@@ -76,12 +76,14 @@ def synthetic_dm(nao, seed=2):
     return d + d.T
 
 
-def flop_model(nao, ng, npts, mesh, fit='pivot_factor'):
+def flop_model(nao, ng, npts, mesh, fit='implicit'):
     """Algorithmic FP64 flop / byte counts per stage."""
     ngh = int(mesh[0]) * int(mesh[1]) * (int(mesh[2]) // 2 + 1)
     f = {}
     f['select'] = 2.0 * ng * nao * npts + 1.0 * ng * npts ** 2
-    if fit == 'pivot_factor':
+    if fit == 'implicit':
+        f['fit'] = 2.0 * npts ** 3                     # W = U^-1 M U^-T: two triangular solves with Np right-hand sides
+    elif fit == 'pivot_factor':
         f['fit'] = 1.0 * npts ** 2 * ng
     else:
         f['fit'] = 2.0 * npts * nao * ng + 2.0 * npts ** 2 * nao + npts ** 3 / 3.0 + 2.0 * npts ** 2 * ng
