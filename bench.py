@@ -239,7 +239,9 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
-        dist.init_process_group('nccl', device_id=dev)
+        import datetime
+        # short watchdog: a mismatched collective must fail fast, not burn GPU time
+        dist.init_process_group('nccl', device_id=dev, timeout=datetime.timedelta(seconds=180))
 
     from pyscf_isdf_b200 import workloads
     from pyscf_isdf_b200.isdf import ISDF

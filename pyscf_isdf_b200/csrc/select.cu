@@ -158,10 +158,17 @@ __global__ void __launch_bounds__(1024) radix_scan_kernel(SelState* st, int shif
     for (int b = tid; b < nbins; b += blockDim.x) hist[b] = 0;
 }
 
-// ---- ordered compaction of the candidate set (single CTA, ascending g) --------
-__global__ void __launch_bounds__(1024) compact_kernel(const double* __restrict__ d, long long ng,
-                                                       SelState* st, int* __restrict__ cand,
-                                                       double* __restrict__ dC)
+// ---- ordered compaction of the candidate set --------------------------------------------
+// candidates = {key > tie_key} + the first tie_take of {key == tie_key} in ascending g.
+// Three launches: per-chunk counts, a scan over the chunks, per-chunk scatter.
+constexpr int COMPACT_CHUNK = 8192;
+
+template <bool SCATTER>
+__global__ void __launch_bounds__(1024)
+compact_chunk_kernel(const double* __restrict__ d, long long ng, const SelState* __restrict__ st,
+                     long long* __restrict__ chunk_cnt, const long long* __restrict__ chunk_base,
+                     unsigned long long* __restrict__ chunk_theta,
+                     int* __restrict__ cand, double* __restrict__ dC)
 {
     __shared__ int s_w[32][2];
     __shared__ long long s_base[2];
@@ -169,13 +176,18 @@ __global__ void __launch_bounds__(1024) compact_kernel(const double* __restrict_
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const unsigned long long tie_key = st->tie_key;
     const long long tie_take = st->tie_take;
-    if (tid == 0) { s_base[0] = 0; s_base[1] = 0; }
+    const long long g_begin = (long long)blockIdx.x * COMPACT_CHUNK;
+    const long long g_end = min(ng, g_begin + COMPACT_CHUNK);
+    if (tid == 0) {
+        s_base[0] = SCATTER ? chunk_base[2 * blockIdx.x] : 0;
+        s_base[1] = SCATTER ? chunk_base[2 * blockIdx.x + 1] : 0;
+    }
     __syncthreads();
-    unsigned long long theta = 0;
-    for (long long g0 = 0; g0 < ng; g0 += blockDim.x) {
+    unsigned long long theta = 0;       // largest key below tie_key in this chunk (count pass)
+    for (long long g0 = g_begin; g0 < g_end; g0 += blockDim.x) {
         const long long g = g0 + tid;
         unsigned long long k = 0;
-        if (g < ng) k = dkey(d[g]);
+        if (g < g_end) k = dkey(d[g]);
         const bool gt = k > tie_key;
         const bool eq = (k == tie_key) && (k != 0);
         const unsigned bgt = __ballot_sync(0xffffffffu, gt), beq = __ballot_sync(0xffffffffu, eq);
@@ -186,25 +198,18 @@ __global__ void __launch_bounds__(1024) compact_kernel(const double* __restrict_
             if (w < wid) { ogt += s_w[w][0]; oeq += s_w[w][1]; }
             tgt += s_w[w][0]; teq += s_w[w][1];
         }
-        const long long eq_rank = s_base[1] + oeq + __popc(beq & ((1u << lane) - 1u));
-        const bool take_eq = eq && (eq_rank < tie_take);
-        // position: candidates are emitted in ascending g; ties taken and greater keys interleave,
-        // so count both kinds that precede this thread.
-        const unsigned btk = __ballot_sync(0xffffffffu, take_eq);
-        // number of taken ties in earlier warps of this chunk
-        long long tk_before = 0;
-        {
-            // ties in earlier warps that are within quota: ranks are contiguous, so
-            // taken = clamp(tie_take - base_eq - 0, 0, oeq)
+        if (SCATTER) {
+            const long long eq_rank = s_base[1] + oeq + __popc(beq & ((1u << lane) - 1u));
+            const bool take_eq = eq && (eq_rank < tie_take);
+            const unsigned btk = __ballot_sync(0xffffffffu, take_eq);
+            // ties of earlier warps within the quota: ranks are contiguous
             long long room = tie_take - s_base[1];
             if (room < 0) room = 0;
-            tk_before = oeq < room ? oeq : room;
-        }
-        const long long pos = s_base[0] + ogt + tk_before + __popc(bgt & ((1u << lane) - 1u)) +
-                              __popc(btk & ((1u << lane) - 1u));
-        if (gt || take_eq) {
-            if (pos < MCAP) { cand[pos] = (int)g; dC[pos] = d[g]; }
-        } else if (k != 0) {
+            const long long tk_before = oeq < room ? oeq : room;
+            const long long pos = s_base[0] + ogt + tk_before + __popc(bgt & ((1u << lane) - 1u)) +
+                                  __popc(btk & ((1u << lane) - 1u));
+            if ((gt || take_eq) && pos < MCAP) { cand[pos] = (int)g; dC[pos] = d[g]; }
+        } else if (!gt && !eq && k != 0) {
             theta = k > theta ? k : theta;
         }
         __syncthreads();
@@ -212,22 +217,49 @@ __global__ void __launch_bounds__(1024) compact_kernel(const double* __restrict_
             long long room = tie_take - s_base[1];
             if (room < 0) room = 0;
             const long long tk = teq < room ? teq : room;
-            s_base[0] += tgt + tk;
+            s_base[0] += tgt + (SCATTER ? tk : 0);
             s_base[1] += teq;
         }
         __syncthreads();
     }
-    for (int o = 16; o > 0; o >>= 1) {
-        const unsigned long long t = __shfl_xor_sync(0xffffffffu, theta, o);
-        theta = t > theta ? t : theta;
+    if (!SCATTER) {
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long t = __shfl_xor_sync(0xffffffffu, theta, o);
+            theta = t > theta ? t : theta;
+        }
+        if (lane == 0) s_theta[wid] = theta;
+        __syncthreads();
+        if (tid == 0) {
+            for (int w = 1; w < 32; ++w) theta = s_theta[w] > theta ? s_theta[w] : theta;
+            chunk_cnt[2 * blockIdx.x] = s_base[0];          // keys above the threshold
+            chunk_cnt[2 * blockIdx.x + 1] = s_base[1];      // ties
+            chunk_theta[blockIdx.x] = theta;
+        }
     }
-    if (lane == 0) s_theta[wid] = theta;
-    __syncthreads();
-    if (tid == 0) {
-        for (int w = 1; w < 32; ++w) theta = s_theta[w] > theta ? s_theta[w] : theta;
-        st->theta_key = theta;
-        st->m = (int)(s_base[0] < MCAP ? s_base[0] : MCAP);
+}
+
+// exclusive scan over the chunks: output position base and tie rank base of every chunk
+__global__ void compact_scan_kernel(SelState* st, int nchunks, const long long* __restrict__ chunk_cnt,
+                                    long long* __restrict__ chunk_base,
+                                    const unsigned long long* __restrict__ chunk_theta)
+{
+    if (threadIdx.x != 0) return;
+    const long long tie_take = st->tie_take;
+    long long pos = 0, eqs = 0;
+    unsigned long long theta = 0;
+    for (int c = 0; c < nchunks; ++c) {
+        chunk_base[2 * c] = pos;
+        chunk_base[2 * c + 1] = eqs;
+        long long room = tie_take - eqs;
+        if (room < 0) room = 0;
+        const long long teq = chunk_cnt[2 * c + 1];
+        pos += chunk_cnt[2 * c] + (teq < room ? teq : room);
+        eqs += teq;
+        theta = chunk_theta[c] > theta ? chunk_theta[c] : theta;
     }
+    if (eqs > tie_take) theta = st->tie_key;        // an untaken tie is the largest residual outside the set
+    st->theta_key = theta;
+    st->m = (int)(pos < MCAP ? pos : MCAP);
 }
 
 // out[r, j] = in[r, idx[j]]  (idx on device, int32)
@@ -500,6 +532,7 @@ struct SelWs {
     double* d; unsigned int* hist; int* cand; double* dC; double* T;
     double* LppT; int* piv_local; double* PivRows; double* LppP; double* resid_dev;
     long long* ip_dev; Partial* partials; SelState* st; double* block;
+    long long* chunk_cnt; long long* chunk_base; unsigned long long* chunk_theta;
 };
 
 inline int pad2(int n) { return (n + 1) & ~1; }
@@ -523,6 +556,10 @@ size_t carve(SelWs& w, void* ws, size_t bytes, int nao, long long ngl, int npts)
     w.partials = a.get<Partial>(2 * PANEL_CTAS);
     w.st = a.get<SelState>(1);
     w.block = a.get<double>((size_t)MCAP * rl);       // local candidate block (quota+1 <= MCAP rows)
+    const size_t nchunks = (size_t)((ngl + COMPACT_CHUNK - 1) / COMPACT_CHUNK);
+    w.chunk_cnt = a.get<long long>(2 * nchunks);
+    w.chunk_base = a.get<long long>(2 * nchunks);
+    w.chunk_theta = a.get<unsigned long long>(nchunks);
     return a.off + 256;
 }
 
@@ -635,13 +672,20 @@ extern "C" int isdf_select_candidates(isdf_select_plan* pl, const double* phi, l
         radix_hist_kernel<<<hist_blocks, 256, 0, s>>>(w.d, pl->ngl, w.st, shifts[pass], bitsv[pass], w.hist);
         radix_scan_kernel<<<1, 1024, 0, s>>>(w.st, shifts[pass], bitsv[pass], w.hist, pass == 5);
     }
-    compact_kernel<<<1, 1024, 0, s>>>(w.d, pl->ngl, w.st, w.cand, w.dC);
+    {
+        const int nchunks = (int)((pl->ngl + COMPACT_CHUNK - 1) / COMPACT_CHUNK);
+        compact_chunk_kernel<false><<<nchunks, 1024, 0, s>>>(w.d, pl->ngl, w.st, w.chunk_cnt, w.chunk_base,
+                                                             w.chunk_theta, w.cand, w.dC);
+        compact_scan_kernel<<<1, 32, 0, s>>>(w.st, nchunks, w.chunk_cnt, w.chunk_base, w.chunk_theta);
+        compact_chunk_kernel<true><<<nchunks, 1024, 0, s>>>(w.d, pl->ngl, w.st, w.chunk_cnt, w.chunk_base,
+                                                            w.chunk_theta, w.cand, w.dC);
+    }
     const int rl = row_len(pl->nao, k0);
     dim3 grid((rl + 255) / 256, quota + 1);
     pack_candidates_kernel<<<grid, 256, 0, s>>>(phi, ldphi, pl->nao, pad2(pl->nao), Lt, ldl, k0, w.cand, w.dC,
                                                w.st, pl->g_offset, quota, rl, block);
     CUDA_TRY(cudaGetLastError());
-    h->other_launches += 15;
+    h->other_launches += 17;
     return ISDF_OK;
 }
 

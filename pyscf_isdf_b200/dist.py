@@ -30,9 +30,14 @@ Results are bit-identical for any number of ranks in stages 1-3 (same FMA
 chains, exact pivots); W, J, K differ only by the summation order of the
 final reductions.
 """
+import os
+
 import numpy as np
 
 from . import _lib
+
+# upper bound of one all-to-all batch of half spectra (per rank, bytes)
+A2A_BATCH_BYTES = int(os.environ.get('ISDF_A2A_BATCH_BYTES', 1 << 30))
 
 
 class Comm:
@@ -202,8 +207,12 @@ def build(mydf, comm, ops=None):
     ncols, ncl, col0 = part.ncols, part.ncol_local(r), int(part.col_off[r])
     ldy = nx * ncl
     Y = ops.empty_complex((npts, ldy))
-    per_vec = max(nxl * ncols, nx * ncl) * 16
-    vb = int(max(1, min(npts, (1 << 30) // per_vec)))
+    # vectors per all-to-all batch: computed from rank-independent maxima so that every rank
+    # runs the same number of exchanges
+    nxl_max = max(part.nx_local(q) for q in range(N))
+    ncl_max = max(part.ncol_local(q) for q in range(N))
+    per_vec = max(nxl_max * ncols, nx * ncl_max) * 16
+    vb = int(max(1, min(npts, A2A_BATCH_BYTES // per_vec)))
     if N > 1:
         spec = ops.empty_complex((vb * nxl * ncols,))
         send = ops.empty_complex((vb * nxl * ncols,))
@@ -264,12 +273,11 @@ def _congruence_solve(ops, comm, part, U, ldu, M, npts):
     N, r = comm.size, comm.rank
     off = [int(x) for x in part.ip_off]
     p0, p1 = off[r], off[r + 1]
-    ncr = p1 - p0
-    if ncr == 0:
-        return M[p0:p1]
+    ncr = p1 - p0                                       # may be 0 on a rank when Np < 8 N: still take part
     Z1 = M[:, p0:p1].contiguous()                       # [Np, ncr]
     del M
-    ops.fit_aux_from_U(U, ldu, npts, Z1, ncr, ncr)      # Z1 = U^-1 M[:, cols]
+    if ncr:
+        ops.fit_aux_from_U(U, ldu, npts, Z1, ncr, ncr)  # Z1 = U^-1 M[:, cols]
     R = ops.empty((npts, ncr))
     if N == 1:
         R.copy_(Z1.t())
@@ -280,12 +288,13 @@ def _congruence_solve(ops, comm, part, U, ldu, M, npts):
         o = 0
         for s in range(N):
             ncs = off[s + 1] - off[s]
-            if ncs:
+            if ncs and ncr:
                 R[off[s]:off[s + 1]] = recv[o:o + ncr * ncs].view(ncr, ncs).t()
             o += ncr * ncs
         del recv
     del Z1
-    ops.fit_aux_from_U(U, ldu, npts, R, ncr, ncr)       # R = U^-1 (U^-1 M)^T[:, cols] = W[:, cols]
+    if ncr:
+        ops.fit_aux_from_U(U, ldu, npts, R, ncr, ncr)   # R = U^-1 (U^-1 M)^T[:, cols] = W[:, cols]
     return R.t().contiguous()                           # W[cols, :] by symmetry
 
 

@@ -86,6 +86,8 @@ def _worker(rank, world, port, q):
     import torch.distributed as dist
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
+    # several small all-to-all batches: their count must not depend on the rank's slab size
+    os.environ['ISDF_A2A_BATCH_BYTES'] = '20000'
     dist.init_process_group('gloo', rank=rank, world_size=world)
     try:
         from pyscf_isdf_b200.dist import Comm

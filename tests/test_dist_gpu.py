@@ -122,6 +122,11 @@ def test_sharded_even_mesh_prime_planes():
     dm = rand_dm(cell.nao)
     ref = ISDF(cell, c=6)
     vj0, vk0 = ref.get_jk(dm)
-    got = _run_threads(4, cell, 6, dm, fit='pivot_factor')
+    old = dist.A2A_BATCH_BYTES
+    dist.A2A_BATCH_BYTES = 60000          # many all-to-all batches; slabs of 3 and 4 planes
+    try:
+        got = _run_threads(4, cell, 6, dm, fit='pivot_factor')
+    finally:
+        dist.A2A_BATCH_BYTES = old
     assert np.array_equal(got[0]['ip'], ref.ip_index)
     assert abs(got[3]['vj'] - vj0).max() < 1e-8 and abs(got[3]['vk'] - vk0).max() < 1e-8
