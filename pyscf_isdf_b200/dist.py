@@ -165,16 +165,30 @@ def build(mydf, comm, ops=None):
     allbuf = ops.empty((N * (cap + 1) * rl_max,)) if N > 1 else blockbuf
     k0 = 0
     npanels = 0
+    prof = ops.timer() if os.environ.get('ISDF_PROFILE_SELECT') else None      # per-step breakdown
+    acc = {'sel_candidates_ms': 0.0, 'sel_allgather_ms': 0.0, 'sel_panel_ms': 0.0, 'sel_flush_ms': 0.0}
     while k0 < npts:
         nbmax = min(NB, npts - k0)
         n_el = (quota + 1) * lib.isdf_select_row_len(nao, k0)
         block = blockbuf[:n_el]
+        if prof:
+            prof = ops.timer()
         plan.candidates(phi, ldl, Lt, ldl, k0, quota, block)
+        if prof:
+            prof.mark('sel_candidates_ms')
         blocks = allbuf[:N * n_el]
         if N > 1:
             comm.all_gather(blocks, block)
+        if prof:
+            prof.mark('sel_allgather_ms')
         nb, stop = plan.panel(blocks, N, quota, k0, nbmax, U, ldu)
+        if prof:
+            prof.mark('sel_panel_ms')
         plan.flush(phi, ldl, Lt, ldl, k0, nb)
+        if prof:
+            prof.mark('sel_flush_ms')
+            for kk, vv in prof.times.items():
+                acc[kk] += vv
         k0 += nb
         npanels += 1
         if stop or nb == 0:
@@ -253,6 +267,8 @@ def build(mydf, comm, ops=None):
                                   ev.times.get('wsolve_ms', 0.0))
     mydf.timings['build_wall_s'] = time.perf_counter() - t0
     mydf.timings['select_panels'] = npanels
+    if prof:
+        mydf.timings.update(acc)
     mydf.n_ip = npts
     mydf.ip_index = ip
     mydf.ip_resid = resid
