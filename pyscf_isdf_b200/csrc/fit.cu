@@ -178,6 +178,32 @@ int solve_upper(isdf_handle* h, const double* U, long long ldu, int np, const do
     return ISDF_OK;
 }
 
+// Z <- U^-1 Z, right-looking: after a block row is solved, ALL rows above are updated with one
+// GEMM (M = r0, K = 128).  Same flops as solve_upper, but the parallelism is r0 x ng instead of
+// 128 x ng -- the better shape when Z is narrow (few right-hand sides: the column-sharded
+// congruence W = U^-1 M U^-T), at the price of re-streaming Z once per block row.
+int solve_upper_right(isdf_handle* h, const double* U, long long ldu, int np, const double* Vinv,
+                      double* Z, long long ldz, long long ng, double* tmp)
+{
+    int rc;
+    cudaStream_t s = h->stream;
+    const int nblk = (np + CB - 1) / CB;
+    for (int ib = nblk - 1; ib >= 0; --ib) {
+        const int r0 = ib * CB;
+        const int cb = std::min(CB, np - r0);
+        double* Zi = Z + (long long)r0 * ldz;
+        // Z_i = Vinv Z_i
+        if ((rc = gemm_call(h, cb, (int)ng, cb, Vinv + (size_t)ib * CB * CB, CB, 0, Zi, ldz, 1,
+                            tmp, pad8(ng), nullptr, 0, EPI_STORE, 0))) return rc;
+        CUDA_TRY(cudaMemcpy2DAsync(Zi, sizeof(double) * ldz, tmp, sizeof(double) * pad8(ng),
+                                   sizeof(double) * ng, cb, cudaMemcpyDeviceToDevice, s));
+        // Z[0:r0] -= U[0:r0, r0:r0+cb] Z_i
+        if (r0 > 0)
+            if ((rc = gemm_call(h, r0, (int)ng, cb, U + r0, ldu, 0, Zi, ldz, 1, Z, ldz, Z, 1, EPI_STORE, 0))) return rc;
+    }
+    return ISDF_OK;
+}
+
 struct FitWs { double* X; double* U; double* Vinv; double* tmp; int* info; };
 
 size_t carve_fit(FitWs& w, void* ws, size_t bytes, int nao, long long ng, int np)
@@ -291,7 +317,11 @@ extern "C" int isdf_fit_aux_from_U(isdf_handle* h, double* U, long long ldu, int
     CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FIT], s));
     CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int) * 4, s));
     if ((rc = invert_diag_blocks(h, U, ldu, np, Vinv, info))) return rc;
-    if ((rc = solve_upper(h, U, ldu, np, Vinv, Z, ldz, ngl, tmp))) return rc;
+    if (ngl <= 4LL * np) {
+        if ((rc = solve_upper_right(h, U, ldu, np, Vinv, Z, ldz, ngl, tmp))) return rc;
+    } else {
+        if ((rc = solve_upper(h, U, ldu, np, Vinv, Z, ldz, ngl, tmp))) return rc;
+    }
     CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FIT], s));
     h->ev_used[ISDF_STAGE_FIT] = true;
     return ISDF_OK;

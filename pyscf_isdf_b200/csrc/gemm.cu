@@ -37,7 +37,7 @@ namespace {
 constexpr int BK = 16;
 constexpr int NSTAGE = 3;
 constexpr int WTM = 64, WTN = 32;          // warp tile
-constexpr int KPAD = BK + 4;               // k-contiguous rows: stride == 4 (mod 16) doubles
+constexpr int MINB = 3;                    // CTAs per SM the 64x128 tile is built for (registers <= 168)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
 {
@@ -51,12 +51,23 @@ __device__ __forceinline__ void dmma884(double (&c)[2], double a, double b)
                  : "d"(a), "d"(b));
 }
 
-// shared-memory footprint (doubles) of one operand tile of BX rows/cols
+// Shared-memory image of one operand tile (BX rows/cols x BK), unpadded, XOR-swizzled so that
+// the DMMA fragment loads (lane = 4*g + t reads element (x = x0 + g, k = k0 + t)) hit 16
+// distinct 8-byte words per half-warp:
+//   k-major     S[k][x ^ ((k & 3) << 2)]      row stride BX
+//   k-contiguous S[x][k ^ ((x & 3) << 2)]      row stride BK
+// The swizzle permutes 4-double groups only, so 16-byte cp.async chunks stay intact.
+// No padding: 3 stages of a 64x128 tile are 72 KiB and three CTAs fit one SM.
 template <int BX, bool KMAJOR>
 struct OpTile {
-    static constexpr int LD = KMAJOR ? BX + 4 : KPAD;       // row stride, == 4 (mod 16)
+    static constexpr int LD = KMAJOR ? BX : BK;
     static constexpr int ROWS = KMAJOR ? BK : BX;
     static constexpr int SIZE = ROWS * LD;
+    // offset of element (x, k)
+    __device__ static __forceinline__ int at(int x, int k)
+    {
+        return KMAJOR ? k * BX + (x ^ ((k & 3) << 2)) : x * BK + (k ^ ((x & 3) << 2));
+    }
 };
 
 // ---- synchronous zero-filling loader (operands that are not 16-byte aligned) -------------------------
@@ -72,7 +83,7 @@ __device__ __forceinline__ void load_slow(double* S, const double* __restrict__ 
         double v = 0.0;
         if (x0 + x < dimX && k0 + k < K)
             v = KMAJOR ? g[(long long)(k0 + k) * ld + x0 + x] : g[(long long)(x0 + x) * ld + k0 + k];
-        S[KMAJOR ? k * T::LD + x : x * T::LD + k] = v;
+        S[T::at(x, k)] = v;
     }
 }
 
@@ -100,7 +111,7 @@ __device__ __forceinline__ void load_async(double* S, const double* __restrict__
             int bytes = 0;
             if (k < K) bytes = (x + 1 < dimX) ? 16 : (x < dimX ? 8 : 0);
             const double* src = bytes ? g + (long long)k * ld + x : g;
-            cp_async16(S + r * T::LD + c, src, bytes);
+            cp_async16(S + T::at(c, r), src, bytes);
         }
     } else {
         constexpr int CPR = BK / 2;                     // 16-byte chunks per x row
@@ -111,13 +122,13 @@ __device__ __forceinline__ void load_async(double* S, const double* __restrict__
             int bytes = 0;
             if (x < dimX) bytes = (k + 1 < K) ? 16 : (k < K ? 8 : 0);
             const double* src = bytes ? g + (long long)x * ld + k : g;
-            cp_async16(S + r * T::LD + c, src, bytes);
+            cp_async16(S + T::at(r, c), src, bytes);
         }
     }
 }
 
 // ---- one k-tile of DMMAs on a resident stage ------------------------------------------------
-template <bool AK, bool BKM, bool NEG, int LDA, int LDB>
+template <typename TA, typename TB, bool NEG>
 __device__ __forceinline__ void compute_stage(const double* __restrict__ As, const double* __restrict__ Bs,
                                               double (&acc)[8][4][2], int wm, int wn, int g, int t)
 {
@@ -126,12 +137,12 @@ __device__ __forceinline__ void compute_stage(const double* __restrict__ As, con
         double a[8], b[4];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            const double v = AK ? As[(kk + t) * LDA + wm + 8 * i + g] : As[(wm + 8 * i + g) * LDA + kk + t];
+            const double v = As[TA::at(wm + 8 * i + g, kk + t)];
             a[i] = NEG ? -v : v;
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j)
-            b[j] = BKM ? Bs[(kk + t) * LDB + wn + 8 * j + g] : Bs[(wn + 8 * j + g) * LDB + kk + t];
+            b[j] = Bs[TB::at(wn + 8 * j + g, kk + t)];
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
@@ -140,7 +151,7 @@ __device__ __forceinline__ void compute_stage(const double* __restrict__ As, con
 }
 
 template <int WM, int WN, bool AK, bool BKM, bool NEG>
-__global__ void __launch_bounds__(32 * WM * WN, (WM * WN <= 4) ? 2 : 1)
+__global__ void __launch_bounds__(32 * WM * WN, (WM * WN == 4) ? MINB : 4)
 dgemm_kernel(GemmParams p)
 {
     constexpr int BM = WTM * WM, BN = WTN * WN, NT = 32 * WM * WN;
@@ -195,7 +206,7 @@ dgemm_kernel(GemmParams p)
         if (kt + NSTAGE - 1 < nfull) issue(kt + NSTAGE - 1);
         cp_async_commit();
         const double* As = smem + s * STAGE;
-        compute_stage<AK, BKM, NEG, TA::LD, TB::LD>(As, As + TA::SIZE, acc, wm, wn, g, t);
+        compute_stage<TA, TB, NEG>(As, As + TA::SIZE, acc, wm, wn, g, t);
     }
     // unaligned operands: synchronous zero-filling loads
     for (int k0 = nfull * BK; k0 < K; k0 += BK) {
@@ -205,7 +216,7 @@ dgemm_kernel(GemmParams p)
         load_slow<BM, AK, NT>(As, p.A, p.lda, M, K, m0, k0, tid);
         load_slow<BN, BKM, NT>(Bs, p.B, p.ldb, N, K, n0, k0, tid);
         __syncthreads();
-        compute_stage<AK, BKM, NEG, TA::LD, TB::LD>(As, Bs, acc, wm, wn, g, t);
+        compute_stage<TA, TB, NEG>(As, Bs, acc, wm, wn, g, t);
     }
 
     // epilogue: lane holds C[m][n], C[m][n+1] of every 8x8 tile
