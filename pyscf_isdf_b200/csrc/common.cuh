@@ -49,7 +49,7 @@ struct isdf_handle {
     int prof_on, prof_n, prof_cap;
     cudaEvent_t* prof_ev;      // 2 * prof_cap events
     double prof_flops;
-    int gemm_force;            // 0 auto, 2: 64x128, 3: 64x64 CTA tile (tuning knob)
+    int gemm_force;            // 0 auto, 2..5: CTA tile / ring depth (tuning knob, see isdf_set_gemm_tile)
 };
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

@@ -35,7 +35,6 @@
 namespace {
 
 constexpr int BK = 16;
-constexpr int NSTAGE = 3;
 constexpr int WTM = 64, WTN = 32;          // warp tile
 constexpr int MINB = 3;                    // CTAs per SM the 64x128 tile is built for (registers <= 168)
 
@@ -150,8 +149,10 @@ __device__ __forceinline__ void compute_stage(const double* __restrict__ As, con
     }
 }
 
-template <int WM, int WN, bool AK, bool BKM, bool NEG>
-__global__ void __launch_bounds__(32 * WM * WN, (WM * WN == 4) ? MINB : 4)
+// NSTAGE = 3: large grids (2-3 CTAs per SM hide the load latency between them);
+// NSTAGE = 6: grids of at most one CTA per SM, where only a deeper ring hides it.
+template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG>
+__global__ void __launch_bounds__(32 * WM * WN, (NSTAGE > 3) ? 1 : ((WM * WN == 4) ? MINB : 4))
 dgemm_kernel(GemmParams p)
 {
     constexpr int BM = WTM * WM, BN = WTN * WN, NT = 32 * WM * WN;
@@ -246,12 +247,12 @@ dgemm_kernel(GemmParams p)
     }
 }
 
-template <int WM, int WN, bool AK, bool BKM, bool NEG>
+template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG>
 int launch_cfg(isdf_handle* h, const GemmParams& p)
 {
     constexpr int BM = WTM * WM, BN = WTN * WN, NT = 32 * WM * WN;
     const size_t smem = sizeof(double) * NSTAGE * (OpTile<BM, AK>::SIZE + OpTile<BN, BKM>::SIZE);
-    auto kern = dgemm_kernel<WM, WN, AK, BKM, NEG>;
+    auto kern = dgemm_kernel<WM, WN, NSTAGE, AK, BKM, NEG>;
     static bool configured = false;
     if (!configured) {
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -280,19 +281,19 @@ int launch_cfg(isdf_handle* h, const GemmParams& p)
     return ISDF_OK;
 }
 
-template <int WM, int WN>
+template <int WM, int WN, int NSTAGE>
 int dispatch_layout(isdf_handle* h, const GemmParams& p)
 {
     const int key = (p.a_kmajor ? 4 : 0) | (p.b_kmajor ? 2 : 0) | (p.neg ? 1 : 0);
     switch (key) {
-    case 0: return launch_cfg<WM, WN, false, false, false>(h, p);
-    case 1: return launch_cfg<WM, WN, false, false, true>(h, p);
-    case 2: return launch_cfg<WM, WN, false, true, false>(h, p);
-    case 3: return launch_cfg<WM, WN, false, true, true>(h, p);
-    case 4: return launch_cfg<WM, WN, true, false, false>(h, p);
-    case 5: return launch_cfg<WM, WN, true, false, true>(h, p);
-    case 6: return launch_cfg<WM, WN, true, true, false>(h, p);
-    default: return launch_cfg<WM, WN, true, true, true>(h, p);
+    case 0: return launch_cfg<WM, WN, NSTAGE, false, false, false>(h, p);
+    case 1: return launch_cfg<WM, WN, NSTAGE, false, false, true>(h, p);
+    case 2: return launch_cfg<WM, WN, NSTAGE, false, true, false>(h, p);
+    case 3: return launch_cfg<WM, WN, NSTAGE, false, true, true>(h, p);
+    case 4: return launch_cfg<WM, WN, NSTAGE, true, false, false>(h, p);
+    case 5: return launch_cfg<WM, WN, NSTAGE, true, false, true>(h, p);
+    case 6: return launch_cfg<WM, WN, NSTAGE, true, true, false>(h, p);
+    default: return launch_cfg<WM, WN, NSTAGE, true, true, true>(h, p);
     }
 }
 
@@ -304,8 +305,17 @@ int gemm_launch(isdf_handle* h, const GemmParams& p)
     ARG_CHECK(p.A && p.B && p.C && p.K >= 0);
     ARG_CHECK(p.epi != EPI_MUL || p.E != nullptr);
     auto tiles = [&](int bm, int bn) { return (long long)((p.M + bm - 1) / bm) * ((p.N + bn - 1) / bn); };
-    // 64x128 CTAs (2 per SM) once they cover the SMs; 64x64 for problems with few tiles
-    if (h->gemm_force == 2 || (h->gemm_force == 0 && tiles(64, 128) >= (long long)h->num_sms))
-        return dispatch_layout<1, 4>(h, p);
-    return dispatch_layout<1, 2>(h, p);
+    const long long t128 = tiles(64, 128);
+    switch (h->gemm_force) {
+    case 2: return dispatch_layout<1, 4, 3>(h, p);
+    case 3: return dispatch_layout<1, 2, 3>(h, p);
+    case 4: return dispatch_layout<1, 4, 6>(h, p);
+    case 5: return dispatch_layout<1, 2, 6>(h, p);
+    default: break;
+    }
+    // 64x128 CTAs, 3 per SM, once the grid is more than one CTA per SM; below that a
+    // 6-stage ring (one CTA per SM has nobody to hide its load latency behind)
+    if (t128 > (long long)h->num_sms) return dispatch_layout<1, 4, 3>(h, p);
+    if (t128 * 2 > (long long)h->num_sms) return dispatch_layout<1, 4, 6>(h, p);
+    return dispatch_layout<1, 2, 6>(h, p);
 }

@@ -507,11 +507,17 @@ panel_sweep_kernel(double* __restrict__ Ltp, long long ldl, long long ng, int nb
         double acc[SB], res[SB];
 #pragma unroll
         for (int i = 0; i < SB; ++i) acc[i] = (kb + i < nb) ? col[(long long)(kb + i) * ldl] : 0.0;
-        for (int j = 0; j < kb; ++j) {
-            const double x = -col[(long long)j * ldl];
+        // kb is a multiple of SB: fetch 8 earlier rows at a time so the loads overlap
+        for (int j0 = 0; j0 < kb; j0 += 8) {
+            double x[8];
 #pragma unroll
-            for (int i = 0; i < SB; ++i)
-                if (kb + i < nb) acc[i] = fma(x, s_l[(kb + i) * (kb + i + 1) / 2 + j], acc[i]);
+            for (int u = 0; u < 8; ++u) x[u] = -col[(long long)(j0 + u) * ldl];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+#pragma unroll
+                for (int i = 0; i < SB; ++i)
+                    if (kb + i < nb) acc[i] = fma(x[u], s_l[(kb + i) * (kb + i + 1) / 2 + j0 + u], acc[i]);
+            }
         }
 #pragma unroll
         for (int i = 0; i < SB; ++i) {
@@ -800,14 +806,15 @@ extern "C" int isdf_select_finish(isdf_select_plan* pl, int rank, long long* h_i
 // certificate ends panels early.
 extern "C" int isdf_select_next_quota(int quota, int nb, int nbmax, int nranks)
 {
+    // quota + 1 rows per rank (candidates + trailer) stays a power of two: whole GEMM tiles
     const int cap = MCAP / nranks - 1;
-    if (nb < nbmax / 2 && quota * 2 <= cap) return quota * 2;
+    if (nb < nbmax / 2 && 2 * quota + 1 <= cap) return 2 * quota + 1;
     return quota;
 }
 
 extern "C" int isdf_select_first_quota(int nranks)
 {
-    return std::max(NB, 1024 / nranks);
+    return std::max(NB, 1024 / nranks) - 1;
 }
 
 // ---- single-GPU driver ----------------------------------------------------------------

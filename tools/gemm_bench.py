@@ -22,7 +22,7 @@ def timeit(fn, reps=3):
 
 
 def main():
-    tiles = [int(x) for x in sys.argv[1:]] or [2, 3]
+    tiles = [int(x) for x in sys.argv[1:]] or [0, 2, 3, 4, 5]
     only = os.environ.get('GEMM_CASE')
     h = Handle(0)
     dev = h.torch_device
@@ -36,6 +36,9 @@ def main():
         ('solveU C-=A B    (kc,km)', 128, NG, 6240, 0, 1, 1, True, 0),
         ('W      A A^T     (kc,kc) upper', 4096, 4096, 65536, 0, 0, 0, False, 1),
         ('T      A^T A     (km,km)', 1024, 1024, 6240, 1, 1, 0, False, 0),
+        ('Tkc    A A^T     (kc,kc)', 1024, 1024, 6240, 0, 0, 0, False, 0),
+        ('wsolvL C-=A B    (kc,km) narrow', 128, 1560, 6240, 0, 1, 1, True, 0),
+        ('wsolvR C-=A B    (kc,km) narrow', 6240, 1560, 128, 0, 1, 1, True, 0),
         ('JK     X^T T     (km,km)', 12480, 12480, 832, 1, 1, 0, False, 0),
         ('JK     U X^T     (kc,kc)', 832, 832, 12480, 0, 0, 0, False, 0),
     ]
