@@ -183,7 +183,7 @@ int isdf_dgemm(isdf_handle* h, int M, int N, int K,
                double alpha, int neg, int epi, int upper_only);
 
 /* Tuning knob: CTA tile of the GEMM kernel, 0 = automatic (default),
- * 2 = 64x128 / 3 stages, 3 = 64x64 / 3 stages, 4 = 64x128 / 6 stages, 5 = 64x64 / 6 stages. */
+ * 2 = 64x128, 3 = 64x64. */
 int isdf_set_gemm_tile(isdf_handle* h, int which);
 
 /* Per-launch timing of the GEMM kernel (bench.py roofline): enable=1 resets and

@@ -149,8 +149,6 @@ __device__ __forceinline__ void compute_stage(const double* __restrict__ As, con
     }
 }
 
-// NSTAGE = 3: large grids (2-3 CTAs per SM hide the load latency between them);
-// NSTAGE = 6: grids of at most one CTA per SM, where only a deeper ring hides it.
 template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG>
 __global__ void __launch_bounds__(32 * WM * WN, (NSTAGE > 3) ? 1 : ((WM * WN == 4) ? MINB : 4))
 dgemm_kernel(GemmParams p)
@@ -305,14 +303,13 @@ int gemm_launch(isdf_handle* h, const GemmParams& p)
     ARG_CHECK(p.A && p.B && p.C && p.K >= 0);
     ARG_CHECK(p.epi != EPI_MUL || p.E != nullptr);
     auto tiles = [&](int bm, int bn) { return (long long)((p.M + bm - 1) / bm) * ((p.N + bn - 1) / bn); };
-    const long long t128 = tiles(64, 128);
-    switch (h->gemm_force) {
-    case 2: return dispatch_layout<1, 4, 3>(h, p);
-    case 3: return dispatch_layout<1, 2, 3>(h, p);
-    case 4: return dispatch_layout<1, 4, 6>(h, p);
-    case 5: return dispatch_layout<1, 2, 6>(h, p);
-    default: break;
-    }
+    // 64x128 CTAs (up to 3 per SM) once the grid exceeds one CTA per SM, else 64x64.
+    // (A 6-stage ring for small grids was measured and bought nothing: small grids are
+    // short of CTAs, not of prefetch depth -- profiles/r01_gemm_loaders.md.)
+    if (h->gemm_force == 2 || (h->gemm_force == 0 && tiles(64, 128) > (long long)h->num_sms))
+        return dispatch_layout<1, 4, 3>(h, p);
+    return dispatch_layout<1, 2, 3>(h, p);
+}
     // 64x128 CTAs, 3 per SM, once the grid is more than one CTA per SM; below that a
     // 6-stage ring (one CTA per SM has nobody to hide its load latency behind)
     if (t128 > (long long)h->num_sms) return dispatch_layout<1, 4, 3>(h, p);

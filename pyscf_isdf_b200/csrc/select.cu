@@ -804,10 +804,16 @@ extern "C" int isdf_select_finish(isdf_select_plan* pl, int rank, long long* h_i
 // Quota policy shared by the single-GPU driver below and the multi-rank host
 // driver (pyscf_isdf_b200/dist.py): grow the candidate set when the exactness
 // certificate ends panels early.
+extern "C" int isdf_select_first_quota(int nranks);
 extern "C" int isdf_select_next_quota(int quota, int nb, int nbmax, int nranks)
 {
-    // quota + 1 rows per rank (candidates + trailer) stays a power of two: whole GEMM tiles
-    const int cap = MCAP / nranks - 1;
+    // quota + 1 rows per rank (candidates + trailer) stays a power of two: whole GEMM tiles.
+    // The redundant panel work grows with (nranks * quota)^2, so the set is enlarged only
+    // while the certificate keeps ending panels early (ties across the set boundary) and
+    // falls back to the base size after every full panel.
+    const int base = isdf_select_first_quota(nranks);
+    const int cap = std::min(MCAP, 2048) / nranks - 1;
+    if (nb >= nbmax) return base;
     if (nb < nbmax / 2 && 2 * quota + 1 <= cap) return 2 * quota + 1;
     return quota;
 }
