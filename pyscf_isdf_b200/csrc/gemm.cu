@@ -310,9 +310,3 @@ int gemm_launch(isdf_handle* h, const GemmParams& p)
         return dispatch_layout<1, 4, 3>(h, p);
     return dispatch_layout<1, 2, 3>(h, p);
 }
-    // 64x128 CTAs, 3 per SM, once the grid is more than one CTA per SM; below that a
-    // 6-stage ring (one CTA per SM has nobody to hide its load latency behind)
-    if (t128 > (long long)h->num_sms) return dispatch_layout<1, 4, 3>(h, p);
-    if (t128 * 2 > (long long)h->num_sms) return dispatch_layout<1, 4, 6>(h, p);
-    return dispatch_layout<1, 2, 6>(h, p);
-}
