@@ -39,6 +39,7 @@ def parse_args():
     ap.add_argument('--fit', default='implicit', choices=['implicit', 'pivot_factor', 'cholesky'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--jk-reps', type=int, default=5)
+    ap.add_argument('--no-e2e', action='store_true', help='exploratory runs only: skip the host-API leg')
     return ap.parse_args()
 
 
@@ -304,14 +305,18 @@ def run_b200(args):
     jk_ms = float(np.median(jk_ms[2:]))
 
     # end to end through the plugin's host API
-    step_e2e()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 2))
-    for _ in range(e2e_steps):
-        vj, vk = step_e2e()
-    barrier()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    if args.no_e2e:
+        vj, vk = mydf.get_jk(dm_host[0], exxdiv=None)
+        e2e_s = float('nan')
+    else:
+        step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        e2e_steps = max(1, min(args.steps, 2))
+        for _ in range(e2e_steps):
+            vj, vk = step_e2e()
+        barrier()
+        e2e_s = (time.perf_counter() - t0) / e2e_steps
     rcut, Ls = cell.ao_eval_params()
     h2d = int(cell._atm.nbytes + cell._bas.nbytes + cell._env.nbytes + np.asarray(Ls).nbytes +
               np.asarray(rcut).nbytes + dm_host.nbytes + 8 * mydf.n_ip)

@@ -243,6 +243,7 @@ def build(mydf, comm, ops=None):
         comm.all_to_all(ops.as_real(recv)[:sum(out_splits)], ops.as_real(send)[:sum(in_splits)],
                         out_splits, in_splits)
         ops.fft_unpack(recv, nv, part.x_off, ncl, Y[v0:], ldy)
+    del Lt                                      # the factor rows are not needed past this point
     ops.fft_x_coulomb(Y, ldy, npts, mesh, a, col0, ncl)
     ev.mark('fft_ms')
     W = ops.empty((npts, npts))
@@ -260,7 +261,7 @@ def build(mydf, comm, ops=None):
     else:
         W = W[p0:p1]
     ops.synchronize()
-    del Lt, U
+    del U
 
     mydf.timings = dict(ev.times)
     mydf.timings['coulomb_ms'] = (ev.times.get('fft_ms', 0.0) + ev.times.get('wgemm_ms', 0.0) +
