@@ -152,6 +152,16 @@ int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nvec,
                        const int* h_mesh, const double* h_a, int col0, int ncl);
 int isdf_symmetrize_upper(isdf_handle* h, double* W, long long ld, int n);
 
+/* Upper triangle of C[n,n] = alpha * A A^T (A [n,K] row-major FP64, 16-byte aligned, lda even)
+ * computed on the int8 tensor cores (tcgen05 kind::i8, exact int32 accumulation) from
+ * `nslices` signed 7-bit digit planes per row-scaled entry (error-free splitting; 8 planes
+ * reproduce FP64-GEMM accuracy, see csrc/syrk_i8.cu).  Replaces the FP64 isdf_dgemm call of
+ * the W build [spec; the exact-FFTDF analogue is the einsum of
+ * pyscf/pbc/df/fft_jk.py:93-94]; follow with isdf_symmetrize_upper. */
+size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices);
+int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A, long long lda,
+                 double* C, long long ldc, double alpha, int nslices, void* ws, size_t ws_bytes);
+
 /* Stage 5 [spec; exact limit pyscf/pbc/df/fft_jk.py:33-109,177-302].
  * X[nao, np] = phi[:, ip];  J = X diag(W rho) X^T, rho_P = (X^T D X)_PP;
  * K = X ((X^T D X) o W) X^T.  dm/vj/vk: [nset, nao, nao]. */

@@ -51,6 +51,8 @@ SIGNATURES = {
     'isdf_fft_unpack': (c_int, [c_vp, c_vp, c_int, c_vp, c_int, c_int, c_vp, c_ll]),
     'isdf_fft_x_coulomb': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_vp, c_int, c_int]),
     'isdf_symmetrize_upper': (c_int, [c_vp, c_vp, c_ll, c_int]),
+    'isdf_syrk_i8_ws_bytes': (c_sz, [c_int, c_ll, c_int]),
+    'isdf_syrk_i8': (c_int, [c_vp, c_int, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_vp, c_sz]),
     'isdf_get_jk_block_ws_bytes': (c_sz, [c_int, c_int, c_int]),
     'isdf_get_jk_block': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_int, c_int, c_int,
                                   c_int, c_int, c_vp, c_vp, c_vp, c_sz]),
@@ -316,6 +318,14 @@ class Handle:
 
     def symmetrize_upper(self, W, ld, n):
         check(self.lib.isdf_symmetrize_upper(self.h, c_vp(W.data_ptr()), ld, n))
+
+    def syrk_i8(self, n, K, A, lda, C, ldc, alpha=1.0, nslices=8):
+        """Upper triangle of C = alpha * A A^T on the int8 tensor cores (csrc/syrk_i8.cu)."""
+        nbytes = self.lib.isdf_syrk_i8_ws_bytes(n, K, nslices)
+        ws = self.workspace(nbytes)
+        check(self.lib.isdf_syrk_i8(self.h, n, K, c_vp(A.data_ptr()), lda, c_vp(C.data_ptr()), ldc,
+                                    float(alpha), int(nslices), c_vp(ws.data_ptr()), nbytes))
+        return ws
 
     def get_jk_block(self, X, Wrows, ldw, p0, npl, dm, nset, nao, npts, with_j, with_k, vj, vk, ws=None):
         nbytes = self.lib.isdf_get_jk_block_ws_bytes(nao, npts, npl)

@@ -84,6 +84,37 @@ __device__ __forceinline__ void dft_small(double2* u, const double2* tw, int n)
         const double2 d = csub(u[1], u[2]);
         const double2 s = make_double2(-c * d.y, c * d.x);       // SIGN * i * (sqrt3/2) * d
         u[0] = cadd(u[0], t); u[1] = cadd(m, s); u[2] = csub(m, s);
+    } else if (R == 5) {
+        // X1,4 = m1 +- i SIGN n1, X2,3 = m2 +- i SIGN n2 (constants cos/sin(2 pi k/5))
+        const double c1 = 0.30901699437494742, c2 = -0.80901699437494742;
+        const double s1 = 0.95105651629515357 * SIGN, s2 = 0.58778525229247313 * SIGN;
+        const double2 t1 = cadd(u[1], u[4]), t2 = cadd(u[2], u[3]);
+        const double2 t3 = csub(u[1], u[4]), t4 = csub(u[2], u[3]);
+        const double2 m1 = make_double2(u[0].x + c1 * t1.x + c2 * t2.x, u[0].y + c1 * t1.y + c2 * t2.y);
+        const double2 m2 = make_double2(u[0].x + c2 * t1.x + c1 * t2.x, u[0].y + c2 * t1.y + c1 * t2.y);
+        // i * (s1 t3 + s2 t4), i * (s2 t3 - s1 t4)
+        const double2 n1 = make_double2(-(s1 * t3.y + s2 * t4.y), s1 * t3.x + s2 * t4.x);
+        const double2 n2 = make_double2(-(s2 * t3.y - s1 * t4.y), s2 * t3.x - s1 * t4.x);
+        u[0] = cadd(u[0], cadd(t1, t2));
+        u[1] = cadd(m1, n1); u[4] = csub(m1, n1);
+        u[2] = cadd(m2, n2); u[3] = csub(m2, n2);
+    } else if (R == 7) {
+        const double c1 = 0.62348980185873353, c2 = -0.22252093395631440, c3 = -0.90096886790241913;
+        const double s1 = 0.78183148246802981 * SIGN, s2 = 0.97492791218182361 * SIGN,
+                     s3 = 0.43388373911755812 * SIGN;
+        const double2 t1 = cadd(u[1], u[6]), t2 = cadd(u[2], u[5]), t3 = cadd(u[3], u[4]);
+        const double2 d1 = csub(u[1], u[6]), d2 = csub(u[2], u[5]), d3 = csub(u[3], u[4]);
+        const double2 m1 = make_double2(u[0].x + c1 * t1.x + c2 * t2.x + c3 * t3.x, u[0].y + c1 * t1.y + c2 * t2.y + c3 * t3.y);
+        const double2 m2 = make_double2(u[0].x + c2 * t1.x + c3 * t2.x + c1 * t3.x, u[0].y + c2 * t1.y + c3 * t2.y + c1 * t3.y);
+        const double2 m3 = make_double2(u[0].x + c3 * t1.x + c1 * t2.x + c2 * t3.x, u[0].y + c3 * t1.y + c1 * t2.y + c2 * t3.y);
+        // i * (s1 d1 + s2 d2 + s3 d3), i * (s2 d1 - s3 d2 - s1 d3), i * (s3 d1 - s1 d2 + s2 d3)
+        const double2 n1 = make_double2(-(s1 * d1.y + s2 * d2.y + s3 * d3.y), s1 * d1.x + s2 * d2.x + s3 * d3.x);
+        const double2 n2 = make_double2(-(s2 * d1.y - s3 * d2.y - s1 * d3.y), s2 * d1.x - s3 * d2.x - s1 * d3.x);
+        const double2 n3 = make_double2(-(s3 * d1.y - s1 * d2.y + s2 * d3.y), s3 * d1.x - s1 * d2.x + s2 * d3.x);
+        u[0] = cadd(cadd(u[0], t1), cadd(t2, t3));
+        u[1] = cadd(m1, n1); u[6] = csub(m1, n1);
+        u[2] = cadd(m2, n2); u[5] = csub(m2, n2);
+        u[3] = cadd(m3, n3); u[4] = csub(m3, n3);
     } else {
         double2 v[R];
         const int step = n / R;
@@ -99,6 +130,16 @@ __device__ __forceinline__ void dft_small(double2* u, const double2* tw, int n)
     }
 }
 
+// exact a / b for 0 <= a < 2^24, b > 0, with a precomputed float reciprocal
+__device__ __forceinline__ int fast_div(int a, int b, float invb)
+{
+    int q = __float2int_rz(__int2float_rn(a) * invb);
+    const int r = a - q * b;
+    if (r < 0) --q;
+    else if (r >= b) ++q;
+    return q;
+}
+
 template <int R, int SIGN>
 __device__ __forceinline__ void stage_small(const double2* __restrict__ in, double2* __restrict__ out,
                                             const Radix& pl, int p, int nlines, int line_stride,
@@ -106,11 +147,12 @@ __device__ __forceinline__ void stage_small(const double2* __restrict__ in, doub
 {
     const int n = pl.n, t = n / R;
     const int tws = n / (p * R);
+    const float inv_nl = 1.0f / (float)nlines, inv_t = 1.0f / (float)t, inv_p = 1.0f / (float)p;
     for (int idx = threadIdx.x; idx < nlines * t; idx += blockDim.x) {
         int line, i;
-        if (line_fast) { i = idx / nlines; line = idx - i * nlines; }
-        else { line = idx / t; i = idx - line * t; }
-        const int k = i % p;
+        if (line_fast) { i = fast_div(idx, nlines, inv_nl); line = idx - i * nlines; }
+        else { line = fast_div(idx, t, inv_t); i = idx - line * t; }
+        const int k = i - fast_div(i, p, inv_p) * p;
         const int j = (i - k) * R + k;
         const double2* src = in + (long long)line * line_stride;
         double2* dst = out + (long long)line * line_stride;

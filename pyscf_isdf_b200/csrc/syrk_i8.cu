@@ -1,0 +1,399 @@
+// FP64-accurate symmetric product C = alpha * A A^T on the int8 tensor cores (tcgen05,
+// sm_100a) by error-free splitting (the Ozaki scheme).
+//
+// B200 has no FP64 tcgen05 kind: the FP64 tensor pipe (DMMA, gemm.cu) peaks at 37 TFLOP/s
+// while kind::i8 runs at 4.5 POP/s with exact int32 accumulation.  Every row of a K-chunk
+// of A is scaled by a power of two and cut into S signed 7-bit digit planes
+//     A[i,k] = 2^e_i * sum_s q_s[i,k] * 2^(-6-7s),   |q_s| <= 64,
+// the digit planes are multiplied exactly on the tensor cores,
+//     P_g = sum_{s+t=g} q_s q_t^T          (int32, exact for (g+1)*Kc*64^2 < 2^31),
+// and C += alpha * 2^(e_i+e_j) * sum_{g<S} 2^(-12-7g) P_g is accumulated in FP64.  With
+// S = 8 the result is as accurate as an FP64 GEMM (profiles/r01_ozaki.md); the cost is
+// S(S+1)/2 = 36 int8 products instead of one FP64 product at 1/120 of the rate.
+//
+// It is used for the Coulomb metric W = (vol/Ng^2) Y Y^T, whose entries
+// only need the 1e-8 J/K tolerance; the interpolation-point selection stays on the
+// bit-reproducible FP64 chain of gemm.cu.
+//
+// Kernel anatomy (one CTA per SM, persistent over upper-triangle 128x256 tiles):
+//   warp 0 (one lane)  TMA producer: 128x128-byte boxes of the digit planes (3-D tensor map
+//                      [K, rows, plane], SWIZZLE_128B) into a 4-stage shared-memory ring
+//   warp 1 (one lane)  tcgen05.mma kind::i8, M=128 N=256 K=32, accumulators in TMEM
+//                      (2 x 256 columns: the epilogue of unit u overlaps the MMAs of u+1)
+//   warps 2-5          epilogue: tcgen05.ld -> int32 -> FP64, scale, C += in global memory
+#include "common.cuh"
+#include "../../include/isdf_b200.h"
+#include <cuda.h>
+#include <cmath>
+#include <vector>
+#include <algorithm>
+
+namespace {
+
+constexpr int TM = 128;            // tile rows   (UMMA M)
+constexpr int TN = 256;            // tile cols   (UMMA N)
+constexpr int BKB = 128;           // K bytes per stage = one 128-byte swizzle atom
+constexpr int UK = 32;             // K per tcgen05.mma (kind::i8)
+constexpr int NSTAGE = 4;
+constexpr int A_BYTES = TM * BKB;  // 16 KiB
+constexpr int B_BYTES = TN * BKB;  // 32 KiB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int SMEM_BYTES = NSTAGE * STAGE_BYTES + 1024;    // + alignment slack
+constexpr int NTHREADS = 192;
+constexpr int KC_MAX = 32768;      // int32 exactness: 12 * 32768 * 64^2 < 2^31
+constexpr int S_MAX = 12;
+constexpr int STRIP = 8;           // tile columns per strip of the persistent schedule
+constexpr long long WAIT_LIMIT = 4000000000LL;             // clocks before a stuck barrier traps
+
+// ---------------------------------------------------------------- PTX wrappers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok = 0;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) break;
+        if (clock64() - t0 > WAIT_LIMIT) __trap();          // never hang the device on a protocol bug
+    }
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 :: "r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_i8(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, int* v)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor of a K-major tile whose rows are 128 bytes (one
+// SWIZZLE_128B atom): 8-row groups are 1024 bytes apart (stride byte offset), the leading
+// byte offset is unused, descriptor version 1 (sm_100), layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t umma_desc_k128(uint32_t saddr)
+{
+    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// Instruction descriptor, kind::i8: D = S32 (bits 4-5 = 2), A and B signed 8 bit (bits 7-9,
+// 10-12 = 1), both K-major (bits 15, 16 = 0), N >> 3 in bits 17-22, M >> 4 in bits 24-28.
+constexpr uint32_t IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+
+struct SyrkArgs {
+    const int2* tiles; int ntiles;     // (ti, tj): rows 128*ti.., cols 256*tj..
+    int n, nkb, S;                     // matrix order, 128-byte K blocks in this chunk, digit planes
+    double* C; long long ldc;
+    const double* sc;                  // row scales 2^e_i of this chunk
+    double alpha;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t bar_full[NSTAGE], bar_empty[NSTAGE], bar_tfull[2], bar_tempty[2];
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;     // SWIZZLE_128B tiles: 1024-byte aligned
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < NSTAGE; ++i) { mbar_init(smem_u32(&bar_full[i]), 1); mbar_init(smem_u32(&bar_empty[i]), 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bar_tfull[i]), 1); mbar_init(smem_u32(&bar_tempty[i]), 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {                                                   // whole TMEM: two 256-column accumulators
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            int st = 0; uint32_t ph = 0;
+            for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
+                const int2 tl = a.tiles[t];
+                for (int g = a.S - 1; g >= 0; --g)
+                    for (int s = 0; s <= g; ++s)
+                        for (int kb = 0; kb < a.nkb; ++kb) {
+                            mbar_wait(smem_u32(&bar_empty[st]), ph ^ 1);
+                            const uint32_t full = smem_u32(&bar_full[st]);
+                            const uint32_t sa = smem0 + st * STAGE_BYTES, sb = sa + A_BYTES;
+                            mbar_expect_tx(full, STAGE_BYTES);
+                            tma_load_3d(sa, &tmap, full, kb * BKB, tl.x * TM, s);
+                            tma_load_3d(sb, &tmap, full, kb * BKB, tl.y * TN, g - s);
+                            tma_load_3d(sb + A_BYTES, &tmap, full, kb * BKB, tl.y * TN + 128, g - s);
+                            if (++st == NSTAGE) { st = 0; ph ^= 1; }
+                        }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            int st = 0; uint32_t ph = 0;
+            uint32_t unit = 0;
+            for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x)
+                for (int g = a.S - 1; g >= 0; --g, ++unit) {
+                    const uint32_t buf = unit & 1, bph = (unit >> 1) & 1;
+                    mbar_wait(smem_u32(&bar_tempty[buf]), bph ^ 1);     // epilogue has drained this accumulator
+                    tc_fence_after();
+                    const uint32_t tmem_d = tmem_base + buf * TN;
+                    const int niter = (g + 1) * a.nkb;
+                    for (int it = 0; it < niter; ++it) {
+                        mbar_wait(smem_u32(&bar_full[st]), ph);
+                        tc_fence_after();
+                        const uint32_t sa = smem0 + st * STAGE_BYTES, sb = sa + A_BYTES;
+#pragma unroll
+                        for (int k = 0; k < BKB / UK; ++k)
+                            tc_mma_i8(tmem_d, umma_desc_k128(sa + k * UK), umma_desc_k128(sb + k * UK), IDESC,
+                                      (it | k) != 0);
+                        tc_commit(smem_u32(&bar_empty[st]));            // frees the stage when these MMAs retire
+                        if (++st == NSTAGE) { st = 0; ph ^= 1; }
+                    }
+                    tc_commit(smem_u32(&bar_tfull[buf]));               // accumulator complete
+                }
+        }
+    } else {
+        // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
+        const int q = warp & 3;
+        uint32_t unit = 0;
+        for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
+            const int2 tl = a.tiles[t];
+            const int row = tl.x * TM + q * 32 + lane;
+            const double srow = row < a.n ? a.sc[row] : 0.0;
+            double* crow = a.C + (long long)row * a.ldc;
+            for (int g = a.S - 1; g >= 0; --g, ++unit) {
+                const uint32_t buf = unit & 1, bph = (unit >> 1) & 1;
+                const double f = a.alpha * srow * exp2((double)(-12 - 7 * g));
+                mbar_wait(smem_u32(&bar_tfull[buf]), bph);
+                tc_fence_after();
+#pragma unroll 1
+                for (int cc = 0; cc < TN / 32; ++cc) {
+                    int v[32];
+                    tc_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + buf * TN + cc * 32, v);
+                    if (cc == TN / 32 - 1) {                            // all TMEM reads of this unit are done
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(smem_u32(&bar_tempty[buf]));
+                    }
+                    const int col0 = tl.y * TN + cc * 32;
+                    if (row < a.n && col0 + 31 >= row) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int col = col0 + j;
+                            if (col < a.n && col >= row) crow[col] += (double)v[j] * (f * a.sc[col]);
+                        }
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
+// ---- digit planes -----------------------------------------------------------------
+// sc[i] = 2^e with max_k |A[i, k0:k0+kc]| = m * 2^e, m in [0.5, 1)
+__global__ void i8_rowscale_kernel(const double* __restrict__ A, long long lda, long long k0, int kc,
+                                   double* __restrict__ sc)
+{
+    const double* row = A + (long long)blockIdx.x * lda + k0;
+    double m = 0.0;
+    for (int k = threadIdx.x; k < kc; k += blockDim.x) m = fmax(m, fabs(row[k]));
+    __shared__ double red[32];
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (threadIdx.x == 0) {
+            int e = 0;
+            if (m > 0.0) frexp(m, &e);
+            sc[blockIdx.x] = ldexp(1.0, e);
+        }
+    }
+}
+
+// planes[s][i][k] = s-th signed 7-bit digit of A[i, k0+k] / sc[i]; 16 consecutive k per thread
+__global__ void i8_split_kernel(const double* __restrict__ A, long long lda, int n, long long k0, int kc, int kcpad,
+                                const double* __restrict__ sc, int8_t* __restrict__ planes,
+                                long long row_stride, long long plane_stride, int S)
+{
+    const int groups = kcpad / 16;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)n * groups) return;
+    const int i = (int)(idx / groups), kg = (int)(idx - (long long)i * groups) * 16;
+    const double inv = 1.0 / sc[i];                     // exact: a power of two
+    const double* src = A + (long long)i * lda + k0 + kg;
+    double x[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] = (kg + j < kc) ? src[j] * inv : 0.0;
+    int8_t* dst = planes + (long long)i * row_stride + kg;
+    for (int s = 0; s < S; ++s) {
+        const double mult = s == 0 ? 64.0 : 128.0;
+        uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const double y = x[j] * mult;
+            const double qd = rint(y);
+            x[j] = y - qd;                              // exact remainder, |.| <= 1/2
+            w[j >> 2] |= ((uint32_t)(__double2int_rn(qd)) & 0xffu) << (8 * (j & 3));
+        }
+        *reinterpret_cast<uint4*>(dst + s * plane_stride) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn()
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+struct Chunks { int nchunks, kc_full; };
+
+Chunks plan_chunks(long long K)
+{
+    Chunks c;
+    c.nchunks = (int)((K + KC_MAX - 1) / KC_MAX);
+    const long long per = (K + c.nchunks - 1) / c.nchunks;
+    c.kc_full = (int)align_up((size_t)per, BKB);
+    return c;
+}
+
+}  // namespace
+
+extern "C" size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices)
+{
+    if (n <= 0 || K <= 0 || nslices <= 0) return 0;
+    const Chunks c = plan_chunks(K);
+    const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
+    return align_up((size_t)nslices * n * c.kc_full, 256) + align_up((size_t)n * sizeof(double), 256) +
+           align_up((size_t)tr * tc * sizeof(int2), 256) + 1024;
+}
+
+extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A, long long lda,
+                            double* C, long long ldc, double alpha, int nslices, void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && A && C && ws);
+    ARG_CHECK(n > 0 && K > 0 && lda >= K && ldc >= n);
+    ARG_CHECK(nslices >= 2 && nslices <= S_MAX);
+    ARG_CHECK(((uintptr_t)A % 16) == 0 && lda % 2 == 0);
+    if (ws_bytes < isdf_syrk_i8_ws_bytes(n, K, nslices)) {
+        isdf_set_error("isdf_syrk_i8: workspace too small");
+        return ISDF_ERR_WS;
+    }
+    EncodeTiledFn encode = get_encode_fn();
+    if (!encode) {
+        isdf_set_error("isdf_syrk_i8: cuTensorMapEncodeTiled not available from the driver");
+        return ISDF_ERR_CUDA;
+    }
+    const Chunks ch = plan_chunks(K);
+    WsAlloc w(ws, ws_bytes);
+    int8_t* planes = w.get<int8_t>((size_t)nslices * n * ch.kc_full);
+    double* sc = w.get<double>(n);
+    const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
+    int2* d_tiles = w.get<int2>((size_t)tr * tc);
+
+    // persistent schedule: strips of STRIP tile columns, rows ascending inside a strip, so that the
+    // ~148 tiles in flight share few distinct row/column blocks (L2 reuse of the digit planes)
+    std::vector<int2> tiles;
+    for (int s0 = 0; s0 < tc; s0 += STRIP)
+        for (int ti = 0; ti < tr; ++ti)
+            for (int tj = s0; tj < std::min(tc, s0 + STRIP); ++tj)
+                if (ti <= 2 * tj + 1) tiles.push_back(make_int2(ti, tj));
+    const int ntiles = (int)tiles.size();
+    CUDA_TRY(cudaMemcpyAsync(d_tiles, tiles.data(), ntiles * sizeof(int2), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));          // `tiles` is pageable host memory
+
+    CUtensorMap tmap;
+    const cuuint64_t gdim[3] = {(cuuint64_t)ch.kc_full, (cuuint64_t)n, (cuuint64_t)nslices};
+    const cuuint64_t gstride[2] = {(cuuint64_t)ch.kc_full, (cuuint64_t)ch.kc_full * (cuuint64_t)n};
+    const cuuint32_t box[3] = {BKB, 128, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstride, box, estr,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) {
+        isdf_set_error("isdf_syrk_i8: cuTensorMapEncodeTiled failed (%d)", (int)cr);
+        return ISDF_ERR_CUDA;
+    }
+    CUDA_TRY(cudaFuncSetAttribute(syrk_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    CUDA_TRY(cudaMemset2DAsync(C, ldc * sizeof(double), 0, (size_t)n * sizeof(double), n, h->stream));
+
+    for (int c = 0; c < ch.nchunks; ++c) {
+        const long long k0 = (long long)c * ch.kc_full;
+        if (k0 >= K) break;
+        const int kc = (int)std::min<long long>(ch.kc_full, K - k0);
+        const int kcpad = (int)align_up((size_t)kc, BKB);
+        i8_rowscale_kernel<<<n, 256, 0, h->stream>>>(A, lda, k0, kc, sc);
+        const long long items = (long long)n * (kcpad / 16);
+        i8_split_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(
+            A, lda, n, k0, kc, kcpad, sc, planes, ch.kc_full, (long long)ch.kc_full * n, nslices);
+        SyrkArgs a;
+        a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = kcpad / BKB; a.S = nslices;
+        a.C = C; a.ldc = ldc; a.sc = sc; a.alpha = alpha;
+        syrk_i8_kernel<<<std::min(h->num_sms, ntiles), NTHREADS, SMEM_BYTES, h->stream>>>(tmap, a);
+        h->other_launches += 3;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return ISDF_OK;
+}

@@ -236,20 +236,41 @@ def build(mydf, comm, ops=None):
         if N == 1:
             ops.fft_zy(Lt[v0:], ldl, nv, nxl, mesh, Y[v0:], ldy)
             continue
+        if prof:
+            prof = ops.timer()
         ops.fft_zy(Lt[v0:], ldl, nv, nxl, mesh, spec, nxl * ncols)
         ops.fft_pack(spec, nxl * ncols, nv, nxl, ncols, part.col_off, send)
+        if prof:
+            prof.mark('fft_zy_pack_ms')
         in_splits = [2 * nv * nxl * part.ncol_local(s) for s in range(N)]
         out_splits = [2 * nv * part.nx_local(s) * ncl for s in range(N)]
         comm.all_to_all(ops.as_real(recv)[:sum(out_splits)], ops.as_real(send)[:sum(in_splits)],
                         out_splits, in_splits)
+        if prof:
+            prof.mark('fft_alltoall_ms')
         ops.fft_unpack(recv, nv, part.x_off, ncl, Y[v0:], ldy)
+        if prof:
+            prof.mark('fft_unpack_ms')
+            for kk, vv in prof.times.items():
+                acc[kk] = acc.get(kk, 0.0) + vv
     del Lt                                      # the factor rows are not needed past this point
+    if prof:
+        prof = ops.timer()
     ops.fft_x_coulomb(Y, ldy, npts, mesh, a, col0, ncl)
+    if prof:
+        prof.mark('fft_x_ms')
+        acc.update(prof.times)
     ev.mark('fft_ms')
     W = ops.empty((npts, npts))
     Yr = ops.as_real(Y)
-    ops.dgemm(npts, npts, 2 * nx * ncl, Yr, 2 * ldy, 0, Yr, 2 * ldy, 0, W, npts,
-              alpha=cell.vol / (float(ng) * float(ng)), upper_only=1)
+    wmode = str(getattr(mydf, 'wgemm', 'fp64'))
+    if wmode.startswith('i8'):
+        planes = int(wmode.split(':')[1]) if ':' in wmode else 8
+        ops.syrk_i8(npts, 2 * nx * ncl, Yr, 2 * ldy, W, npts,
+                    alpha=cell.vol / (float(ng) * float(ng)), nslices=planes)
+    else:
+        ops.dgemm(npts, npts, 2 * nx * ncl, Yr, 2 * ldy, 0, Yr, 2 * ldy, 0, W, npts,
+                  alpha=cell.vol / (float(ng) * float(ng)), upper_only=1)
     ops.symmetrize_upper(W, npts, npts)
     comm.all_reduce_sum(W)
     ev.mark('wgemm_ms')

@@ -30,10 +30,10 @@ from .cell import madelung as _madelung
 class ISDF:
     _keys = {'cell', 'kpts', 'mesh', 'c', 'n_ip', 'select', 'fit', 'tol', 'exxdiv',
              'ip_index', 'ip_resid', 'W', 'aoR', 'aoR_ip', 'stdout', 'verbose', 'max_memory',
-             'keep_aoR', 'timings', 'comm'}
+             'keep_aoR', 'timings', 'comm', 'wgemm'}
 
     def __init__(self, cell, kpts=np.zeros((1, 3)), c=15, n_ip=None, select='cholesky',
-                 fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None):
+                 fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None, wgemm='fp64'):
         self.cell = cell
         self.stdout = sys.stdout
         self.verbose = getattr(cell, 'verbose', 0)
@@ -46,6 +46,9 @@ class ISDF:
         self.tol = tol
         self.exxdiv = None
         self.keep_aoR = keep_aoR
+        # wgemm: how the Coulomb-metric product Y Y^T is computed: 'fp64' (FP64 tensor pipe) or
+        # 'i8' / 'i8:<planes>' (int8 tcgen05 split product, csrc/syrk_i8.cu; 8 planes by default)
+        self.wgemm = wgemm
         self._device = device
         self._handle = None
         # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
@@ -95,6 +98,8 @@ class ISDF:
             raise NotImplementedError("select=%r (only 'cholesky' pivoting is implemented)" % self.select)
         if self.fit not in ('implicit', 'cholesky', 'pivot_factor'):
             raise ValueError("fit must be 'implicit', 'cholesky' or 'pivot_factor'")
+        if self.wgemm != 'fp64' and not str(self.wgemm).startswith('i8'):
+            raise ValueError("wgemm must be 'fp64', 'i8' or 'i8:<planes>'")
         if self.comm is not None and self.fit == 'cholesky':
             raise NotImplementedError("fit='cholesky' is single-GPU only; use 'implicit' or 'pivot_factor'")
         if getattr(self.cell, 'dimension', 3) != 3:

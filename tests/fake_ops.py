@@ -243,6 +243,10 @@ class FakeOps:
         acc = acc * acc if epi == 1 else (acc * _np(E)[:M, :N] if epi == 2 else alpha * acc)
         _np(C)[:M, :N] = acc
 
+    def syrk_i8(self, n, K, A, lda, C, ldc, alpha=1.0, nslices=8):
+        An = _np(A)[:n, :K]
+        _np(C)[:n, :n] = np.triu(alpha * An.dot(An.T))
+
     def symmetrize_upper(self, W, ld, n):
         Wn = _np(W)
         Wn[:n, :n] = np.triu(Wn[:n, :n]) + np.triu(Wn[:n, :n], 1).T

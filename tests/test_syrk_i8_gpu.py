@@ -1,0 +1,48 @@
+"""GPU: the int8 tensor-core (tcgen05) split product isdf_syrk_i8 against the FP64 product.
+Tolerance: 8 digit planes reproduce FP64-GEMM accuracy, so the two agree to a few 1e-15
+relative to max|C| (written below as 2e-13 to cover long accumulations)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+pytestmark = pytest.mark.gpu
+
+
+def _run(n, K, S=8, alpha=1.0, pad=0, decay=False, seed=0):
+    import torch
+    from pyscf_isdf_b200 import _lib
+    h = _lib.Handle(0)
+    g = torch.Generator(device='cuda').manual_seed(seed)
+    lda = K + (K % 2) + 2 * pad
+    A = torch.zeros((n, lda), dtype=torch.float64, device='cuda')
+    A[:, :K] = torch.randn((n, K), dtype=torch.float64, device='cuda', generator=g)
+    if decay:
+        A[:, :K] *= torch.logspace(0, -8, K, dtype=torch.float64, device='cuda')[None, :]
+        A[n // 2] = 0.0                                     # an all-zero row
+    ldc = n + pad
+    C = torch.full((n, ldc), 7.0, dtype=torch.float64, device='cuda')
+    h.syrk_i8(n, K, A, lda, C, ldc, alpha=alpha, nslices=S)
+    h.symmetrize_upper(C, ldc, n)
+    torch.cuda.synchronize()
+    ref = alpha * (A[:, :K] @ A[:, :K].t())
+    err = float((C[:, :n] - ref).abs().max() / ref.abs().max())
+    if pad:
+        assert float((C[:, n:] - 7.0).abs().max()) == 0.0    # padding columns untouched
+    return err
+
+
+@pytest.mark.parametrize('n,K', [(200, 300), (128, 128), (257, 1000), (700, 5000), (1000, 70001)])
+def test_matches_fp64(n, K):
+    assert _run(n, K) < 2e-13
+
+
+def test_alpha_ld_and_dynamic_range():
+    assert _run(520, 40000, alpha=0.37, pad=3, decay=True) < 2e-13
+
+
+def test_fewer_planes_lose_accuracy_gracefully():
+    e6, e8 = _run(300, 4000, S=6), _run(300, 4000, S=8)
+    assert e8 < 2e-13 and e6 < 1e-9 and e6 > e8
