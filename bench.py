@@ -37,6 +37,9 @@ def parse_args():
     ap.add_argument('--workload', default=None, help='c8 | c64 | h2o32 | si216 | c8-small')
     ap.add_argument('--c', type=float, default=15.0, help='ISDF rank parameter: N_IP = c * nao')
     ap.add_argument('--fit', default='implicit', choices=['implicit', 'pivot_factor', 'cholesky'])
+    ap.add_argument('--wgemm', default='fp64',
+                    help="Coulomb-metric product Y Y^T: 'fp64' (FP64 tensor pipe) or 'i8[:planes]' "
+                         "(int8 tcgen05 split product, 8 digit planes = FP64-GEMM accuracy)")
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--jk-reps', type=int, default=5)
     ap.add_argument('--no-e2e', action='store_true', help='exploratory runs only: skip the host-API leg')
@@ -251,7 +254,7 @@ def run_b200(args):
     if world > 1:
         from pyscf_isdf_b200.dist import Comm
         comm = Comm()                 # grid sharded by x-planes, one rank per GPU (pyscf_isdf_b200/dist.py)
-    mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=False, comm=comm)
+    mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=False, comm=comm, wgemm=args.wgemm)
     h = mydf.handle
     dm_host = workloads.synthetic_dm(nao)[None]
     dm_pinned = torch.from_numpy(dm_host).pin_memory()
@@ -351,7 +354,7 @@ def run_b200(args):
         'higher_is_better': False, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f64',
         'data': 'synthetic',
         'config': {'workload': workloads.describe(name), 'c': args.c, 'nao': nao, 'ngrids': ng,
-                   'n_ip': int(mydf.n_ip), 'fit': args.fit, 'l2': 'inputs_exceed_l2' if 8.0 * ng * nao > 126e6 else 'inputs_fit_l2',
+                   'n_ip': int(mydf.n_ip), 'fit': args.fit, 'wgemm': args.wgemm, 'l2': 'inputs_exceed_l2' if 8.0 * ng * nao > 126e6 else 'inputs_fit_l2',
                    'parallelism': 'single' if world == 1 else 'grid-slab x%d (all-gather/all-to-all/all-reduce over NCCL)' % world},
         'build_s': build_s, 'jk_s': jk_ms / 1e3, 'stages_ms': stages_ms,
         'flop_model': fm,
@@ -359,6 +362,13 @@ def run_b200(args):
         'gpu_launches': int((l1[0] - l0[0]) + (l1[1] - l0[1])),
         'roofline': roofline, 'clocks': clocks,
     }
+    if args.wgemm.startswith('i8') and stages_ms.get('wgemm_ms'):
+        planes = int(args.wgemm.split(':')[1]) if ':' in args.wgemm else 8
+        ops = planes * (planes + 1) / 2.0 * fm['coulomb_gemm'] / world      # int8 ops of this rank's digit products
+        line['wgemm_i8'] = {'kernel': 'syrk_i8_kernel (tcgen05 kind::i8, TMEM accumulators, bulk-copy ring)',
+                            'planes': planes, 'int8_ops_per_rank': ops, 'ms': stages_ms['wgemm_ms'],
+                            'achieved_pops': ops / (stages_ms['wgemm_ms'] * 1e-3) / 1e15,
+                            'fp64_equivalent_tflops': fm['coulomb_gemm'] / world / (stages_ms['wgemm_ms'] * 1e-3) / 1e12}
     if world == 1 and not args.no_cpu_baseline:
         ncores = os.cpu_count() or 1
         t, dims = cpu_sample_step(ncores)

@@ -16,17 +16,20 @@
 // bit-reproducible FP64 chain of gemm.cu.
 //
 // Kernel anatomy (one CTA per SM, persistent over upper-triangle 128x256 tiles):
-//   warp 0 (one lane)  TMA producer: 128x128-byte boxes of the digit planes (3-D tensor map
-//                      [K, rows, plane], SWIZZLE_128B) into a 4-stage shared-memory ring
+//   warp 0 (one lane)  bulk-copy producer (cp.async.bulk, the TMA unit): the digit planes are
+//                      stored pre-tiled and pre-swizzled, [plane][row block][K block] of
+//                      128 rows x 128 bytes in the SWIZZLE_128B order, so one operand block is
+//                      one contiguous 16 KiB copy (full DRAM pages; a strided 128-row box was
+//                      latency bound, profiles/r01_syrk_i8.md) into a 4-stage shared-memory ring
 //   warp 1 (one lane)  tcgen05.mma kind::i8, M=128 N=256 K=32, accumulators in TMEM
 //                      (2 x 256 columns: the epilogue of unit u overlaps the MMAs of u+1)
 //   warps 2-5          epilogue: tcgen05.ld -> int32 -> FP64, scale, C += in global memory
 #include "common.cuh"
 #include "../../include/isdf_b200.h"
-#include <cuda.h>
 #include <cmath>
 #include <vector>
 #include <algorithm>
+#include <cstdlib>
 
 namespace {
 
@@ -73,10 +76,32 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
         if (clock64() - t0 > WAIT_LIMIT) __trap();          // never hang the device on a protocol bug
     }
 }
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2)
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar)
 {
-    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
-                 :: "r"(dst), "l"((uint64_t)map), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void bulk_load_mc(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint16_t mask)
+{
+    // the copy lands at the same shared-memory offset (and signals the same barrier offset) in every CTA of `mask`
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void tc_commit_mc(uint32_t bar, uint16_t mask)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 :: "r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_rank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -117,15 +142,22 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t saddr)
 constexpr uint32_t IDESC = (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 
 struct SyrkArgs {
-    const int2* tiles; int ntiles;     // (ti, tj): rows 128*ti.., cols 256*tj..
+    const int8_t* planes;              // [S][nrb][nkb_full] blocks of 128 rows x 128 bytes (swizzled)
+    long long plane_stride, rb_stride; // bytes
+    const int2* tiles; int ntiles;     // (gi, tj): a cluster of CL CTAs takes row tiles CL*gi + rank, cols 256*tj..
     int n, nkb, S;                     // matrix order, 128-byte K blocks in this chunk, digit planes
     double* C; long long ldc;
     const double* sc;                  // row scales 2^e_i of this chunk
     double alpha;
 };
 
-__global__ void __launch_bounds__(NTHREADS, 1)
-syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
+// CL = cluster size: the CL CTAs of a cluster own CL vertically adjacent 128x256 tiles; each
+// loads its own A block and 1/CL of the common B block, which is multicast to the whole cluster
+// (L2 -> SM traffic per tile 16 + 32/CL KiB per stage instead of 48 KiB, and the CTAs of a
+// cluster advance in lockstep).  A stage is refilled only after all CL CTAs released it.
+template <int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(NTHREADS, 1)
+syrk_i8_kernel(const SyrkArgs a)
 {
     extern __shared__ uint8_t smem_raw[];
     __shared__ uint64_t bar_full[NSTAGE], bar_empty[NSTAGE], bar_tfull[2], bar_tempty[2];
@@ -135,7 +167,7 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
     const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;     // SWIZZLE_128B tiles: 1024-byte aligned
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < NSTAGE; ++i) { mbar_init(smem_u32(&bar_full[i]), 1); mbar_init(smem_u32(&bar_empty[i]), 1); }
+        for (int i = 0; i < NSTAGE; ++i) { mbar_init(smem_u32(&bar_full[i]), 1); mbar_init(smem_u32(&bar_empty[i]), CL); }
         for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(&bar_tfull[i]), 1); mbar_init(smem_u32(&bar_tempty[i]), 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -147,27 +179,43 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
     }
     tc_fence_before();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();                                    // peers' barriers are initialised
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_s;
+    const int rank = CL > 1 ? (int)cluster_rank() : 0;
+    const int cid = blockIdx.x / CL, ncl = gridDim.x / CL;
+    constexpr uint16_t CMASK = (uint16_t)((1u << CL) - 1);
 
     if (warp == 0) {
         if (lane == 0) {
             // ===== TMA producer =====
             int st = 0; uint32_t ph = 0;
-            for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
+            for (int t = cid; t < a.ntiles; t += ncl) {
                 const int2 tl = a.tiles[t];
+                const int8_t* arow = a.planes + (long long)(tl.x * CL + rank) * a.rb_stride;
+                const int8_t* brow = a.planes + (long long)(2 * tl.y) * a.rb_stride;
                 for (int g = a.S - 1; g >= 0; --g)
-                    for (int s = 0; s <= g; ++s)
+                    for (int s = 0; s <= g; ++s) {
+                        const int8_t* pa = arow + (long long)s * a.plane_stride;
+                        const int8_t* pb = brow + (long long)(g - s) * a.plane_stride;
                         for (int kb = 0; kb < a.nkb; ++kb) {
-                            mbar_wait(smem_u32(&bar_empty[st]), ph ^ 1);
+                            mbar_wait(smem_u32(&bar_empty[st]), ph ^ 1);    // all CL CTAs are done with this stage
                             const uint32_t full = smem_u32(&bar_full[st]);
                             const uint32_t sa = smem0 + st * STAGE_BYTES, sb = sa + A_BYTES;
                             mbar_expect_tx(full, STAGE_BYTES);
-                            tma_load_3d(sa, &tmap, full, kb * BKB, tl.x * TM, s);
-                            tma_load_3d(sb, &tmap, full, kb * BKB, tl.y * TN, g - s);
-                            tma_load_3d(sb + A_BYTES, &tmap, full, kb * BKB, tl.y * TN + 128, g - s);
+                            bulk_load(sa, pa + (long long)kb * A_BYTES, A_BYTES, full);
+                            if (CL == 1) {
+                                bulk_load(sb, pb + (long long)kb * A_BYTES, A_BYTES, full);
+                                bulk_load(sb + A_BYTES, pb + a.rb_stride + (long long)kb * A_BYTES, A_BYTES, full);
+                            } else {
+                                constexpr int PB = B_BYTES / CL;            // this CTA's share of the B tile
+                                const int off = rank * PB;
+                                bulk_load_mc(sb + off, pb + (long long)(off / A_BYTES) * a.rb_stride +
+                                             (long long)kb * A_BYTES + (off % A_BYTES), PB, full, CMASK);
+                            }
                             if (++st == NSTAGE) { st = 0; ph ^= 1; }
                         }
+                    }
             }
         }
     } else if (warp == 1) {
@@ -175,7 +223,7 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
             // ===== MMA issuer =====
             int st = 0; uint32_t ph = 0;
             uint32_t unit = 0;
-            for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x)
+            for (int t = cid; t < a.ntiles; t += ncl)
                 for (int g = a.S - 1; g >= 0; --g, ++unit) {
                     const uint32_t buf = unit & 1, bph = (unit >> 1) & 1;
                     mbar_wait(smem_u32(&bar_tempty[buf]), bph ^ 1);     // epilogue has drained this accumulator
@@ -190,7 +238,9 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
                         for (int k = 0; k < BKB / UK; ++k)
                             tc_mma_i8(tmem_d, umma_desc_k128(sa + k * UK), umma_desc_k128(sb + k * UK), IDESC,
                                       (it | k) != 0);
-                        tc_commit(smem_u32(&bar_empty[st]));            // frees the stage when these MMAs retire
+                        // frees the stage (in every CTA of the cluster) when these MMAs retire
+                        if (CL == 1) tc_commit(smem_u32(&bar_empty[st]));
+                        else tc_commit_mc(smem_u32(&bar_empty[st]), CMASK);
                         if (++st == NSTAGE) { st = 0; ph ^= 1; }
                     }
                     tc_commit(smem_u32(&bar_tfull[buf]));               // accumulator complete
@@ -199,10 +249,11 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
     } else {
         // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
         const int q = warp & 3;
+        const bool vec2 = (a.ldc % 2 == 0) && ((uintptr_t)a.C % 16 == 0);
         uint32_t unit = 0;
-        for (int t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
+        for (int t = cid; t < a.ntiles; t += ncl) {
             const int2 tl = a.tiles[t];
-            const int row = tl.x * TM + q * 32 + lane;
+            const int row = (tl.x * CL + rank) * TM + q * 32 + lane;
             const double srow = row < a.n ? a.sc[row] : 0.0;
             double* crow = a.C + (long long)row * a.ldc;
             for (int g = a.S - 1; g >= 0; --g, ++unit) {
@@ -220,11 +271,34 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
                         if (lane == 0) mbar_arrive(smem_u32(&bar_tempty[buf]));
                     }
                     const int col0 = tl.y * TN + cc * 32;
-                    if (row < a.n && col0 + 31 >= row) {
+                    if (row < a.n && col0 + 31 >= row && col0 < a.n) {
+                        if (col0 >= row && col0 + 32 <= a.n) {
+                            // interior chunk: all 32 loads in flight before the first use
+                            double c[32];
+                            if (vec2) {
+                                const double2* p2 = reinterpret_cast<const double2*>(crow + col0);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const int col = col0 + j;
-                            if (col < a.n && col >= row) crow[col] += (double)v[j] * (f * a.sc[col]);
+                                for (int j = 0; j < 16; ++j) { const double2 t2 = p2[j]; c[2 * j] = t2.x; c[2 * j + 1] = t2.y; }
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) c[j] = crow[col0 + j];
+                            }
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) c[j] += (double)v[j] * (f * a.sc[col0 + j]);
+                            if (vec2) {
+                                double2* p2 = reinterpret_cast<double2*>(crow + col0);
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) p2[j] = make_double2(c[2 * j], c[2 * j + 1]);
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < 32; ++j) crow[col0 + j] = c[j];
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const int col = col0 + j;
+                                if (col < a.n && col >= row) crow[col] += (double)v[j] * (f * a.sc[col]);
+                            }
                         }
                     }
                 }
@@ -233,6 +307,7 @@ syrk_i8_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkArgs a)
     }
     tc_fence_before();
     __syncthreads();
+    if (CL > 1) cluster_sync_all();            // no CTA exits while a peer may still signal its barriers
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(512) : "memory");
@@ -262,21 +337,30 @@ __global__ void i8_rowscale_kernel(const double* __restrict__ A, long long lda, 
     }
 }
 
-// planes[s][i][k] = s-th signed 7-bit digit of A[i, k0+k] / sc[i]; 16 consecutive k per thread
-__global__ void i8_split_kernel(const double* __restrict__ A, long long lda, int n, long long k0, int kc, int kcpad,
-                                const double* __restrict__ sc, int8_t* __restrict__ planes,
-                                long long row_stride, long long plane_stride, int S)
+// s-th signed 7-bit digit of A[i, k0+k] / sc[i], 16 consecutive k per thread, stored in the
+// pre-tiled SWIZZLE_128B order: block (i / 128, k / 128) is 16 KiB contiguous, row r of a block
+// at r * 128 bytes, its 16-byte chunk c at position c ^ (r & 7).  Rows >= n (padding up to a
+// multiple of 256) and columns >= kc are written as zeros.
+__global__ void i8_split_kernel(const double* __restrict__ A, long long lda, int n, int nrows_pad, long long k0,
+                                int kc, int kcpad, const double* __restrict__ sc, int8_t* __restrict__ planes,
+                                long long rb_stride, long long plane_stride, int S)
 {
     const int groups = kcpad / 16;
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)n * groups) return;
+    if (idx >= (long long)nrows_pad * groups) return;
     const int i = (int)(idx / groups), kg = (int)(idx - (long long)i * groups) * 16;
-    const double inv = 1.0 / sc[i];                     // exact: a power of two
-    const double* src = A + (long long)i * lda + k0 + kg;
     double x[16];
+    if (i < n) {
+        const double inv = 1.0 / sc[i];                 // exact: a power of two
+        const double* src = A + (long long)i * lda + k0 + kg;
 #pragma unroll
-    for (int j = 0; j < 16; ++j) x[j] = (kg + j < kc) ? src[j] * inv : 0.0;
-    int8_t* dst = planes + (long long)i * row_stride + kg;
+        for (int j = 0; j < 16; ++j) x[j] = (kg + j < kc) ? src[j] * inv : 0.0;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) x[j] = 0.0;
+    }
+    const int r = i & 127, c = (kg & 127) >> 4;
+    int8_t* dst = planes + (long long)(i >> 7) * rb_stride + (long long)(kg >> 7) * A_BYTES + r * 128 + ((c ^ (r & 7)) << 4);
     for (int s = 0; s < S; ++s) {
         const double mult = s == 0 ? 64.0 : 128.0;
         uint32_t w[4] = {0, 0, 0, 0};
@@ -291,23 +375,6 @@ __global__ void i8_split_kernel(const double* __restrict__ A, long long lda, int
     }
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn get_encode_fn()
-{
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult qres;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
-            qres == cudaDriverEntryPointSuccess)
-            fn = (EncodeTiledFn)p;
-    }
-    return fn;
-}
-
 struct Chunks { int nchunks, kc_full; };
 
 Chunks plan_chunks(long long K)
@@ -319,15 +386,54 @@ Chunks plan_chunks(long long K)
     return c;
 }
 
+
+int cluster_size()
+{
+    static int cl = 0;
+    if (!cl) {
+        const char* e = getenv("ISDF_SYRK_CLUSTER");          // tuning knob: 1, 2, 4 or 8 CTAs per cluster
+        cl = e ? atoi(e) : 4;
+        if (cl != 1 && cl != 2 && cl != 4 && cl != 8) cl = 4;
+    }
+    return cl;
+}
+
+int rows_padded(int n, int cl) { return (int)align_up((size_t)n, (size_t)std::max(TN, TM * cl)); }
+
+template <int CL>
+int launch_syrk(isdf_handle* h, const SyrkArgs& a, int& nclusters)
+{
+    auto kern = syrk_i8_kernel<CL>;
+    if (nclusters == 0) {
+        CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        int fit = h->num_sms / CL;
+        if (CL > 1) {                                          // how many clusters are co-resident on this GPU
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(h->num_sms / CL * CL); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = SMEM_BYTES;
+            cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension;
+            at.val.clusterDim.x = CL; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+            cfg.attrs = &at; cfg.numAttrs = 1;
+            int nmax = 0;
+            if (cudaOccupancyMaxActiveClusters(&nmax, kern, &cfg) == cudaSuccess && nmax > 0) fit = std::min(fit, nmax);
+            else (void)cudaGetLastError();
+        }
+        nclusters = std::max(1, std::min(fit, a.ntiles));
+    }
+    kern<<<nclusters * CL, NTHREADS, SMEM_BYTES, h->stream>>>(a);
+    return ISDF_OK;
+}
+
 }  // namespace
 
 extern "C" size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices)
 {
     if (n <= 0 || K <= 0 || nslices <= 0) return 0;
     const Chunks c = plan_chunks(K);
+    const int cl = cluster_size();
     const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
-    return align_up((size_t)nslices * n * c.kc_full, 256) + align_up((size_t)n * sizeof(double), 256) +
-           align_up((size_t)tr * tc * sizeof(int2), 256) + 1024;
+    return align_up((size_t)nslices * (size_t)rows_padded(n, cl) * ((c.kc_full / BKB | 1) * BKB), 1024) +
+           align_up((size_t)n * sizeof(double), 256) +
+           align_up((size_t)tr * tc * sizeof(int2), 256) + 2048;
 }
 
 extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A, long long lda,
@@ -336,62 +442,61 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     ARG_CHECK(h && A && C && ws);
     ARG_CHECK(n > 0 && K > 0 && lda >= K && ldc >= n);
     ARG_CHECK(nslices >= 2 && nslices <= S_MAX);
-    ARG_CHECK(((uintptr_t)A % 16) == 0 && lda % 2 == 0);
     if (ws_bytes < isdf_syrk_i8_ws_bytes(n, K, nslices)) {
         isdf_set_error("isdf_syrk_i8: workspace too small");
         return ISDF_ERR_WS;
     }
-    EncodeTiledFn encode = get_encode_fn();
-    if (!encode) {
-        isdf_set_error("isdf_syrk_i8: cuTensorMapEncodeTiled not available from the driver");
-        return ISDF_ERR_CUDA;
-    }
     const Chunks ch = plan_chunks(K);
-    WsAlloc w(ws, ws_bytes);
-    int8_t* planes = w.get<int8_t>((size_t)nslices * n * ch.kc_full);
-    double* sc = w.get<double>(n);
+    const int cl = cluster_size();
     const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
-    int2* d_tiles = w.get<int2>((size_t)tr * tc);
+    const int nrows_pad = rows_padded(n, cl);              // whole 256-row B tiles and whole clusters of row tiles
+    // an odd number of 16 KiB blocks per row block: a power-of-two stride would map the ~30 row and
+    // column blocks that are live at the same K offset onto the same L2 sets
+    const long long rb_stride = (long long)(ch.kc_full / BKB | 1) * A_BYTES;
+    const long long plane_stride = rb_stride * (nrows_pad / TM);
+    char* base = (char*)align_up((size_t)ws, 1024);
+    int8_t* planes = (int8_t*)base;
+    base += align_up((size_t)nslices * plane_stride, 1024);
+    double* sc = (double*)base;
+    base += align_up((size_t)n * sizeof(double), 256);
+    int2* d_tiles = (int2*)base;
 
-    // persistent schedule: strips of STRIP tile columns, rows ascending inside a strip, so that the
-    // ~148 tiles in flight share few distinct row/column blocks (L2 reuse of the digit planes)
+    // persistent schedule: strips of STRIP tile columns, row groups ascending inside a strip, so that
+    // the tiles in flight share few distinct row/column blocks (L2 reuse of the digit planes)
     std::vector<int2> tiles;
+    const int ngr = (tr + cl - 1) / cl;
     for (int s0 = 0; s0 < tc; s0 += STRIP)
-        for (int ti = 0; ti < tr; ++ti)
+        for (int gi = 0; gi < ngr; ++gi)
             for (int tj = s0; tj < std::min(tc, s0 + STRIP); ++tj)
-                if (ti <= 2 * tj + 1) tiles.push_back(make_int2(ti, tj));
+                if (gi * cl <= 2 * tj + 1) tiles.push_back(make_int2(gi, tj));
     const int ntiles = (int)tiles.size();
     CUDA_TRY(cudaMemcpyAsync(d_tiles, tiles.data(), ntiles * sizeof(int2), cudaMemcpyHostToDevice, h->stream));
     CUDA_TRY(cudaStreamSynchronize(h->stream));          // `tiles` is pageable host memory
 
-    CUtensorMap tmap;
-    const cuuint64_t gdim[3] = {(cuuint64_t)ch.kc_full, (cuuint64_t)n, (cuuint64_t)nslices};
-    const cuuint64_t gstride[2] = {(cuuint64_t)ch.kc_full, (cuuint64_t)ch.kc_full * (cuuint64_t)n};
-    const cuuint32_t box[3] = {BKB, 128, 1};
-    const cuuint32_t estr[3] = {1, 1, 1};
-    const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, planes, gdim, gstride, box, estr,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (cr != CUDA_SUCCESS) {
-        isdf_set_error("isdf_syrk_i8: cuTensorMapEncodeTiled failed (%d)", (int)cr);
-        return ISDF_ERR_CUDA;
-    }
-    CUDA_TRY(cudaFuncSetAttribute(syrk_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     CUDA_TRY(cudaMemset2DAsync(C, ldc * sizeof(double), 0, (size_t)n * sizeof(double), n, h->stream));
 
+    int nclusters = 0;
     for (int c = 0; c < ch.nchunks; ++c) {
         const long long k0 = (long long)c * ch.kc_full;
         if (k0 >= K) break;
         const int kc = (int)std::min<long long>(ch.kc_full, K - k0);
         const int kcpad = (int)align_up((size_t)kc, BKB);
         i8_rowscale_kernel<<<n, 256, 0, h->stream>>>(A, lda, k0, kc, sc);
-        const long long items = (long long)n * (kcpad / 16);
+        const long long items = (long long)nrows_pad * (kcpad / 16);
         i8_split_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(
-            A, lda, n, k0, kc, kcpad, sc, planes, ch.kc_full, (long long)ch.kc_full * n, nslices);
+            A, lda, n, nrows_pad, k0, kc, kcpad, sc, planes, rb_stride, plane_stride, nslices);
         SyrkArgs a;
+        a.planes = planes; a.plane_stride = plane_stride; a.rb_stride = rb_stride;
         a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = kcpad / BKB; a.S = nslices;
         a.C = C; a.ldc = ldc; a.sc = sc; a.alpha = alpha;
-        syrk_i8_kernel<<<std::min(h->num_sms, ntiles), NTHREADS, SMEM_BYTES, h->stream>>>(tmap, a);
+        int rc;
+        switch (cl) {
+        case 1: rc = launch_syrk<1>(h, a, nclusters); break;
+        case 2: rc = launch_syrk<2>(h, a, nclusters); break;
+        case 8: rc = launch_syrk<8>(h, a, nclusters); break;
+        default: rc = launch_syrk<4>(h, a, nclusters); break;
+        }
+        if (rc != ISDF_OK) return rc;
         h->other_launches += 3;
     }
     CUDA_TRY(cudaGetLastError());

@@ -89,3 +89,22 @@ def test_isdf_matches_committed_golden_fixture():
         assert abs(W[:16, :16] - z['W_block']).max() < 1e-8
         vj, vk = mydf.get_jk(rand_dm(cell.nao))
         assert abs(vj - z['vj']).max() < 1e-8 and abs(vk - z['vk']).max() < 1e-8
+
+
+@pytest.mark.parametrize('wgemm', ['i8', 'i8:7'])
+def test_isdf_int8_coulomb_metric(wgemm):
+    """W through the int8 tensor-core split product (csrc/syrk_i8.cu): same pivots, W equal to the
+    FP64-GEMM route to ~1e-13 relative, J/K within the 1e-8 north_star tolerance of the CPU oracle."""
+    cell = diamond_c8([14, 14, 14], basis='gth-dzvp', jitter=0.15)
+    dm = rand_dm(cell.nao)
+    ref = ISDF(cell, c=6, fit='implicit')
+    vj0, vk0 = ref.get_jk(dm, exxdiv=None)
+    mydf = ISDF(cell, c=6, fit='implicit', wgemm=wgemm)
+    vj, vk = mydf.get_jk(dm, exxdiv=None)
+    assert np.array_equal(mydf.ip_index, ref.ip_index)
+    W0, W1 = ref.W.cpu().numpy(), mydf.W.cpu().numpy()
+    assert abs(W1 - W0).max() < (1e-12 if wgemm == 'i8' else 1e-10) * abs(W0).max()
+    assert abs(vj - vj0).max() < 1e-10 and abs(vk - vk0).max() < 1e-10
+    orc = oracle.isdf_build(oracle_phi(cell), cell.lattice_vectors(), cell.mesh, 6 * cell.nao)
+    vjo, vko = oracle.isdf_get_jk(orc['X'], orc['W'], dm)
+    assert abs(vj - vjo).max() < 1e-8 and abs(vk - vko).max() < 1e-8
