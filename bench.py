@@ -37,7 +37,7 @@ def parse_args():
     ap.add_argument('--workload', default=None, help='c8 | c64 | h2o32 | si216 | c8-small')
     ap.add_argument('--c', type=float, default=15.0, help='ISDF rank parameter: N_IP = c * nao')
     ap.add_argument('--fit', default='implicit', choices=['implicit', 'pivot_factor', 'cholesky'])
-    ap.add_argument('--wgemm', default='fp64',
+    ap.add_argument('--wgemm', default='i8',
                     help="Coulomb-metric product Y Y^T: 'fp64' (FP64 tensor pipe) or 'i8[:planes]' "
                          "(int8 tcgen05 split product, 8 digit planes = FP64-GEMM accuracy)")
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -364,9 +364,9 @@ def run_b200(args):
     }
     if args.wgemm.startswith('i8') and stages_ms.get('wgemm_ms'):
         planes = int(args.wgemm.split(':')[1]) if ':' in args.wgemm else 8
-        ops = planes * (planes + 1) / 2.0 * fm['coulomb_gemm'] / world      # int8 ops of this rank's digit products
-        line['wgemm_i8'] = {'kernel': 'syrk_i8_kernel (tcgen05 kind::i8, TMEM accumulators, bulk-copy ring)',
-                            'planes': planes, 'int8_ops_per_rank': ops, 'ms': stages_ms['wgemm_ms'],
+        ops = float(getattr(h, 'syrk_i8_ops', 0.0))         # int8 ops issued by this rank's last W product
+        line['wgemm_i8'] = {'kernel': 'syrk_i8_kernel (tcgen05 kind::i8, TMEM accumulators, bulk-copy ring, cluster multicast)',
+                            'max_planes': planes, 'int8_ops_per_rank': ops, 'ms': stages_ms['wgemm_ms'],
                             'achieved_pops': ops / (stages_ms['wgemm_ms'] * 1e-3) / 1e15,
                             'fp64_equivalent_tflops': fm['coulomb_gemm'] / world / (stages_ms['wgemm_ms'] * 1e-3) / 1e12}
     if world == 1 and not args.no_cpu_baseline:

@@ -152,13 +152,17 @@ int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nvec,
                        const int* h_mesh, const double* h_a, int col0, int ncl);
 int isdf_symmetrize_upper(isdf_handle* h, double* W, long long ld, int n);
 
-/* Upper triangle of C[n,n] = alpha * A A^T (A [n,K] row-major FP64, 16-byte aligned, lda even)
+/* Upper triangle of C[n,n] = alpha * A A^T (A [n,K] row-major FP64)
  * computed on the int8 tensor cores (tcgen05 kind::i8, exact int32 accumulation) from
- * `nslices` signed 7-bit digit planes per row-scaled entry (error-free splitting; 8 planes
- * reproduce FP64-GEMM accuracy, see csrc/syrk_i8.cu).  Replaces the FP64 isdf_dgemm call of
+ * at most `nslices` signed 7-bit digit planes per row-scaled entry (error-free splitting; 8
+ * planes reproduce FP64-GEMM accuracy; K chunks that are small against the whole rows take
+ * fewer planes for the same normwise accuracy 2^-(7 nslices - 6), see csrc/syrk_i8.cu).  Replaces the FP64 isdf_dgemm call of
  * the W build [spec; the exact-FFTDF analogue is the einsum of
  * pyscf/pbc/df/fft_jk.py:93-94]; follow with isdf_symmetrize_upper. */
 size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices);
+/* int8 operations (2 per multiply-add, all tiles and digit products) issued by the last
+ * isdf_syrk_i8 call of this process: the numerator of its roofline figure in bench.py. */
+double isdf_syrk_i8_last_ops(void);
 int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A, long long lda,
                  double* C, long long ldc, double alpha, int nslices, void* ws, size_t ws_bytes);
 

@@ -52,6 +52,7 @@ SIGNATURES = {
     'isdf_fft_x_coulomb': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_vp, c_int, c_int]),
     'isdf_symmetrize_upper': (c_int, [c_vp, c_vp, c_ll, c_int]),
     'isdf_syrk_i8_ws_bytes': (c_sz, [c_int, c_ll, c_int]),
+    'isdf_syrk_i8_last_ops': (c_dbl, []),
     'isdf_syrk_i8': (c_int, [c_vp, c_int, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_vp, c_sz]),
     'isdf_get_jk_block_ws_bytes': (c_sz, [c_int, c_int, c_int]),
     'isdf_get_jk_block': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_int, c_int, c_int,
@@ -325,6 +326,7 @@ class Handle:
         ws = self.workspace(nbytes)
         check(self.lib.isdf_syrk_i8(self.h, n, K, c_vp(A.data_ptr()), lda, c_vp(C.data_ptr()), ldc,
                                     float(alpha), int(nslices), c_vp(ws.data_ptr()), nbytes))
+        self.syrk_i8_ops = float(self.lib.isdf_syrk_i8_last_ops())
         return ws
 
     def get_jk_block(self, X, Wrows, ldw, p0, npl, dm, nset, nao, npts, with_j, with_k, vj, vk, ws=None):

@@ -315,25 +315,63 @@ syrk_i8_kernel(const SyrkArgs a)
 }
 
 // ---- digit planes -----------------------------------------------------------------
-// sc[i] = 2^e with max_k |A[i, k0:k0+kc]| = m * 2^e, m in [0.5, 1)
-__global__ void i8_rowscale_kernel(const double* __restrict__ A, long long lda, long long k0, int kc,
-                                   double* __restrict__ sc)
+// Row statistics, one CTA per row: sc[c][i] = 2^e with max_k |A[i, chunk c]| = m * 2^e,
+// m in [0.5, 1), and nrm[i] = ||A[i, :]||_2.
+__global__ void i8_rowstats_kernel(const double* __restrict__ A, long long lda, long long K, int kc_full, int nchunks,
+                                   int n, double* __restrict__ sc, double* __restrict__ nrm)
 {
-    const double* row = A + (long long)blockIdx.x * lda + k0;
+    const int i = blockIdx.x;
+    const double* row = A + (long long)i * lda;
+    __shared__ double red[32];
+    double ssq = 0.0;
+    for (int c = 0; c < nchunks; ++c) {
+        const long long k0 = (long long)c * kc_full;
+        const int kc = (int)min((long long)kc_full, K - k0);
+        double m = 0.0;
+        for (int k = threadIdx.x; k < kc; k += blockDim.x) {
+            const double v = row[k0 + k];
+            m = fmax(m, fabs(v));
+            ssq = fma(v, v, ssq);
+        }
+        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+            for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+            if (threadIdx.x == 0) {
+                int e = 0;
+                if (m > 0.0) frexp(m, &e);
+                sc[(long long)c * n + i] = ldexp(1.0, e);
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) ssq += __shfl_xor_sync(0xffffffffu, ssq, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ssq;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        nrm[i] = sqrt(t);
+    }
+}
+
+// rho[c] = max_i sc[c][i] / nrm[i]: how large chunk c is relative to the whole rows (one CTA per chunk)
+__global__ void i8_rho_kernel(const double* __restrict__ sc, const double* __restrict__ nrm, int n, double* __restrict__ rho)
+{
+    const double* s = sc + (long long)blockIdx.x * n;
     double m = 0.0;
-    for (int k = threadIdx.x; k < kc; k += blockDim.x) m = fmax(m, fabs(row[k]));
+    for (int i = threadIdx.x; i < n; i += blockDim.x)
+        if (nrm[i] > 0.0) m = fmax(m, s[i] / nrm[i]);
     __shared__ double red[32];
     for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
     __syncthreads();
-    if (threadIdx.x < 32) {
-        m = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
-        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
-        if (threadIdx.x == 0) {
-            int e = 0;
-            if (m > 0.0) frexp(m, &e);
-            sc[blockIdx.x] = ldexp(1.0, e);
-        }
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) m = fmax(m, red[w]);
+        rho[blockIdx.x] = fmax(m, red[0]);
     }
 }
 
@@ -387,6 +425,8 @@ Chunks plan_chunks(long long K)
 }
 
 
+double g_last_ops = 0.0;      // int8 operations (2 per multiply-add) issued by the last isdf_syrk_i8 call
+
 int cluster_size()
 {
     static int cl = 0;
@@ -425,6 +465,8 @@ int launch_syrk(isdf_handle* h, const SyrkArgs& a, int& nclusters)
 
 }  // namespace
 
+extern "C" double isdf_syrk_i8_last_ops(void) { return g_last_ops; }
+
 extern "C" size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices)
 {
     if (n <= 0 || K <= 0 || nslices <= 0) return 0;
@@ -432,7 +474,7 @@ extern "C" size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices)
     const int cl = cluster_size();
     const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
     return align_up((size_t)nslices * (size_t)rows_padded(n, cl) * ((c.kc_full / BKB | 1) * BKB), 1024) +
-           align_up((size_t)n * sizeof(double), 256) +
+           align_up((size_t)(c.nchunks + 1) * n * sizeof(double), 256) + align_up((size_t)c.nchunks * sizeof(double), 256) +
            align_up((size_t)tr * tc * sizeof(int2), 256) + 2048;
 }
 
@@ -457,8 +499,11 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     char* base = (char*)align_up((size_t)ws, 1024);
     int8_t* planes = (int8_t*)base;
     base += align_up((size_t)nslices * plane_stride, 1024);
-    double* sc = (double*)base;
-    base += align_up((size_t)n * sizeof(double), 256);
+    double* sc_all = (double*)base;                        // [nchunks][n] row scales, then [n] row norms
+    double* nrm = sc_all + (size_t)ch.nchunks * n;
+    base += align_up((size_t)(ch.nchunks + 1) * n * sizeof(double), 256);
+    double* d_rho = (double*)base;
+    base += align_up((size_t)ch.nchunks * sizeof(double), 256);
     int2* d_tiles = (int2*)base;
 
     // persistent schedule: strips of STRIP tile columns, row groups ascending inside a strip, so that
@@ -471,23 +516,53 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
                 if (gi * cl <= 2 * tj + 1) tiles.push_back(make_int2(gi, tj));
     const int ntiles = (int)tiles.size();
     CUDA_TRY(cudaMemcpyAsync(d_tiles, tiles.data(), ntiles * sizeof(int2), cudaMemcpyHostToDevice, h->stream));
-    CUDA_TRY(cudaStreamSynchronize(h->stream));          // `tiles` is pageable host memory
+
+    // Digit planes per chunk.  A chunk whose entries are small against the whole rows needs fewer
+    // planes for the same normwise accuracy: the error of chunk c in C[i,j] is about
+    // sqrt(kc) (S+3) 2^(-7S) sc_i sc_j, to be kept below 2^-T |a_i| |a_j| with T = 7 nslices - 6
+    // (nslices = 8: T = 50, the accuracy of an FP64 GEMM over this K).  The weighted spectra of
+    // the W build decay with |G|, so the high-frequency chunks take 2-4 planes less.
+    ARG_CHECK(ch.nchunks * sizeof(double) <= 65536);
+    i8_rowstats_kernel<<<n, 256, 0, h->stream>>>(A, lda, K, ch.kc_full, ch.nchunks, n, sc_all, nrm);
+    i8_rho_kernel<<<ch.nchunks, 256, 0, h->stream>>>(sc_all, nrm, n, d_rho);
+    double* h_rho = (double*)h->h_pinned;
+    CUDA_TRY(cudaMemcpyAsync(h_rho, d_rho, ch.nchunks * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));          // also covers `tiles` (pageable host memory)
+    h->other_launches += 2;
+    std::vector<int> planes_of(ch.nchunks, 0);
+    const double T = 7.0 * nslices - 6.0;
+    for (int c = 0; c < ch.nchunks; ++c) {
+        const long long k0 = (long long)c * ch.kc_full;
+        if (k0 >= K || !(h_rho[c] > 0.0)) continue;
+        const double kc = (double)std::min<long long>(ch.kc_full, K - k0);
+        int S = 0;
+        while (S < nslices && 7.0 * S < T + 0.5 * std::log2(kc) + std::log2(S + 3.0) + 2.0 * std::log2(h_rho[c])) ++S;
+        planes_of[c] = S;
+    }
 
     CUDA_TRY(cudaMemset2DAsync(C, ldc * sizeof(double), 0, (size_t)n * sizeof(double), n, h->stream));
 
+    if (getenv("ISDF_SYRK_VERBOSE")) {
+        fprintf(stderr, "isdf_syrk_i8: n=%d K=%lld chunks=%d x %d, planes per chunk:", n, K, ch.nchunks, ch.kc_full);
+        for (int c = 0; c < ch.nchunks; ++c) fprintf(stderr, " %d", planes_of[c]);
+        fprintf(stderr, "\n");
+    }
+    g_last_ops = 0.0;
     int nclusters = 0;
     for (int c = 0; c < ch.nchunks; ++c) {
         const long long k0 = (long long)c * ch.kc_full;
         if (k0 >= K) break;
         const int kc = (int)std::min<long long>(ch.kc_full, K - k0);
         const int kcpad = (int)align_up((size_t)kc, BKB);
-        i8_rowscale_kernel<<<n, 256, 0, h->stream>>>(A, lda, k0, kc, sc);
+        const int S = planes_of[c];
+        if (S == 0) continue;                              // below the accuracy target altogether
+        const double* sc = sc_all + (size_t)c * n;
         const long long items = (long long)nrows_pad * (kcpad / 16);
         i8_split_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(
-            A, lda, n, nrows_pad, k0, kc, kcpad, sc, planes, rb_stride, plane_stride, nslices);
+            A, lda, n, nrows_pad, k0, kc, kcpad, sc, planes, rb_stride, plane_stride, S);
         SyrkArgs a;
         a.planes = planes; a.plane_stride = plane_stride; a.rb_stride = rb_stride;
-        a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = kcpad / BKB; a.S = nslices;
+        a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = kcpad / BKB; a.S = S;
         a.C = C; a.ldc = ldc; a.sc = sc; a.alpha = alpha;
         int rc;
         switch (cl) {
@@ -497,7 +572,8 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
         default: rc = launch_syrk<4>(h, a, nclusters); break;
         }
         if (rc != ISDF_OK) return rc;
-        h->other_launches += 3;
+        g_last_ops += 2.0 * (S * (S + 1) / 2) * (double)ntiles * cl * TM * TN * (double)kcpad;
+        h->other_launches += 2;
     }
     CUDA_TRY(cudaGetLastError());
     return ISDF_OK;

@@ -263,7 +263,7 @@ def build(mydf, comm, ops=None):
     ev.mark('fft_ms')
     W = ops.empty((npts, npts))
     Yr = ops.as_real(Y)
-    wmode = str(getattr(mydf, 'wgemm', 'fp64'))
+    wmode = str(getattr(mydf, 'wgemm', 'i8'))
     if wmode.startswith('i8'):
         planes = int(wmode.split(':')[1]) if ':' in wmode else 8
         ops.syrk_i8(npts, 2 * nx * ncl, Yr, 2 * ldy, W, npts,

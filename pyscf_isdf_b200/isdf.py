@@ -33,7 +33,7 @@ class ISDF:
              'keep_aoR', 'timings', 'comm', 'wgemm'}
 
     def __init__(self, cell, kpts=np.zeros((1, 3)), c=15, n_ip=None, select='cholesky',
-                 fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None, wgemm='fp64'):
+                 fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None, wgemm='i8'):
         self.cell = cell
         self.stdout = sys.stdout
         self.verbose = getattr(cell, 'verbose', 0)
@@ -46,8 +46,8 @@ class ISDF:
         self.tol = tol
         self.exxdiv = None
         self.keep_aoR = keep_aoR
-        # wgemm: how the Coulomb-metric product Y Y^T is computed: 'fp64' (FP64 tensor pipe) or
-        # 'i8' / 'i8:<planes>' (int8 tcgen05 split product, csrc/syrk_i8.cu; 8 planes by default)
+        # wgemm: how the Coulomb-metric product Y Y^T is computed: 'i8' / 'i8:<planes>' (int8 tcgen05
+        # split product, csrc/syrk_i8.cu; 8 digit planes = FP64-GEMM accuracy) or 'fp64' (FP64 tensor pipe)
         self.wgemm = wgemm
         self._device = device
         self._handle = None

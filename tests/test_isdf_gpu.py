@@ -97,7 +97,7 @@ def test_isdf_int8_coulomb_metric(wgemm):
     FP64-GEMM route to ~1e-13 relative, J/K within the 1e-8 north_star tolerance of the CPU oracle."""
     cell = diamond_c8([14, 14, 14], basis='gth-dzvp', jitter=0.15)
     dm = rand_dm(cell.nao)
-    ref = ISDF(cell, c=6, fit='implicit')
+    ref = ISDF(cell, c=6, fit='implicit', wgemm='fp64')
     vj0, vk0 = ref.get_jk(dm, exxdiv=None)
     mydf = ISDF(cell, c=6, fit='implicit', wgemm=wgemm)
     vj, vk = mydf.get_jk(dm, exxdiv=None)
