@@ -306,6 +306,9 @@ __device__ __forceinline__ double coulG_at(const CoulGeom& g, int ix, int iy, in
 }
 
 // ---- z pass: real lines -> half spectrum ------------------------------------
+// Two real lines share one complex transform: z = x_even + i x_odd, then
+// X_even[k] = (Z[k] + conj Z[n-k]) / 2 and X_odd[k] = -i (Z[k] - conj Z[n-k]) / 2.
+// LB = complex (paired) lines per CTA, i.e. 2 LB real lines.
 __global__ void __launch_bounds__(FFT_THREADS)
 fft_z_r2c_kernel(const double* __restrict__ in, long long ldin, double2* __restrict__ out, long long ldout,
                  FftPlan pl, int nlines, int LB)
@@ -313,19 +316,28 @@ fft_z_r2c_kernel(const double* __restrict__ in, long long ldin, double2* __restr
     extern __shared__ double2 sm[];
     const int nz = pl.n(), nzh = nz / 2 + 1, LS = pl.lalloc();
     double2* a = sm; double2* b = sm + LB * LS;
-    const int line0 = blockIdx.x * LB;
-    const int nl = min(LB, nlines - line0);
+    const int line0 = blockIdx.x * 2 * LB;
+    const int nl = min(2 * LB, nlines - line0);          // real lines of this CTA
+    const int np = (nl + 1) >> 1;                        // complex lines
     const double* src = in + (long long)blockIdx.y * ldin + (long long)line0 * nz;
-    for (int idx = threadIdx.x; idx < nl * nz; idx += blockDim.x) {
-        const int line = idx / nz, e = idx - line * nz;
-        a[line * LS + e] = make_double2(src[idx], 0.0);
+    const float inv_nz = 1.0f / (float)nz, inv_nzh = 1.0f / (float)nzh;
+    for (int idx = threadIdx.x; idx < np * nz; idx += blockDim.x) {
+        const int p = fast_div(idx, nz, inv_nz), e = idx - p * nz;
+        const double re = src[(long long)(2 * p) * nz + e];
+        const double im = (2 * p + 1 < nl) ? src[(long long)(2 * p + 1) * nz + e] : 0.0;
+        a[p * LS + e] = make_double2(re, im);
     }
     __syncthreads();
-    double2* r = fft_smem<-1>(a, b, pl, nl, LS, 1, false);
+    double2* r = fft_smem<-1>(a, b, pl, np, LS, 1, false);
     double2* dst = out + (long long)blockIdx.y * ldout + (long long)line0 * nzh;
     for (int idx = threadIdx.x; idx < nl * nzh; idx += blockDim.x) {
-        const int line = idx / nzh, e = idx - line * nzh;
-        dst[idx] = r[line * LS + e];
+        const int line = fast_div(idx, nzh, inv_nzh), e = idx - line * nzh;
+        const double2* rp = r + (line >> 1) * LS;
+        const double2 zk = rp[e];
+        double2 zc = rp[e ? nz - e : 0];
+        zc.y = -zc.y;
+        dst[idx] = (line & 1) ? make_double2(0.5 * (zk.y - zc.y), -0.5 * (zk.x - zc.x))
+                              : make_double2(0.5 * (zk.x + zc.x), 0.5 * (zk.y + zc.y));
     }
 }
 
@@ -371,8 +383,9 @@ fft_cols_kernel(double2* __restrict__ data, long long vec_stride, long long oute
     const int c0 = blockIdx.x * CH;
     const int nc = min(CH, ncols - c0);
     double2* base = data + (long long)blockIdx.z * vec_stride + (long long)blockIdx.y * outer_stride + c0;
+    const float inv_nc = 1.0f / (float)nc, inv_nzh = 1.0f / (float)geo.nzh;
     for (int idx = threadIdx.x; idx < n * nc; idx += blockDim.x) {
-        const int i = idx / nc, c = idx - i * nc;
+        const int i = fast_div(idx, nc, inv_nc), c = idx - i * nc;
         a[i * CH + c] = base[(long long)i * ncols + c];
     }
     __syncthreads();
@@ -381,9 +394,9 @@ fft_cols_kernel(double2* __restrict__ data, long long vec_stride, long long oute
     else r = fft_smem<-1>(a, b, pl, nc, 1, CH, true);
     if (MODE == 1 || MODE == 2) {
         for (int idx = threadIdx.x; idx < n * nc; idx += blockDim.x) {
-            const int i = idx / nc, c = idx - i * nc;
+            const int i = fast_div(idx, nc, inv_nc), c = idx - i * nc;
             const int col = geo.col0 + c0 + c;
-            const int iy = col / geo.nzh, iz = col - iy * geo.nzh;
+            const int iy = fast_div(col, geo.nzh, inv_nzh), iz = col - iy * geo.nzh;
             double f = coulG_at(geo, i, iy, iz);
             if (MODE == 1) {
                 const bool self = (iz == 0) || (2 * iz == geo.mesh[2]);
@@ -400,7 +413,7 @@ fft_cols_kernel(double2* __restrict__ data, long long vec_stride, long long oute
         }
     }
     for (int idx = threadIdx.x; idx < n * nc; idx += blockDim.x) {
-        const int i = idx / nc, c = idx - i * nc;
+        const int i = fast_div(idx, nc, inv_nc), c = idx - i * nc;
         base[(long long)i * ncols + c] = r[i * CH + c];
     }
 }
@@ -583,7 +596,7 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
         const int LB = pick_lb(P.ax[2].lalloc(), budget);
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         int rc; if ((rc = set_smem(fft_z_r2c_kernel, smem))) return rc;
-        dim3 grid((nx * ny + LB - 1) / LB, nvec);
+        dim3 grid((nx * ny + 2 * LB - 1) / (2 * LB), nvec);
         fft_z_r2c_kernel<<<grid, FFT_THREADS, smem, s>>>(in, ldin, spec, lds, P.ax[2], nx * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
@@ -767,7 +780,7 @@ extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int
         const int LB = pick_lb(P.ax[2].lalloc(), budget);
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         if ((rc = set_smem(fft_z_r2c_kernel, smem))) return rc;
-        dim3 grid((nxl * ny + LB - 1) / LB, nvec);
+        dim3 grid((nxl * ny + 2 * LB - 1) / (2 * LB), nvec);
         fft_z_r2c_kernel<<<grid, FFT_THREADS, smem, s>>>(in, ldin, (double2*)spec, lds, P.ax[2], nxl * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
