@@ -165,6 +165,12 @@ class Handle:
         v = torch.view_as_real(t)
         return v.reshape(*t.shape[:-1], 2 * t.shape[-1])
 
+    @staticmethod
+    def as_complex(t):
+        """float64 [m, 2n] (contiguous rows) -> complex128 view [m, n] (same memory)"""
+        import torch
+        return torch.view_as_complex(t.view(t.shape[0], t.shape[1] // 2, 2))
+
     def index(self, idx):
         import torch
         return torch.as_tensor(np.asarray(idx, dtype=np.int64), device=self.torch_device)

@@ -570,15 +570,19 @@ void fill_geom(CoulGeom& g, const int* mesh, const double* a, double scale)
 
 // shared memory per CTA of the FFT kernels (two ping-pong line buffers); smaller = more CTAs per SM.
 // Tuning knob: environment ISDF_FFT_SMEM_KB.
-size_t fft_smem_budget()
+// shared memory per CTA: column passes (y, x) want long contiguous row segments (wide CTAs), the z
+// pass reads whole lines and prefers more resident CTAs (tuning knobs ISDF_FFT_SMEM_KB / _Z_KB)
+size_t fft_smem_budget(bool zpass = false)
 {
-    static size_t v = 0;
-    if (v == 0) {
+    static size_t v[2] = {0, 0};
+    if (v[0] == 0) {
         const char* e = getenv("ISDF_FFT_SMEM_KB");
-        const long kb = e ? atol(e) : 96;
-        v = (size_t)std::min(200L, std::max(8L, kb)) * 1024;
+        const char* ez = getenv("ISDF_FFT_SMEM_Z_KB");
+        const long kb = e ? atol(e) : 64, kbz = ez ? atol(ez) : 64;
+        v[0] = (size_t)std::min(200L, std::max(8L, kb)) * 1024;
+        v[1] = (size_t)std::min(200L, std::max(8L, kbz)) * 1024;
     }
-    return v;
+    return v[zpass ? 1 : 0];
 }
 
 // lines (or columns) per CTA such that two ping-pong buffers of `nalloc` slots per line fit the budget
@@ -593,7 +597,7 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
     cudaStream_t s = h->stream;
     const size_t budget = fft_smem_budget();
     {
-        const int LB = pick_lb(P.ax[2].lalloc(), budget);
+        const int LB = pick_lb(P.ax[2].lalloc(), fft_smem_budget(true));
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         int rc; if ((rc = set_smem(fft_z_r2c_kernel, smem))) return rc;
         dim3 grid((nx * ny + 2 * LB - 1) / (2 * LB), nvec);
@@ -777,7 +781,7 @@ extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int
     const size_t budget = fft_smem_budget();
     CoulGeom geo; memset(&geo, 0, sizeof(geo));
     {
-        const int LB = pick_lb(P.ax[2].lalloc(), budget);
+        const int LB = pick_lb(P.ax[2].lalloc(), fft_smem_budget(true));
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         if ((rc = set_smem(fft_z_r2c_kernel, smem))) return rc;
         dim3 grid((nxl * ny + 2 * LB - 1) / (2 * LB), nvec);

@@ -149,7 +149,12 @@ def build(mydf, comm, ops=None):
 
     # stage 2: interpolation points
     NB = lib.isdf_select_panel_width()
-    Lt = ops.empty((npts, ldl))
+    # The two big buffers (factor rows, weighted spectra) are carved from flat allocations of one
+    # common size, so that the caching allocator hands the same two blocks back on every rebuild
+    # instead of splitting them and mapping new ones (tens of GB each).
+    nbig = max(npts * ldl, 2 * npts * nx * part.ncol_local(r))
+    big_lt = ops.empty((nbig,))
+    Lt = big_lt[:npts * ldl].view(npts, ldl)
     ldu = _lib.pad8(npts)
     U = ops.zeros((npts, ldu))
     plan = ops.select_create(nao, ngl, g0, ng, npts)
@@ -220,7 +225,9 @@ def build(mydf, comm, ops=None):
     # stage 4: Coulomb metric W through the slab-decomposed FFT
     ncols, ncl, col0 = part.ncols, part.ncol_local(r), int(part.col_off[r])
     ldy = nx * ncl
-    Y = ops.empty_complex((npts, ldy))
+    big_y = ops.empty((nbig,))
+    Yr = big_y[:2 * npts * ldy].view(npts, 2 * ldy)
+    Y = ops.as_complex(Yr)
     # vectors per all-to-all batch: computed from rank-independent maxima so that every rank
     # runs the same number of exchanges
     nxl_max = max(part.nx_local(q) for q in range(N))
@@ -253,7 +260,7 @@ def build(mydf, comm, ops=None):
             prof.mark('fft_unpack_ms')
             for kk, vv in prof.times.items():
                 acc[kk] = acc.get(kk, 0.0) + vv
-    del Lt                                      # the factor rows are not needed past this point
+    del Lt, big_lt                              # the factor rows are not needed past this point
     if prof:
         prof = ops.timer()
     ops.fft_x_coulomb(Y, ldy, npts, mesh, a, col0, ncl)
@@ -262,7 +269,6 @@ def build(mydf, comm, ops=None):
         acc.update(prof.times)
     ev.mark('fft_ms')
     W = ops.empty((npts, npts))
-    Yr = ops.as_real(Y)
     wmode = str(getattr(mydf, 'wgemm', 'i8'))
     if wmode.startswith('i8'):
         planes = int(wmode.split(':')[1]) if ':' in wmode else 8
@@ -274,7 +280,7 @@ def build(mydf, comm, ops=None):
     ops.symmetrize_upper(W, npts, npts)
     comm.all_reduce_sum(W)
     ev.mark('wgemm_ms')
-    del Y, Yr
+    del Y, Yr, big_y
     p0, p1 = int(part.ip_off[r]), int(part.ip_off[r + 1])
     if implicit:
         W = _congruence_solve(ops, comm, part, U, ldu, W, npts)

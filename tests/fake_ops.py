@@ -151,6 +151,10 @@ class FakeOps:
         v = torch.view_as_real(t)
         return v.reshape(*t.shape[:-1], 2 * t.shape[-1])
 
+    @staticmethod
+    def as_complex(t):
+        return torch.view_as_complex(t.view(t.shape[0], t.shape[1] // 2, 2))
+
     def index(self, idx):
         return torch.as_tensor(np.asarray(idx, dtype=np.int64))
 
