@@ -129,6 +129,16 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, int* v)
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, int* v)
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
 // Shared-memory matrix descriptor of a K-major tile whose rows are 128 bytes (one
 // SWIZZLE_128B atom): 8-row groups are 1024 bytes apart (stride byte offset), the leading
 // byte offset is unused, descriptor version 1 (sm_100), layout type 2 = SWIZZLE_128B.
@@ -314,6 +324,181 @@ syrk_i8_kernel(const SyrkArgs a)
     }
 }
 
+// ---- second kernel: 256x256 tile per CTA, clusters of 2x2 CTAs (512x512 per cluster) ----------
+// The 128x256-tile kernel above is bound by what one SM can take in from L2 (48 KiB per
+// 128x256x128 MMA block, ~55 B/clk/SM; profiles/r01_syrk_i8.md).  Here a CTA owns two row tiles
+// that share one B block (two MMAs per K step into the two halves of TMEM), 64 KiB per stage for
+// twice the work, and the 2x2 cluster multicasts A along rows and B along columns: every CTA
+// issues 32 KiB of copies per stage and receives 64 KiB.  TMEM is one 512-column buffer, so the
+// epilogue (8 warps) is not overlapped with the next unit; it is ~3 % of a unit.
+constexpr int NST2 = 3;
+constexpr int STAGE2 = 4 * A_BYTES;                       // A0 | A1 | B0 | B1, 16 KiB each
+constexpr int SMEM2 = NST2 * STAGE2 + 1024;
+constexpr int NTHREADS2 = 320;                            // producer, MMA, 8 epilogue warps
+constexpr int CT = 512;                                   // cluster tile
+
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(NTHREADS2, 1)
+syrk_i8_kernel2(const SyrkArgs a)
+{
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ uint64_t bar_full[NST2], bar_empty[NST2], bar_tfull, bar_tempty;
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t smem0 = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < NST2; ++i) { mbar_init(smem_u32(&bar_full[i]), 1); mbar_init(smem_u32(&bar_empty[i]), 4); }
+        mbar_init(smem_u32(&bar_tfull), 1);
+        mbar_init(smem_u32(&bar_tempty), 8);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     :: "r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = tmem_base_s;
+    const int rank = (int)cluster_rank();
+    const int r = rank >> 1, c = rank & 1;                 // position in the 2x2 cluster
+    const int cid = blockIdx.x / 4, ncl = gridDim.x / 4;
+    const uint16_t mask_row = (uint16_t)(3u << (2 * r));   // the two CTAs of my cluster row
+    const uint16_t mask_col = (uint16_t)((1u << c) | (1u << (c + 2)));
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== bulk-copy producer: A_c of my row block -> my cluster row, B_r of my column tile -> my cluster column
+            int st = 0; uint32_t ph = 0;
+            for (int t = cid; t < a.ntiles; t += ncl) {
+                const int2 tl = a.tiles[t];
+                const int8_t* arow = a.planes + (long long)(4 * tl.x + 2 * r + c) * a.rb_stride;
+                const int8_t* brow = a.planes + (long long)(4 * tl.y + 2 * c + r) * a.rb_stride;
+                for (int g = a.S - 1; g >= 0; --g)
+                    for (int s = 0; s <= g; ++s) {
+                        const int8_t* pa = arow + (long long)s * a.plane_stride;
+                        const int8_t* pb = brow + (long long)(g - s) * a.plane_stride;
+                        for (int kb = 0; kb < a.nkb; ++kb) {
+                            mbar_wait(smem_u32(&bar_empty[st]), ph ^ 1);
+                            const uint32_t full = smem_u32(&bar_full[st]);
+                            const uint32_t sa = smem0 + st * STAGE2, sb = sa + 2 * A_BYTES;
+                            mbar_expect_tx(full, STAGE2);
+                            bulk_load_mc(sa + c * A_BYTES, pa + (long long)kb * A_BYTES, A_BYTES, full, mask_row);
+                            bulk_load_mc(sb + r * A_BYTES, pb + (long long)kb * A_BYTES, A_BYTES, full, mask_col);
+                            if (++st == NST2) { st = 0; ph ^= 1; }
+                        }
+                    }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer: two M=128 MMAs per K step share the B block =====
+            int st = 0; uint32_t ph = 0;
+            uint32_t unit = 0;
+            for (int t = cid; t < a.ntiles; t += ncl) {
+                const int2 tl = a.tiles[t];
+                const int row0 = tl.x * CT + r * 256, col0 = tl.y * CT + c * 256;
+                const bool idle = row0 > col0 + 255 || row0 >= a.n || col0 >= a.n;    // nothing of this tile is stored
+                for (int g = a.S - 1; g >= 0; --g, ++unit) {
+                    mbar_wait(smem_u32(&bar_tempty), (unit & 1) ^ 1);
+                    tc_fence_after();
+                    const int niter = (g + 1) * a.nkb;
+                    for (int it = 0; it < niter; ++it) {
+                        mbar_wait(smem_u32(&bar_full[st]), ph);
+                        tc_fence_after();
+                        if (!idle) {
+                            const uint32_t sa = smem0 + st * STAGE2, sb = sa + 2 * A_BYTES;
+#pragma unroll
+                            for (int k = 0; k < BKB / UK; ++k) {
+                                const uint64_t db = umma_desc_k128(sb + k * UK);
+                                tc_mma_i8(tmem_base, umma_desc_k128(sa + k * UK), db, IDESC, (it | k) != 0);
+                                tc_mma_i8(tmem_base + TN, umma_desc_k128(sa + A_BYTES + k * UK), db, IDESC, (it | k) != 0);
+                            }
+                        }
+                        tc_commit_mc(smem_u32(&bar_empty[st]), 0xF);
+                        if (++st == NST2) { st = 0; ph ^= 1; }
+                    }
+                    tc_commit(smem_u32(&bar_tfull));
+                }
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2..9; lane quarter = warp % 4, accumulator half = (warp - 2) / 4 =====
+        const int q = warp & 3, hh = (warp - 2) >> 2;
+        const bool vec2 = (a.ldc % 2 == 0) && ((uintptr_t)a.C % 16 == 0);
+        uint32_t unit = 0;
+        for (int t = cid; t < a.ntiles; t += ncl) {
+            const int2 tl = a.tiles[t];
+            const int row0 = tl.x * CT + r * 256, colt = tl.y * CT + c * 256;
+            const bool idle = row0 > colt + 255 || row0 >= a.n || colt >= a.n;
+            const int row = row0 + hh * 128 + q * 32 + lane;
+            const double srow = row < a.n ? a.sc[row] : 0.0;
+            double* crow = a.C + (long long)row * a.ldc;
+            for (int g = a.S - 1; g >= 0; --g, ++unit) {
+                const double f = a.alpha * srow * exp2((double)(-12 - 7 * g));
+                mbar_wait(smem_u32(&bar_tfull), unit & 1);
+                tc_fence_after();
+                if (!idle) {
+#pragma unroll 1
+                    for (int cc = 0; cc < TN / 16; ++cc) {
+                        int v[16];
+                        tc_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + hh * TN + cc * 16, v);
+                        if (cc == TN / 16 - 1) {                        // last TMEM read: the MMA warp may go on
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(smem_u32(&bar_tempty));
+                        }
+                        const int col0 = colt + cc * 16;
+                        if (row < a.n && col0 + 15 >= row && col0 < a.n) {
+                            if (col0 >= row && col0 + 16 <= a.n) {
+                                double cv[16];
+                                if (vec2) {
+                                    const double2* p2 = reinterpret_cast<const double2*>(crow + col0);
+#pragma unroll
+                                    for (int j = 0; j < 8; ++j) { const double2 t2 = p2[j]; cv[2 * j] = t2.x; cv[2 * j + 1] = t2.y; }
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) cv[j] = crow[col0 + j];
+                                }
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) cv[j] += (double)v[j] * (f * a.sc[col0 + j]);
+                                if (vec2) {
+                                    double2* p2 = reinterpret_cast<double2*>(crow + col0);
+#pragma unroll
+                                    for (int j = 0; j < 8; ++j) p2[j] = make_double2(cv[2 * j], cv[2 * j + 1]);
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) crow[col0 + j] = cv[j];
+                                }
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) {
+                                    const int col = col0 + j;
+                                    if (col < a.n && col >= row) crow[col] += (double)v[j] * (f * a.sc[col]);
+                                }
+                            }
+                        }
+                    }
+                }
+                else {
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(smem_u32(&bar_tempty));
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
 // ---- digit planes -----------------------------------------------------------------
 // Row statistics, one CTA per row: sc[c][i] = 2^e with max_k |A[i, chunk c]| = m * 2^e,
 // m in [0.5, 1), and nrm[i] = ||A[i, :]||_2.
@@ -438,7 +623,41 @@ int cluster_size()
     return cl;
 }
 
-int rows_padded(int n, int cl) { return (int)align_up((size_t)n, (size_t)std::max(TN, TM * cl)); }
+// 2 (default): 256x256 tiles, 2x2 clusters (syrk_i8_kernel2); 1: 128x256 tiles, CL x 1 clusters
+int kernel_variant()
+{
+    static int v = 0;
+    if (!v) {
+        const char* e = getenv("ISDF_SYRK_KERNEL");
+        v = (e && atoi(e) == 1) ? 1 : 2;
+    }
+    return v;
+}
+
+int rows_padded(int n, int cl)
+{
+    if (kernel_variant() == 2) return (int)align_up((size_t)n, (size_t)CT);
+    return (int)align_up((size_t)n, (size_t)std::max(TN, TM * cl));
+}
+
+int launch_syrk2(isdf_handle* h, const SyrkArgs& a, int& nclusters)
+{
+    if (nclusters == 0) {
+        CUDA_TRY(cudaFuncSetAttribute(syrk_i8_kernel2, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
+        int fit = h->num_sms / 4;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(h->num_sms / 4 * 4); cfg.blockDim = dim3(NTHREADS2); cfg.dynamicSmemBytes = SMEM2;
+        cudaLaunchAttribute at; at.id = cudaLaunchAttributeClusterDimension;
+        at.val.clusterDim.x = 4; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+        cfg.attrs = &at; cfg.numAttrs = 1;
+        int nmax = 0;
+        if (cudaOccupancyMaxActiveClusters(&nmax, syrk_i8_kernel2, &cfg) == cudaSuccess && nmax > 0) fit = std::min(fit, nmax);
+        else (void)cudaGetLastError();
+        nclusters = std::max(1, std::min(fit, a.ntiles));
+    }
+    syrk_i8_kernel2<<<nclusters * 4, NTHREADS2, SMEM2, h->stream>>>(a);
+    return ISDF_OK;
+}
 
 template <int CL>
 int launch_syrk(isdf_handle* h, const SyrkArgs& a, int& nclusters)
@@ -509,11 +728,20 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     // persistent schedule: strips of STRIP tile columns, row groups ascending inside a strip, so that
     // the tiles in flight share few distinct row/column blocks (L2 reuse of the digit planes)
     std::vector<int2> tiles;
-    const int ngr = (tr + cl - 1) / cl;
-    for (int s0 = 0; s0 < tc; s0 += STRIP)
-        for (int gi = 0; gi < ngr; ++gi)
-            for (int tj = s0; tj < std::min(tc, s0 + STRIP); ++tj)
-                if (gi * cl <= 2 * tj + 1) tiles.push_back(make_int2(gi, tj));
+    const int variant = kernel_variant();
+    if (variant == 2) {
+        const int nb = nrows_pad / CT;                     // 512x512 cluster tiles of the upper triangle
+        for (int bj = 0; bj < nb; ++bj)
+            for (int bi = 0; bi <= bj; ++bi) tiles.push_back(make_int2(bi, bj));
+    } else {
+        const int ngr = (tr + cl - 1) / cl;
+        for (int s0 = 0; s0 < tc; s0 += STRIP)
+            for (int gi = 0; gi < ngr; ++gi)
+                for (int tj = s0; tj < std::min(tc, s0 + STRIP); ++tj)
+                    if (gi * cl <= 2 * tj + 1) tiles.push_back(make_int2(gi, tj));
+    }
+    if (getenv("ISDF_SYRK_DEBUG_SAMETILE"))               // traffic experiment only (results are garbage):
+        for (auto& t : tiles) t = make_int2(0, 0);         // every cluster streams the same blocks
     const int ntiles = (int)tiles.size();
     CUDA_TRY(cudaMemcpyAsync(d_tiles, tiles.data(), ntiles * sizeof(int2), cudaMemcpyHostToDevice, h->stream));
 
@@ -565,14 +793,15 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
         a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = kcpad / BKB; a.S = S;
         a.C = C; a.ldc = ldc; a.sc = sc; a.alpha = alpha;
         int rc;
-        switch (cl) {
+        if (variant == 2) rc = launch_syrk2(h, a, nclusters);
+        else switch (cl) {
         case 1: rc = launch_syrk<1>(h, a, nclusters); break;
         case 2: rc = launch_syrk<2>(h, a, nclusters); break;
         case 8: rc = launch_syrk<8>(h, a, nclusters); break;
         default: rc = launch_syrk<4>(h, a, nclusters); break;
         }
         if (rc != ISDF_OK) return rc;
-        g_last_ops += 2.0 * (S * (S + 1) / 2) * (double)ntiles * cl * TM * TN * (double)kcpad;
+        g_last_ops += 2.0 * (S * (S + 1) / 2) * (double)ntiles * (variant == 2 ? (double)CT * CT : (double)cl * TM * TN) * (double)kcpad;
         h->other_launches += 2;
     }
     CUDA_TRY(cudaGetLastError());
