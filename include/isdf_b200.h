@@ -166,6 +166,19 @@ double isdf_syrk_i8_last_ops(void);
 int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A, long long lda,
                  double* C, long long ldc, double alpha, int nslices, void* ws, size_t ws_bytes);
 
+/* Exact-density J on the FFT grid, the reference's FFTDF route
+ * [pyscf/pbc/df/fft_jk.py:33-109: rhoR = einsum(ao, dm, ao); vR = ifft(coulG fft(rhoR)).real;
+ * vj = weight * ao^T diag(vR) ao, weight = vol/ngrids].  Slab form for the grid-sharded driver:
+ * rho on ngl local grid points, then isdf_coulomb_apply on the gathered density, then the J
+ * contribution of the slab.  Workspace of both calls: isdf_grid_j_ws_bytes. */
+size_t isdf_grid_j_ws_bytes(int nao, long long ldphi);
+int isdf_density_on_grid(isdf_handle* h, const double* phi, long long ldphi, int nao, long long ngl,
+                         const double* dm, int nset, double* rho, long long ldr,
+                         void* ws, size_t ws_bytes);
+int isdf_j_from_potential(isdf_handle* h, const double* phi, long long ldphi, int nao, long long ngl,
+                          const double* vR, long long ldv, int nset, double weight,
+                          double* vj, void* ws, size_t ws_bytes);
+
 /* Stage 5 [spec; exact limit pyscf/pbc/df/fft_jk.py:33-109,177-302].
  * X[nao, np] = phi[:, ip];  J = X diag(W rho) X^T, rho_P = (X^T D X)_PP;
  * K = X ((X^T D X) o W) X^T.  dm/vj/vk: [nset, nao, nao]. */

@@ -54,6 +54,9 @@ SIGNATURES = {
     'isdf_syrk_i8_ws_bytes': (c_sz, [c_int, c_ll, c_int]),
     'isdf_syrk_i8_last_ops': (c_dbl, []),
     'isdf_syrk_i8': (c_int, [c_vp, c_int, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_vp, c_sz]),
+    'isdf_grid_j_ws_bytes': (c_sz, [c_int, c_ll]),
+    'isdf_density_on_grid': (c_int, [c_vp, c_vp, c_ll, c_int, c_ll, c_vp, c_int, c_vp, c_ll, c_vp, c_sz]),
+    'isdf_j_from_potential': (c_int, [c_vp, c_vp, c_ll, c_int, c_ll, c_vp, c_ll, c_int, c_dbl, c_vp, c_vp, c_sz]),
     'isdf_get_jk_block_ws_bytes': (c_sz, [c_int, c_int, c_int]),
     'isdf_get_jk_block': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_int, c_int, c_int,
                                   c_int, c_int, c_vp, c_vp, c_vp, c_sz]),
@@ -333,6 +336,22 @@ class Handle:
         check(self.lib.isdf_syrk_i8(self.h, n, K, c_vp(A.data_ptr()), lda, c_vp(C.data_ptr()), ldc,
                                     float(alpha), int(nslices), c_vp(ws.data_ptr()), nbytes))
         self.syrk_i8_ops = float(self.lib.isdf_syrk_i8_last_ops())
+        return ws
+
+    def density_on_grid(self, phi, ldphi, nao, ngl, dm, nset, rho, ldr, ws=None):
+        nbytes = self.lib.isdf_grid_j_ws_bytes(nao, ldphi)
+        if ws is None:
+            ws = self.workspace(nbytes)
+        check(self.lib.isdf_density_on_grid(self.h, c_vp(phi.data_ptr()), ldphi, nao, ngl, c_vp(dm.data_ptr()), nset,
+                                            c_vp(rho.data_ptr()), ldr, c_vp(ws.data_ptr()), nbytes))
+        return ws
+
+    def j_from_potential(self, phi, ldphi, nao, ngl, vR, ldv, nset, weight, vj, ws=None):
+        nbytes = self.lib.isdf_grid_j_ws_bytes(nao, ldphi)
+        if ws is None:
+            ws = self.workspace(nbytes)
+        check(self.lib.isdf_j_from_potential(self.h, c_vp(phi.data_ptr()), ldphi, nao, ngl, c_vp(vR.data_ptr()), ldv,
+                                             nset, float(weight), c_vp(vj.data_ptr()), c_vp(ws.data_ptr()), nbytes))
         return ws
 
     def get_jk_block(self, X, Wrows, ldw, p0, npl, dm, nset, nao, npts, with_j, with_k, vj, vk, ws=None):

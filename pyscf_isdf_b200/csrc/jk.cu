@@ -123,3 +123,55 @@ extern "C" int isdf_get_jk(isdf_handle* h, const double* X, const double* W,
 {
     return isdf_get_jk_block(h, X, W, np, 0, np, dm, nset, nao, np, with_j, with_k, vj, vk, ws, ws_bytes);
 }
+
+// ---- exact-density J on the FFT grid (the FFTDF route, pyscf/pbc/df/fft_jk.py:33-109) ----------
+// rho_g = sum_{mu nu} phi[mu,g] D[mu,nu] phi[nu,g] on a slab of grid points;
+// the caller solves vR = ifft(coulG * fft(rho)).real (isdf_coulomb_apply on the whole grid) and
+// J = weight * phi diag(vR) phi^T comes from isdf_j_from_potential.  Workspace: nao * ldphi doubles.
+extern "C" size_t isdf_grid_j_ws_bytes(int nao, long long ldphi)
+{
+    return (size_t)nao * (size_t)ldphi * sizeof(double) + 256;
+}
+
+extern "C" int isdf_density_on_grid(isdf_handle* h, const double* phi, long long ldphi, int nao, long long ngl,
+                                    const double* dm, int nset, double* rho, long long ldr,
+                                    void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && phi && dm && rho && ws && nao > 0 && ngl > 0 && nset > 0 && ldphi >= ngl && ldr >= ngl);
+    ARG_CHECK(ngl < 0x7fffffffLL);
+    if (ws_bytes < isdf_grid_j_ws_bytes(nao, ldphi)) { isdf_set_error("isdf_density_on_grid: workspace too small"); return ISDF_ERR_WS; }
+    double* T = (double*)align_up((size_t)ws, 256);
+    cudaStream_t s = h->stream;
+    for (int i = 0; i < nset; ++i) {
+        int rc;      // T[mu,g] = sum_nu D[mu,nu] phi[nu,g]
+        if ((rc = gemm6(h, nao, (int)ngl, nao, dm + (size_t)i * nao * nao, nao, 0, phi, ldphi, 1, T, ldphi, nullptr, 0, EPI_STORE))) return rc;
+        coldot_kernel<<<(unsigned)((ngl + 255) / 256), 256, 0, s>>>(phi, T, nao, (int)ngl, ldphi, rho + (size_t)i * ldr);
+        h->other_launches++;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return ISDF_OK;
+}
+
+extern "C" int isdf_j_from_potential(isdf_handle* h, const double* phi, long long ldphi, int nao, long long ngl,
+                                     const double* vR, long long ldv, int nset, double weight,
+                                     double* vj, void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && phi && vR && vj && ws && nao > 0 && ngl > 0 && nset > 0 && ldphi >= ngl && ldv >= ngl);
+    ARG_CHECK(ngl < 0x7fffffffLL);
+    if (ws_bytes < isdf_grid_j_ws_bytes(nao, ldphi)) { isdf_set_error("isdf_j_from_potential: workspace too small"); return ISDF_ERR_WS; }
+    double* Y = (double*)align_up((size_t)ws, 256);
+    cudaStream_t s = h->stream;
+    for (int i = 0; i < nset; ++i) {
+        dim3 g((unsigned)((ngl + 255) / 256), (unsigned)std::min(nao, 64));
+        scale_cols_kernel<<<g, 256, 0, s>>>(phi, vR + (size_t)i * ldv, nao, (int)ngl, ldphi, ldphi, Y);
+        h->other_launches++;
+        GemmParams p;       // J = weight * Y phi^T
+        p.M = nao; p.N = nao; p.K = (int)ngl; p.A = Y; p.lda = ldphi; p.a_kmajor = 0;
+        p.B = phi; p.ldb = ldphi; p.b_kmajor = 0; p.C = vj + (size_t)i * nao * nao; p.ldc = nao;
+        p.Cin = nullptr; p.ldcin = 0; p.E = nullptr; p.lde = 0; p.alpha = weight; p.neg = 0; p.epi = EPI_STORE; p.upper_only = 0;
+        int rc;
+        if ((rc = gemm_launch(h, p))) return rc;
+    }
+    CUDA_TRY(cudaGetLastError());
+    return ISDF_OK;
+}

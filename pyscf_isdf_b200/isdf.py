@@ -30,10 +30,11 @@ from .cell import madelung as _madelung
 class ISDF:
     _keys = {'cell', 'kpts', 'mesh', 'c', 'n_ip', 'select', 'fit', 'tol', 'exxdiv',
              'ip_index', 'ip_resid', 'W', 'aoR', 'aoR_ip', 'stdout', 'verbose', 'max_memory',
-             'keep_aoR', 'timings', 'comm', 'wgemm'}
+             'keep_aoR', 'timings', 'comm', 'wgemm', 'exact_j'}
 
     def __init__(self, cell, kpts=np.zeros((1, 3)), c=15, n_ip=None, select='cholesky',
-                 fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None, wgemm='i8'):
+                 fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None, wgemm='i8',
+                 exact_j=False):
         self.cell = cell
         self.stdout = sys.stdout
         self.verbose = getattr(cell, 'verbose', 0)
@@ -49,6 +50,9 @@ class ISDF:
         # wgemm: how the Coulomb-metric product Y Y^T is computed: 'i8' / 'i8:<planes>' (int8 tcgen05
         # split product, csrc/syrk_i8.cu; 8 digit planes = FP64-GEMM accuracy) or 'fp64' (FP64 tensor pipe)
         self.wgemm = wgemm
+        # exact_j: J from the exact density on the FFT grid (the reference's FFTDF route,
+        # pyscf/pbc/df/fft_jk.py:33-109) instead of the ISDF contraction; K stays ISDF.  Needs keep_aoR.
+        self.exact_j = exact_j
         self._device = device
         self._handle = None
         # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
@@ -259,15 +263,20 @@ class ISDF:
         h = self.handle
         nao, npts = self.aoR_ip.shape
         nset = d_dm.shape[0]
-        if self.comm is not None:
+        isdf_j = with_j and not self.exact_j
+        if self.comm is not None and (isdf_j or with_k):
             from . import dist                  # self.W is this rank's row block of W
-            vj, vk = dist.get_jk_device(self, self.comm, d_dm, with_j, with_k)
-        else:
-            vj = h.empty((nset, nao, nao)) if with_j else None
+            vj, vk = dist.get_jk_device(self, self.comm, d_dm, isdf_j, with_k)
+        elif isdf_j or with_k:
+            vj = h.empty((nset, nao, nao)) if isdf_j else None
             vk = h.empty((nset, nao, nao)) if with_k else None
             if self._jk_ws is None:
                 self._jk_ws = h.workspace(h.lib.isdf_get_jk_ws_bytes(nao, npts))
-            h.get_jk(self.aoR_ip, self.W, d_dm, nset, nao, npts, with_j, with_k, vj, vk, ws=self._jk_ws)
+            h.get_jk(self.aoR_ip, self.W, d_dm, nset, nao, npts, isdf_j, with_k, vj, vk, ws=self._jk_ws)
+        else:
+            vj = vk = None
+        if with_j and self.exact_j:
+            vj = self.get_j_exact_device(d_dm)
         if with_k and exxdiv == 'ewald':
             # vk += madelung * S D S   (pyscf/pbc/df/df_jk.py:1446-1455)
             S = self.get_ovlp()
@@ -279,6 +288,36 @@ class ISDF:
                 h.dgemm(nao, nao, nao, tmp, nao, 0, S, nao, 1, sds, nao, alpha=mad)    # mad (S D) S
                 vk[i] += sds
         return vj, vk
+
+    def get_j_exact_device(self, d_dm):
+        """J from the exact density on the FFT grid: rho = diag(Phi^T D Phi), vR = ifft(coulG fft(rho)).real,
+        J = (vol/ng) Phi diag(vR) Phi^T (pyscf/pbc/df/fft_jk.py:33-109).  With a sharded grid every rank
+        forms rho on its slab, the slabs are gathered (8 ng bytes), every rank solves the one-vector
+        Poisson problem on the whole grid and contracts its slab; J is summed over ranks."""
+        if self.W is None:
+            self.build()
+        if self.aoR is None:
+            raise RuntimeError('exact J needs the AO matrix on the grid: build with keep_aoR=True')
+        h = self.handle
+        nao = self.aoR.shape[0]
+        nset = d_dm.shape[0]
+        ng = int(np.prod(self.mesh))
+        g0, g1 = self._slab if self._slab is not None else (0, ng)
+        ngl = g1 - g0
+        ld = self._ld
+        ws = h.workspace(h.lib.isdf_grid_j_ws_bytes(nao, ld))
+        ngp = _lib.pad8(ng)
+        rho = h.zeros((nset, ngp))
+        h.density_on_grid(self.aoR, ld, nao, ngl, d_dm, nset, rho[:, g0:], ngp, ws=ws)
+        if self.comm is not None and self.comm.size > 1:
+            self.comm.all_reduce_sum(rho)           # slabs are disjoint: the sum is the gather
+        vR = h.empty((nset, ngp))
+        h.coulomb_apply(rho, ngp, nset, self.mesh, self.cell.lattice_vectors(), vR, ngp)
+        vj = h.empty((nset, nao, nao))
+        h.j_from_potential(self.aoR, ld, nao, ngl, vR[:, g0:], ngp, nset, self.cell.vol / ng, vj, ws=ws)
+        if self.comm is not None and self.comm.size > 1:
+            self.comm.all_reduce_sum(vj)
+        return vj
 
     def get_j(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None):
         return self.get_jk(dm, hermi, kpts, kpts_band, True, False, omega)[0]

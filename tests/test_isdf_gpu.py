@@ -108,3 +108,24 @@ def test_isdf_int8_coulomb_metric(wgemm):
     orc = oracle.isdf_build(oracle_phi(cell), cell.lattice_vectors(), cell.mesh, 6 * cell.nao)
     vjo, vko = oracle.isdf_get_jk(orc['X'], orc['W'], dm)
     assert abs(vj - vjo).max() < 1e-8 and abs(vk - vko).max() < 1e-8
+
+
+def test_exact_density_j_matches_reference_fftdf():
+    """exact_j=True: J by the reference's FFTDF route (pyscf/pbc/df/fft_jk.py:33-109) on the device;
+    reproduces the reference golden fp(vj) of pyscf/pbc/df/test/test_fft.py:642-645 and the
+    oracle's FFTDF J on a second cell, for one and two density matrices; K stays ISDF."""
+    cell = he_c_cell()
+    mydf = ISDF(cell, n_ip=60, exact_j=True)
+    dm = np.eye(cell.nao, dtype=int)
+    vj, vk = mydf.get_jk(dm, exxdiv=None)
+    assert abs(oracle.fp(vj) - 3.7955873127283377) < 1e-9
+    assert abs(oracle.fp(vk) - 4.290076429522121) < 1e-7
+    cell = diamond_c8([14, 14, 14], basis='gth-dzvp', jitter=0.15)
+    mydf = ISDF(cell, c=6, exact_j=True)
+    dms = np.stack([rand_dm(cell.nao), rand_dm(cell.nao)[::-1, ::-1].copy()])
+    vj = mydf.get_j(dms)
+    ref = oracle.fftdf_get_j(oracle_phi(cell).T, dms, cell.lattice_vectors(), cell.mesh)
+    assert vj.shape == dms.shape and abs(vj - ref).max() < 1e-10
+    # J-only call does not need (or touch) the ISDF contraction
+    j_only, none = mydf.get_jk(dms[0], with_k=False)
+    assert none is None and abs(j_only - ref[0]).max() < 1e-10
