@@ -346,7 +346,10 @@ def run_b200(args):
         'peak_source': 'cuBLAS DGEMM 8192^3 best-of-10 measured in this run (MEASURED_PEAKS.json has no FP64 entry)',
         'launches_per_step': gcount / args.steps, 'flops_per_step': gflops / args.steps,
         'gemm_ms_per_step': gms / args.steps, 'gemm_share_of_step': gms / total_ms,
-        'traffic': None,
+        # DRAM bytes of one representative launch of this kernel from an `ncu --set full` capture
+        # (flush GEMM M=128 N=357912 K=6240: 19.3 GB against 18.6 GB algorithmic, profiles/r01_ncu_final.md)
+        'traffic': 1.93e10 if name == 'c64' else None,
+        'traffic_launch': 'C[128,357912] -= A^T B, K=6240 (selection flush): algorithmic 1.86e10 B' if name == 'c64' else None,
     }
     line = {
         'metric': METRIC, 'value': step_ms / 1e3, 'unit': 's', 'n_gpus': world,
