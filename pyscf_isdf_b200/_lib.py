@@ -185,6 +185,10 @@ class Handle:
     def timer(self):
         return StageTimer(self)
 
+    def device_mem_bytes(self):
+        import torch
+        return int(torch.cuda.get_device_properties(self.device).total_memory)
+
     def workspace(self, nbytes):
         import torch
         return torch.empty(int(nbytes), dtype=torch.uint8, device=self.torch_device)

@@ -323,6 +323,10 @@ panel_kernel(SelState* st, const double* __restrict__ T, long long ldT,
     const int nthr = gridDim.x * blockDim.x;
     const int gtid = blockIdx.x * blockDim.x + tid;
     const int m = st->m;
+    // candidates are dealt evenly over the CTAs (a contiguous block of cpb per CTA, one per thread):
+    // with m = 1024 a linear thread index would leave 12 of the 16 CTAs without work
+    const int cpb = (((m + (int)gridDim.x - 1) / (int)gridDim.x) + 31) & ~31;
+    const int myc = (tid < cpb && blockIdx.x * cpb + tid < m) ? blockIdx.x * cpb + tid : -1;
     const double tol = st->tol;
     const double theta = st->theta_key ? __longlong_as_double((long long)st->theta_key) : 0.0;
     unsigned int epoch = 0;
@@ -331,7 +335,8 @@ panel_kernel(SelState* st, const double* __restrict__ T, long long ldT,
     for (; kk < nbmax; ++kk) {
         // ---- argmax over owned candidates (ties -> lowest grid index) ----
         double bv = -1e300; int bg = 0x7fffffff, bc = -1;
-        for (int c = gtid; c < m; c += nthr) {
+        if (myc >= 0) {
+            const int c = myc;
             const double v = dC[c]; const int g = cand[c];
             if (better(v, g, bv, bg)) { bv = v; bg = g; bc = c; }
         }
@@ -365,7 +370,8 @@ panel_kernel(SelState* st, const double* __restrict__ T, long long ldT,
         for (int j = tid; j < kk; j += blockDim.x) s_row[j] = LppT[(long long)j * MCAP + sc];
         __syncthreads();
         const double* Trow = T + (long long)sc * ldT;
-        for (int c = gtid; c < m; c += nthr) {
+        if (myc >= 0) {
+            const int c = myc;
             double acc = Trow[c];
             for (int j = 0; j < kk; ++j) acc = fma(-LppT[(long long)j * MCAP + c], s_row[j], acc);
             const double L = acc / piv;
@@ -697,15 +703,23 @@ extern "C" int isdf_select_candidates(isdf_select_plan* pl, const double* phi, l
 
 static int gemm_kc(isdf_handle* h, int M, int N, int K, const double* A, long long lda,
                    const double* B, long long ldb, int b_kmajor, double* C, long long ldc,
-                   const double* Cin, int neg, int epi)
+                   const double* Cin, int neg, int epi, int upper_only = 0)
 {
     GemmParams p;
     p.M = M; p.N = N; p.K = K;
     p.A = A; p.lda = lda; p.a_kmajor = 0;
     p.B = B; p.ldb = ldb; p.b_kmajor = b_kmajor;
     p.C = C; p.ldc = ldc; p.Cin = Cin; p.ldcin = ldc;
-    p.E = nullptr; p.lde = 0; p.alpha = 1.0; p.neg = neg; p.epi = epi; p.upper_only = 0;
+    p.E = nullptr; p.lde = 0; p.alpha = 1.0; p.neg = neg; p.epi = epi; p.upper_only = upper_only;
     return gemm_launch(h, p);
+}
+
+// T[i][j] = T[j][i] for i > j (the candidate Gram is symmetric: only its upper tiles are computed)
+__global__ void mirror_upper_kernel(double* __restrict__ T, long long ld, int n)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y * blockDim.y + threadIdx.y;
+    if (i < n && j < i) T[(long long)i * ld + j] = T[(long long)j * ld + i];
 }
 
 // Panel factorisation on the gathered candidate blocks of all ranks
@@ -727,9 +741,16 @@ extern "C" int isdf_select_panel(isdf_select_plan* pl, const double* blocks, int
     panel_prepare_kernel<<<1, 1024, 0, s>>>(blocks, nranks, quota, rl, w.cand, w.dC, w.st);
     h->other_launches++;
     // T = G[C,C] - Lc Lc^T  (same FMA chains as the flush GEMMs)
-    if ((rc = gemm_kc(h, m, m, pl->nao, blocks + META, rl, blocks + META, rl, 0, w.T, MCAP, nullptr, 0, EPI_SQUARE))) return rc;
+    // symmetric: upper tiles only, then mirrored (x*y == y*x, so the mirrored entries are the bits
+    // the full product would have produced)
+    if ((rc = gemm_kc(h, m, m, pl->nao, blocks + META, rl, blocks + META, rl, 0, w.T, MCAP, nullptr, 0, EPI_SQUARE, 1))) return rc;
     if (k0 > 0)
-        if ((rc = gemm_kc(h, m, m, k0, blocks + META + naop, rl, blocks + META + naop, rl, 0, w.T, MCAP, w.T, 1, EPI_STORE))) return rc;
+        if ((rc = gemm_kc(h, m, m, k0, blocks + META + naop, rl, blocks + META + naop, rl, 0, w.T, MCAP, w.T, 1, EPI_STORE, 1))) return rc;
+    {
+        dim3 blk(32, 8), grd((m + 31) / 32, (m + 7) / 8);
+        mirror_upper_kernel<<<grd, blk, 0, s>>>(w.T, MCAP, m);
+        h->other_launches++;
+    }
     {
         SelState* st = w.st; const double* T = w.T; long long ldT = MCAP; const int* cand = w.cand;
         double* dC = w.dC; double* LppT = w.LppT; int* pvl = w.piv_local; double* rs = w.resid_dev;

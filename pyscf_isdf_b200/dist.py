@@ -149,11 +149,21 @@ def build(mydf, comm, ops=None):
 
     # stage 2: interpolation points
     NB = lib.isdf_select_panel_width()
-    # The two big buffers (factor rows, weighted spectra) are carved from flat allocations of one
-    # common size, so that the caching allocator hands the same two blocks back on every rebuild
-    # instead of splitting them and mapping new ones (tens of GB each).
+    # The two big buffers (factor rows, weighted spectra) are two flat allocations of one common
+    # size owned by the ISDF object: handing tens of GB back to the caching allocator between
+    # rebuilds lets it split the blocks for small requests and map new ones (seen as 0.2-0.5 s
+    # stalls in the AO / selection / FFT stages of later builds).
     nbig = max(npts * ldl, 2 * npts * nx * part.ncol_local(r))
-    big_lt = ops.empty((nbig,))
+    arena = getattr(mydf, '_arena', None)
+    if arena is None or arena[0].numel() < nbig:
+        mydf._arena = arena = None                # release the old pair before mapping a larger one
+        arena = (ops.empty((nbig,)), ops.empty((nbig,)))
+        # kept by the object across reset()/build() cycles unless that would pin most of the device
+        total = ops.device_mem_bytes() if hasattr(ops, 'device_mem_bytes') else 1 << 62
+        if getattr(mydf, 'keep_buffers', True) and 16 * nbig <= 0.45 * total:
+            mydf._arena = arena
+    big_lt, big_y = arena
+    del arena
     Lt = big_lt[:npts * ldl].view(npts, ldl)
     ldu = _lib.pad8(npts)
     U = ops.zeros((npts, ldu))
@@ -225,7 +235,6 @@ def build(mydf, comm, ops=None):
     # stage 4: Coulomb metric W through the slab-decomposed FFT
     ncols, ncl, col0 = part.ncols, part.ncol_local(r), int(part.col_off[r])
     ldy = nx * ncl
-    big_y = ops.empty((nbig,))
     Yr = big_y[:2 * npts * ldy].view(npts, 2 * ldy)
     Y = ops.as_complex(Yr)
     # vectors per all-to-all batch: computed from rank-independent maxima so that every rank

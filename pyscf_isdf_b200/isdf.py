@@ -30,7 +30,7 @@ from .cell import madelung as _madelung
 class ISDF:
     _keys = {'cell', 'kpts', 'mesh', 'c', 'n_ip', 'select', 'fit', 'tol', 'exxdiv',
              'ip_index', 'ip_resid', 'W', 'aoR', 'aoR_ip', 'stdout', 'verbose', 'max_memory',
-             'keep_aoR', 'timings', 'comm', 'wgemm', 'exact_j'}
+             'keep_aoR', 'timings', 'comm', 'wgemm', 'exact_j', 'keep_buffers'}
 
     def __init__(self, cell, kpts=np.zeros((1, 3)), c=15, n_ip=None, select='cholesky',
                  fit='implicit', tol=-1.0, device=None, keep_aoR=True, comm=None, wgemm='i8',
@@ -53,6 +53,10 @@ class ISDF:
         # exact_j: J from the exact density on the FFT grid (the reference's FFTDF route,
         # pyscf/pbc/df/fft_jk.py:33-109) instead of the ISDF contraction; K stays ISDF.  Needs keep_aoR.
         self.exact_j = exact_j
+        # keep_buffers: the two build-time work buffers (factor rows, spectra) stay with the object
+        # for the next build() after reset(); release_buffers() drops them
+        self.keep_buffers = True
+        self._arena = None
         self._device = device
         self._handle = None
         # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
@@ -86,6 +90,11 @@ class ISDF:
         self._jk_ws = None
         self._part = None
         self._slab = None
+        return self
+
+    def release_buffers(self):
+        """Give the build-time work buffers back to the allocator (they are only needed by build())."""
+        self._arena = None
         return self
 
     def dump_flags(self, verbose=None):
