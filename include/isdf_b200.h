@@ -210,7 +210,7 @@ int isdf_dgemm(isdf_handle* h, int M, int N, int K,
                double alpha, int neg, int epi, int upper_only);
 
 /* Tuning knob: CTA tile of the GEMM kernel, 0 = automatic (default),
- * 2 = 64x128, 3 = 64x64. */
+ * 2 = 64x128 (four 64x32 warps), 3 = 64x64 (two 64x32 warps), 4 = 64x64 (four 32x32 warps). */
 int isdf_set_gemm_tile(isdf_handle* h, int which);
 
 /* Per-launch timing of the GEMM kernel (bench.py roofline): enable=1 resets and

@@ -35,7 +35,7 @@
 namespace {
 
 constexpr int BK = 16;
-constexpr int WTM = 64, WTN = 32;          // warp tile
+constexpr int WTN = 32;                    // warp tile: (8 MI) x 32, MI = 8 (throughput) or 4 (latency)
 constexpr int MINB = 3;                    // CTAs per SM the 64x128 tile is built for (registers <= 168)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p)
@@ -127,15 +127,15 @@ __device__ __forceinline__ void load_async(double* S, const double* __restrict__
 }
 
 // ---- one k-tile of DMMAs on a resident stage ------------------------------------------------
-template <typename TA, typename TB, bool NEG>
+template <typename TA, typename TB, bool NEG, int MI>
 __device__ __forceinline__ void compute_stage(const double* __restrict__ As, const double* __restrict__ Bs,
-                                              double (&acc)[8][4][2], int wm, int wn, int g, int t)
+                                              double (&acc)[MI][4][2], int wm, int wn, int g, int t)
 {
 #pragma unroll
     for (int kk = 0; kk < BK; kk += 4) {
-        double a[8], b[4];
+        double a[MI], b[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < MI; ++i) {
             const double v = As[TA::at(wm + 8 * i + g, kk + t)];
             a[i] = NEG ? -v : v;
         }
@@ -143,16 +143,17 @@ __device__ __forceinline__ void compute_stage(const double* __restrict__ As, con
         for (int j = 0; j < 4; ++j)
             b[j] = Bs[TB::at(wn + 8 * j + g, kk + t)];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < MI; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j) dmma884(acc[i][j], a[i], b[j]);
     }
 }
 
-template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG>
-__global__ void __launch_bounds__(32 * WM * WN, (NSTAGE > 3) ? 1 : ((WM * WN == 4) ? MINB : 4))
+template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG, int MI>
+__global__ void __launch_bounds__(32 * WM * WN, (MI == 8 && WM * WN == 4) ? MINB : (WM * WN <= 4 ? 4 : (WM * WN <= 8 ? 2 : 1)))
 dgemm_kernel(GemmParams p)
 {
+    constexpr int WTM = 8 * MI;
     constexpr int BM = WTM * WM, BN = WTN * WN, NT = 32 * WM * WN;
     using TA = OpTile<BM, AK>;
     using TB = OpTile<BN, BKM>;
@@ -181,9 +182,9 @@ dgemm_kernel(GemmParams p)
     }
 
     // accumulator init (the FMA chain starts here)
-    double acc[8][4][2];
+    double acc[MI][4][2];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < MI; ++i) {
         const int m = m0 + wm + 8 * i + g;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -205,7 +206,7 @@ dgemm_kernel(GemmParams p)
         if (kt + NSTAGE - 1 < nfull) issue(kt + NSTAGE - 1);
         cp_async_commit();
         const double* As = smem + s * STAGE;
-        compute_stage<TA, TB, NEG>(As, As + TA::SIZE, acc, wm, wn, g, t);
+        compute_stage<TA, TB, NEG, MI>(As, As + TA::SIZE, acc, wm, wn, g, t);
     }
     // unaligned operands: synchronous zero-filling loads
     for (int k0 = nfull * BK; k0 < K; k0 += BK) {
@@ -215,12 +216,12 @@ dgemm_kernel(GemmParams p)
         load_slow<BM, AK, NT>(As, p.A, p.lda, M, K, m0, k0, tid);
         load_slow<BN, BKM, NT>(Bs, p.B, p.ldb, N, K, n0, k0, tid);
         __syncthreads();
-        compute_stage<TA, TB, NEG>(As, Bs, acc, wm, wn, g, t);
+        compute_stage<TA, TB, NEG, MI>(As, Bs, acc, wm, wn, g, t);
     }
 
     // epilogue: lane holds C[m][n], C[m][n+1] of every 8x8 tile
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < MI; ++i) {
         const int m = m0 + wm + 8 * i + g;
         if (m >= M) continue;
 #pragma unroll
@@ -245,12 +246,12 @@ dgemm_kernel(GemmParams p)
     }
 }
 
-template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG>
+template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG, int MI>
 int launch_cfg(isdf_handle* h, const GemmParams& p)
 {
-    constexpr int BM = WTM * WM, BN = WTN * WN, NT = 32 * WM * WN;
+    constexpr int BM = 8 * MI * WM, BN = WTN * WN, NT = 32 * WM * WN;
     const size_t smem = sizeof(double) * NSTAGE * (OpTile<BM, AK>::SIZE + OpTile<BN, BKM>::SIZE);
-    auto kern = dgemm_kernel<WM, WN, NSTAGE, AK, BKM, NEG>;
+    auto kern = dgemm_kernel<WM, WN, NSTAGE, AK, BKM, NEG, MI>;
     static bool configured = false;
     if (!configured) {
         CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -279,19 +280,19 @@ int launch_cfg(isdf_handle* h, const GemmParams& p)
     return ISDF_OK;
 }
 
-template <int WM, int WN, int NSTAGE>
+template <int WM, int WN, int NSTAGE, int MI>
 int dispatch_layout(isdf_handle* h, const GemmParams& p)
 {
     const int key = (p.a_kmajor ? 4 : 0) | (p.b_kmajor ? 2 : 0) | (p.neg ? 1 : 0);
     switch (key) {
-    case 0: return launch_cfg<WM, WN, NSTAGE, false, false, false>(h, p);
-    case 1: return launch_cfg<WM, WN, NSTAGE, false, false, true>(h, p);
-    case 2: return launch_cfg<WM, WN, NSTAGE, false, true, false>(h, p);
-    case 3: return launch_cfg<WM, WN, NSTAGE, false, true, true>(h, p);
-    case 4: return launch_cfg<WM, WN, NSTAGE, true, false, false>(h, p);
-    case 5: return launch_cfg<WM, WN, NSTAGE, true, false, true>(h, p);
-    case 6: return launch_cfg<WM, WN, NSTAGE, true, true, false>(h, p);
-    default: return launch_cfg<WM, WN, NSTAGE, true, true, true>(h, p);
+    case 0: return launch_cfg<WM, WN, NSTAGE, false, false, false, MI>(h, p);
+    case 1: return launch_cfg<WM, WN, NSTAGE, false, false, true, MI>(h, p);
+    case 2: return launch_cfg<WM, WN, NSTAGE, false, true, false, MI>(h, p);
+    case 3: return launch_cfg<WM, WN, NSTAGE, false, true, true, MI>(h, p);
+    case 4: return launch_cfg<WM, WN, NSTAGE, true, false, false, MI>(h, p);
+    case 5: return launch_cfg<WM, WN, NSTAGE, true, false, true, MI>(h, p);
+    case 6: return launch_cfg<WM, WN, NSTAGE, true, true, false, MI>(h, p);
+    default: return launch_cfg<WM, WN, NSTAGE, true, true, true, MI>(h, p);
     }
 }
 
@@ -302,11 +303,15 @@ int gemm_launch(isdf_handle* h, const GemmParams& p)
     if (p.M <= 0 || p.N <= 0) return ISDF_OK;
     ARG_CHECK(p.A && p.B && p.C && p.K >= 0);
     ARG_CHECK(p.epi != EPI_MUL || p.E != nullptr);
-    auto tiles = [&](int bm, int bn) { return (long long)((p.M + bm - 1) / bm) * ((p.N + bn - 1) / bn); };
-    // 64x128 CTAs (up to 3 per SM) once the grid exceeds one CTA per SM, else 64x64.
-    // (A 6-stage ring for small grids was measured and bought nothing: small grids are
-    // short of CTAs, not of prefetch depth -- profiles/r01_gemm_loaders.md.)
-    if (h->gemm_force == 2 || (h->gemm_force == 0 && tiles(64, 128) > (long long)h->num_sms))
-        return dispatch_layout<1, 4, 3>(h, p);
-    return dispatch_layout<1, 2, 3>(h, p);
+    // Default: 64x64 CTAs of four 32x32 warps (128 registers, 4 CTAs per SM).  Measured against
+    // 64x128 CTAs of four 64x32 warps it is 1-5 % faster on the large streaming products and
+    // 1.5x faster on small grids, which are bound by the K loop of a single warp (one DMMA per 16
+    // clocks and sub-core): half the DMMAs per warp and K step, all four sub-cores busy
+    // (profiles/r01_gemm_loaders.md).  Tuning knob: 2 = 64x128 / 64x32 warps, 3 = 64x64 / two 64x32
+    // warps, 5 = 64x128 / eight 32x32 warps, 6 = 128x128 / sixteen 32x32 warps.
+    if (h->gemm_force == 2) return dispatch_layout<1, 4, 3, 8>(h, p);
+    if (h->gemm_force == 3) return dispatch_layout<1, 2, 3, 8>(h, p);
+    if (h->gemm_force == 5) return dispatch_layout<2, 4, 3, 4>(h, p);
+    if (h->gemm_force == 6) return dispatch_layout<4, 4, 3, 4>(h, p);
+    return dispatch_layout<2, 2, 3, 4>(h, p);
 }
