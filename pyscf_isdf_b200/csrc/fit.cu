@@ -20,11 +20,18 @@ static inline long long pad8(long long n) { return (n + 7) & ~7LL; }
 // A: [cb, cb] block inside a row-major matrix (ld); Vinv: [CB, CB] block, ld CB.
 __global__ void __launch_bounds__(256)
 chol_diag_kernel(double* __restrict__ A, long long ld, int cb, double* __restrict__ Vinv, int* __restrict__ info,
-                 int block_id, int do_factor)
+                 int block_id, int do_factor, int batched_np)
 {
     extern __shared__ double S[];      // [cb][CB+1]
     constexpr int LD = CB + 1;
     const int tid = threadIdx.x;
+    if (batched_np > 0) {              // one CTA per diagonal block of a [batched_np]^2 matrix starting at A
+        const int r0 = blockIdx.x * CB;
+        A += (long long)r0 * ld + r0;
+        Vinv += (size_t)blockIdx.x * CB * CB;
+        cb = min(CB, batched_np - r0);
+        block_id = blockIdx.x;
+    }
     for (int i = tid; i < cb * cb; i += blockDim.x) {
         const int r = i / cb, c = i - r * cb;
         S[r * LD + c] = (c >= r) ? A[(long long)r * ld + c] : 0.0;
@@ -101,7 +108,7 @@ int cholesky_upper(isdf_handle* h, double* A, long long lda_, int np, double* Vi
     for (int r0 = 0, ib = 0; r0 < np; r0 += CB, ++ib) {
         const int cb = std::min(CB, np - r0);
         double* Aii = A + (long long)r0 * lda_ + r0;
-        chol_diag_kernel<<<1, 256, smem, s>>>(Aii, lda_, cb, Vinv + (size_t)ib * CB * CB, d_info, ib, 1);
+        chol_diag_kernel<<<1, 256, smem, s>>>(Aii, lda_, cb, Vinv + (size_t)ib * CB * CB, d_info, ib, 1, 0);
         CUDA_TRY(cudaGetLastError());
         h->other_launches++;
         const int r1 = r0 + cb, nrem = np - r1;
@@ -124,13 +131,10 @@ int invert_diag_blocks(isdf_handle* h, double* U, long long ldu, int np, double*
     int rc;
     if ((rc = diag_kernel_cfg())) return rc;
     const size_t smem = sizeof(double) * CB * (CB + 1);
-    for (int r0 = 0, ib = 0; r0 < np; r0 += CB, ++ib) {
-        const int cb = std::min(CB, np - r0);
-        chol_diag_kernel<<<1, 256, smem, h->stream>>>(U + (long long)r0 * ldu + r0, ldu, cb,
-                                                      Vinv + (size_t)ib * CB * CB, d_info, ib, 0);
-        CUDA_TRY(cudaGetLastError());
-        h->other_launches++;
-    }
+    // the blocks are independent: one launch, one CTA per block
+    chol_diag_kernel<<<(np + CB - 1) / CB, 256, smem, h->stream>>>(U, ldu, 0, Vinv, d_info, 0, 0, np);
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches++;
     return ISDF_OK;
 }
 
