@@ -27,9 +27,10 @@
 // of them per stage), and ncu shows the kernel is DMMA-pipe bound either way
 // (tensor pipe 84 % active, no operand-feed stalls) -- so LDGSTS is the loader.
 //
-// Tiling: warp tile 64x32 (8x4 DMMA tiles, 64 FP64 accumulators per lane);
-// CTA tiles 64x128 (4 warps, 2 CTAs/SM; 4 warps/SM already saturate the DMMA
-// pipe, measured) and 64x64 (2 warps) for problems with few tiles.
+// Tiling: warp tile (8 MI) x 32 with MI = 4 (32x32, 32 FP64 accumulators per lane; default) or
+// MI = 8 (64x32); default CTA tile 64x64 = four 32x32 warps, 4 CTAs per SM (128 registers).
+// A sub-core retires one DMMA per 16 clocks, so small grids are bound by the K loop of one
+// warp: the 32x32 warp tile halves that path (profiles/r01_gemm_loaders.md, last table).
 #include "common.cuh"
 
 namespace {

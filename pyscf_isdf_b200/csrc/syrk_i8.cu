@@ -15,7 +15,9 @@
 // only need the 1e-8 J/K tolerance; the interpolation-point selection stays on the
 // bit-reproducible FP64 chain of gemm.cu.
 //
-// Kernel anatomy (one CTA per SM, persistent over upper-triangle 128x256 tiles):
+// Two kernels.  syrk_i8_kernel2 (default, further down): 256x256 tile per CTA, 2x2 clusters.
+// syrk_i8_kernel<CL> (first version, ISDF_SYRK_KERNEL=1), one CTA per SM, persistent over
+// upper-triangle 128x256 tiles:
 //   warp 0 (one lane)  bulk-copy producer (cp.async.bulk, the TMA unit): the digit planes are
 //                      stored pre-tiled and pre-swizzled, [plane][row block][K block] of
 //                      128 rows x 128 bytes in the SWIZZLE_128B order, so one operand block is

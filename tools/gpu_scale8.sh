@@ -12,4 +12,4 @@ d=json.loads(open('gpurun_out/scale_${w}_n$n.json').read().strip().splitlines()[
 }
 run 8 c64 2 1 ""
 run 4 c64 2 1 ""
-run 8 si216 1 1 "--no-e2e"
+# run 8 si216 1 1 "--no-e2e"
