@@ -285,14 +285,19 @@ def run_b200(args):
     h.gemm_profile(True)
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     stage_acc = {}
+    marks = []
     e0.record()
     for _ in range(args.steps):
         step_device()
         for k, v in mydf.timings.items():
             stage_acc.setdefault(k, []).append(v)
+        m = torch.cuda.Event(enable_timing=True)
+        m.record()
+        marks.append(m)
     e1.record()
     barrier()
     total_ms = e0.elapsed_time(e1)
+    each_ms = [a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks)]
     gflops, gms, gcount = h.gemm_profile_read()
     h.gemm_profile(False)
     l1 = h.launches()
@@ -360,6 +365,8 @@ def run_b200(args):
                    'n_ip': int(mydf.n_ip), 'fit': args.fit, 'wgemm': args.wgemm, 'l2': 'inputs_exceed_l2' if 8.0 * ng * nao > 126e6 else 'inputs_fit_l2',
                    'parallelism': 'single' if world == 1 else 'grid-slab x%d (all-gather/all-to-all/all-reduce over NCCL)' % world},
         'build_s': build_s, 'jk_s': jk_ms / 1e3, 'stages_ms': stages_ms,
+        'each_step_ms': each_ms,
+        'stages_ms_each': {k: [float(x) for x in v] for k, v in stage_acc.items() if k.endswith('_ms')},
         'flop_model': fm,
         'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
         'gpu_launches': int((l1[0] - l0[0]) + (l1[1] - l0[1])),

@@ -314,8 +314,9 @@ panel_kernel(SelState* st, const double* __restrict__ T, long long ldT,
              const int* __restrict__ cand, double* __restrict__ dC,
              double* __restrict__ LppT, int* __restrict__ piv_local,
              double* __restrict__ resid_out, Partial* __restrict__ partials,
-             int k0, int nbmax)
+             int k0, int nbmax, int use_smem)
 {
+    extern __shared__ double s_lpp[];          // [NB][cpb]: this CTA's columns of the panel factor (use_smem)
     __shared__ double s_row[NB];
     __shared__ Partial s_part[PANEL_THREADS / 32];
     __shared__ Partial s_best;
@@ -373,9 +374,13 @@ panel_kernel(SelState* st, const double* __restrict__ T, long long ldT,
         if (myc >= 0) {
             const int c = myc;
             double acc = Trow[c];
-            for (int j = 0; j < kk; ++j) acc = fma(-LppT[(long long)j * MCAP + c], s_row[j], acc);
+            if (use_smem)
+                for (int j = 0; j < kk; ++j) acc = fma(-s_lpp[j * cpb + tid], s_row[j], acc);
+            else
+                for (int j = 0; j < kk; ++j) acc = fma(-LppT[(long long)j * MCAP + c], s_row[j], acc);
             const double L = acc / piv;
             LppT[(long long)kk * MCAP + c] = L;
+            if (use_smem) s_lpp[kk * cpb + tid] = L;
             double dn = fma(-L, L, dC[c]);
             if (c == sc) dn = -1.0;
             dC[c] = dn;
@@ -755,8 +760,17 @@ extern "C" int isdf_select_panel(isdf_select_plan* pl, const double* blocks, int
         SelState* st = w.st; const double* T = w.T; long long ldT = MCAP; const int* cand = w.cand;
         double* dC = w.dC; double* LppT = w.LppT; int* pvl = w.piv_local; double* rs = w.resid_dev;
         Partial* pa = w.partials; int k0a = k0, nbm = nbmax;
-        void* args[] = {&st, &T, &ldT, &cand, &dC, &LppT, &pvl, &rs, &pa, &k0a, &nbm};
-        CUDA_TRY(cudaLaunchCooperativeKernel((void*)panel_kernel, dim3(PANEL_CTAS), dim3(PANEL_THREADS), args, 0, s));
+        // the CTA's own factor columns live in shared memory when they fit (cpb <= 192 candidates per CTA)
+        const int cpb = (((m + PANEL_CTAS - 1) / PANEL_CTAS) + 31) & ~31;
+        int use_smem = cpb <= 192 ? 1 : 0;
+        const size_t psmem = use_smem ? sizeof(double) * NB * cpb : 0;
+        static size_t psmem_cfg = 0;
+        if (psmem > psmem_cfg) {
+            CUDA_TRY(cudaFuncSetAttribute(panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * NB * 192)));
+            psmem_cfg = sizeof(double) * NB * 192;
+        }
+        void* args[] = {&st, &T, &ldT, &cand, &dC, &LppT, &pvl, &rs, &pa, &k0a, &nbm, &use_smem};
+        CUDA_TRY(cudaLaunchCooperativeKernel((void*)panel_kernel, dim3(PANEL_CTAS), dim3(PANEL_THREADS), args, psmem, s));
         h->other_launches++;
     }
     SelState* hst = (SelState*)h->h_pinned;
