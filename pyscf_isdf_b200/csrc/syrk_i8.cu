@@ -8,7 +8,7 @@
 // the digit planes are multiplied exactly on the tensor cores,
 //     P_g = sum_{s+t=g} q_s q_t^T          (int32, exact for (g+1)*Kc*64^2 < 2^31),
 // and C += alpha * 2^(e_i+e_j) * sum_{g<S} 2^(-12-7g) P_g is accumulated in FP64.  With
-// S = 8 the result is as accurate as an FP64 GEMM (profiles/r01_ozaki.md); the cost is
+// S = 8 the result is as accurate as an FP64 GEMM (profiles/r01_syrk_i8.md); the cost is
 // S(S+1)/2 = 36 int8 products instead of one FP64 product at 1/120 of the rate.
 //
 // It is used for the Coulomb metric W = (vol/Ng^2) Y Y^T, whose entries
