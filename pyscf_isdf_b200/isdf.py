@@ -328,6 +328,74 @@ class ISDF:
             self.comm.all_reduce_sum(vj)
         return vj
 
+    # -- hcore pieces on the same device-resident AO values ("next" row 2 of SURVEY 8f) ----------
+    def _check_gamma(self, kpts):
+        if kpts is not None and abs(np.asarray(kpts)).sum() > 1e-9:
+            raise NotImplementedError('ISDF is Gamma-point only')
+
+    def _ao_on_grid(self):
+        """AO values of this rank's grid slab: the build's copy when it was kept, else stage 1 alone."""
+        if self.aoR is not None:
+            return self.aoR, self._ld
+        h = self.handle
+        cell = self.cell
+        if self.comm is not None and self.comm.size > 1:
+            raise RuntimeError('the AO matrix was not kept (keep_aoR=False) on a sharded grid')
+        ng = int(np.prod(self.mesh))
+        ld = _lib.pad8(ng)
+        rcut, Ls = cell.ao_eval_params()
+        phi = h.empty((cell.nao_nr(), ld))
+        if ld > ng:
+            phi[:, ng:].zero_()
+        h.eval_ao(cell._atm, cell._bas, cell._env,
+                  np.ascontiguousarray(cell.lattice_vectors(), dtype=np.float64),
+                  np.asarray(cell.mesh, dtype=np.int32), Ls, rcut, 0, ng, phi, ld)
+        return phi, ld
+
+    def potential_matrix_device(self, vR):
+        """V = Phi diag(vR) Phi^T for a host vector vR[ng] (the contraction of
+        pyscf/pbc/df/fft.py:55-56 and :79-81) as a device tensor [nao, nao]; with a sharded grid every
+        rank contracts its slab and the partial matrices are summed."""
+        import torch
+        h = self.handle
+        phi, ld = self._ao_on_grid()
+        nao = phi.shape[0]
+        ng = int(np.prod(self.mesh))
+        g0, g1 = self._slab if self._slab is not None else (0, ng)
+        ngl = g1 - g0
+        ngp = _lib.pad8(ngl)
+        v = np.zeros((1, ngp))
+        v[0, :ngl] = np.asarray(vR, dtype=np.float64).reshape(-1)[g0:g1]
+        d_v = torch.from_numpy(v).pin_memory().to(h.torch_device, non_blocking=True)
+        out = h.empty((1, nao, nao))
+        h.j_from_potential(phi, ld, nao, ngl, d_v, ngp, 1, 1.0, out)
+        if self.comm is not None and self.comm.size > 1:
+            self.comm.all_reduce_sum(out)
+        return out[0]
+
+    def get_nuc(self, kpts=None):
+        """Nuclear attraction of point charges -Z, G=0 removed (FFTDF.get_nuc, pyscf/pbc/df/fft.py:39-62)."""
+        from . import pseudo
+        self._check_gamma(kpts)
+        return self.potential_matrix_device(pseudo.nuc_on_grid(self.cell, self.mesh)).cpu().numpy()
+
+    def get_pp_loc(self, kpts=None):
+        """Local part of the GTH pseudopotential matrix (pyscf/pbc/df/fft.py:70-84)."""
+        from . import pseudo
+        self._check_gamma(kpts)
+        return self.potential_matrix_device(pseudo.pp_loc_on_grid(self.cell, self.mesh)).cpu().numpy()
+
+    def get_pp(self, kpts=None):
+        """FFTDF.get_pp (pyscf/pbc/df/fft.py:64-152).  The local part runs here; the non-local
+        projector part (:86-141, analytic Fourier transforms of the AOs from libcint's ft_ao) is not
+        part of this path: cells whose species carry projectors must add it from the reference's CPU
+        code (pyscf.pbc.gto.pseudo.pp_int.get_pp_nl) -- raise rather than return a partial matrix."""
+        from . import pseudo
+        if pseudo.has_nonlocal(self.cell):
+            raise NotImplementedError('get_pp: non-local GTH projectors are outside the ISDF path; '
+                                      'use get_pp_loc() + pyscf.pbc.gto.pseudo.pp_int.get_pp_nl(cell)')
+        return self.get_pp_loc(kpts)
+
     def get_j(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None):
         return self.get_jk(dm, hermi, kpts, kpts_band, True, False, omega)[0]
 

@@ -1,0 +1,79 @@
+"""GPU: hcore pieces on the device-resident AO values ("next" row 2 of SURVEY 8f):
+ISDF.get_nuc / get_pp_loc against the oracle's restatement of FFTDF.get_nuc / get_pp local part
+(pyscf/pbc/df/fft.py:39-84).  Tolerance 1e-10 abs (one FP64 contraction over the grid).
+
+(File name sorts last: this row was added after the last GPU session of round 1.)"""
+import numpy as np
+import pytest
+from oracle import pseudo as opp
+from util import diamond_c8, he_c_cell, oracle_phi
+from pyscf_isdf_b200.cell import Cell
+from pyscf_isdf_b200.isdf import ISDF
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref(cell):
+    coords = cell.atom_coords()
+    charges = [float(z) for z in cell.atom_charges()]
+    pps = [cell._pseudo_for(cell.atom_symbol(i)) for i in range(cell.natm)]
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    ao = oracle_phi(cell).T
+    vpp = opp.potential_matrix(ao, opp.pp_loc_on_grid(a, mesh, coords, charges, pps))
+    vne = opp.potential_matrix(ao, opp.nuc_on_grid(a, mesh, coords, charges))
+    return vpp, vne
+
+
+@pytest.mark.parametrize('which', ['c8', 'he_c'])
+def test_local_potentials_match_oracle(which):
+    cell = diamond_c8([15, 14, 12], basis='gth-dzvp', jitter=0.15) if which == 'c8' else he_c_cell()
+    vpp0, vne0 = _ref(cell)
+    mydf = ISDF(cell, c=4)
+    vne = mydf.get_nuc()                      # before any build: evaluates the AO values itself
+    assert mydf.W is None
+    assert vne.shape == vne0.shape and abs(vne - vne0).max() < 1e-10
+    mydf.build()
+    vpp = mydf.get_pp_loc(np.zeros(3))
+    assert abs(vpp - vpp0).max() < 1e-10
+    assert abs(vpp - vpp.T).max() < 1e-12
+    with pytest.raises(NotImplementedError):
+        mydf.get_pp()                         # C carries non-local projectors
+    with pytest.raises(NotImplementedError):
+        mydf.get_nuc(np.array([0.1, 0, 0]))
+
+
+def test_get_pp_without_projectors_is_complete():
+    cell = Cell(atom='He 0.3 0.2 0.1; He 1.6 1.4 1.5', a=np.eye(3) * 3, basis='gth-dzvp',
+                pseudo='gth-pade', mesh=[15] * 3).build()
+    vpp0, _ = _ref(cell)
+    assert abs(ISDF(cell, c=4).get_pp() - vpp0).max() < 1e-10
+
+
+def test_sharded_local_potential():
+    """Grid sharded over 3 ranks (threads on one GPU): slab contractions summed."""
+    import threading
+    from test_dist_gpu import ThreadComm
+    cell = diamond_c8([13, 10, 12], basis='gth-szv', jitter=0.2)
+    vpp0, _ = _ref(cell)
+    n = 3
+    shared = ThreadComm.Shared(n)
+    out, err = [None] * n, []
+
+    def work(r):
+        try:
+            mydf = ISDF(cell, c=6, comm=ThreadComm(shared, r))
+            mydf.build()
+            out[r] = mydf.get_pp_loc()
+        except Exception as e:        # noqa: BLE001
+            err.append(e)
+            shared.barrier.abort()
+
+    ths = [threading.Thread(target=work, args=(r,)) for r in range(n)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join(timeout=600)
+    if err:
+        raise err[0]
+    for r in range(n):
+        assert abs(out[r] - vpp0).max() < 1e-10
