@@ -103,68 +103,129 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- CPU arm
-def cpu_sample_step(nthreads):
-    """One bounded sample of the CPU port (the NumPy/SciPy oracle): the C8 cell
-    of BASELINE configs[0] at mesh 35^3, c = 8, AO values on 1/4 of the grid.
-    Returns measured per-stage seconds and the sample's algorithmic flop counts."""
+def cpu_sample_target(cell, npts, seed=5):
+    """One bounded sample of the CPU port on the TARGET workload itself (its cell, nao, mesh, Np):
+    every stage of the NumPy/SciPy oracle is run on a slab of that workload's own arrays and the
+    slab time is multiplied by the slab count (the oracle's stages are loops over grid points,
+    pivots or aux functions, so a slab is a fixed fraction of the stage).  Returns the per-stage
+    seconds scaled to the whole workload and a description of what was run.
+
+      ao      oracle.eval_ao on ng/64 grid points of the cell                          x 64
+      select  oracle.pivot_step on ng/16 and ng/32 points at k = Np/8, 3Np/8, 5Np/8, 7Np/8 (best of
+              3 pivots each; the step cost is affine in k, so the midpoint rule is exact); the two
+              slab sizes give the per-grid-point slope, extended to the whole grid      x Np
+      fit     A = (X^T X)^2 and its Cholesky factorisation in full; B and the two triangular
+              solves on ng/256 grid points                                               x 256
+      fft     oracle.build_V (fft, coulG, ifft) of 16 aux functions on the full mesh     x Np/16
+      wgemm   zeta V^T over ng/256 grid points                                           x 256
+      jk      oracle.isdf_get_jk in full (one call)
+    """
     import oracle
-    from pyscf_isdf_b200 import workloads
-    cell = workloads.make_cell('c8')
+    import scipy.linalg
+    from oracle import isdf_ref
+    from pyscf_isdf_b200.workloads import synthetic_dm
+    rng = np.random.default_rng(seed)
     nao = cell.nao
     mesh = list(cell.mesh)
     ng = int(np.prod(mesh))
-    npts = 8 * nao
+    a = cell.lattice_vectors()
     rcut, Ls = cell.ao_eval_params()
     coords = cell.get_uniform_grids()
     t = {}
+    # stage 1 on a slab of ng/64 points spread over the cell
+    sl = np.arange(0, ng, 64)
+    ngs = len(sl)
     t0 = time.perf_counter()
-    part = oracle.eval_ao(cell._atm, cell._bas, cell._env, coords[:ng // 4], Ls, rcut)
-    t['ao'] = (time.perf_counter() - t0) * 4.0          # scaled to the whole grid
-    rest = oracle.eval_ao(cell._atm, cell._bas, cell._env, coords[ng // 4:], Ls, rcut)
-    phi = np.ascontiguousarray(np.vstack([part, rest]).T)
+    phi_s = np.ascontiguousarray(oracle.eval_ao(cell._atm, cell._bas, cell._env, coords[sl], Ls, rcut).T)
+    t['ao'] = (time.perf_counter() - t0) * (ng / ngs)
+    # stage 2: per-pivot cost on that slab with a factor of the real shape
+    # (the AO slab is repeated: the step's time does not depend on the values.  Two slab sizes,
+    # ng/32 and ng/16, separate the per-call overhead from the part that grows with the grid:
+    # a full-size step costs  T(ng/16) + slope * (ng - ng/16), the overhead counted once.)
+    phi_sel = np.ascontiguousarray(np.tile(phi_s, (1, 4)))
+    ngsel = phi_sel.shape[1]
+    half = ngsel // 2
+    Lt = np.full((npts, ngsel), 1e-3)
+    Lt_half = np.full((npts, half), 1e-3)
+    phi_half = np.ascontiguousarray(phi_sel[:, :half])
+    d = np.einsum('ig,ig->g', phi_sel, phi_sel) ** 2 + 1.0
+    d_half = d[:half].copy()
+
+    def one_step(ph, L, dd, k):
+        best = 1e30
+        for r in range(3):
+            pcol = int(rng.integers(ph.shape[1]))
+            dd[pcol] = abs(dd[pcol]) + 1.0
+            t0 = time.perf_counter()
+            int(np.argmax(dd))
+            isdf_ref.pivot_step(ph, L, dd, k, pcol)
+            best = min(best, time.perf_counter() - t0)
+        return best
+
+    per_pivot = []
+    for frac in (1, 3, 5, 7):
+        k = max(1, npts * frac // 8)
+        t_full = one_step(phi_sel, Lt, d, k)
+        t_half = one_step(phi_half, Lt_half, d_half, k)
+        slope = max(t_full - t_half, 0.0) / (ngsel - half)
+        per_pivot.append(t_full + slope * (ng - ngsel))
+    t['select'] = float(np.mean(per_pivot)) * npts
+    del Lt, Lt_half, phi_sel, phi_half
+    # stage 3 (the oracle's route: Cholesky of A, two triangular solves)
+    ipx = rng.integers(ngs, size=npts)
+    X = np.ascontiguousarray(phi_s[:, ipx])
     t0 = time.perf_counter()
-    ip, _ = oracle.select_ip(phi, npts)
-    t['select'] = time.perf_counter() - t0
+    A = X.T.dot(X) ** 2
+    t_A = time.perf_counter() - t0
+    A[np.diag_indices_from(A)] += 2.0 * np.abs(A).sum(axis=1).max()      # slab columns repeat: make it factorisable (not timed)
     t0 = time.perf_counter()
-    zeta = oracle.fit_aux(phi, ip)
-    t['fit'] = time.perf_counter() - t0
-    a = cell.lattice_vectors()
+    cfac = scipy.linalg.cholesky(A, lower=True)
+    t_chol = time.perf_counter() - t0
+    del A
+    sl3 = slice(0, max(1, ngs // 4))
+    n3 = len(range(*sl3.indices(ngs)))
     t0 = time.perf_counter()
-    V = oracle.build_V(zeta, a, mesh)
-    t['fft'] = time.perf_counter() - t0
+    B = X.T.dot(phi_s[:, sl3]) ** 2
+    y = scipy.linalg.solve_triangular(cfac, B, lower=True)
+    zeta_s = scipy.linalg.solve_triangular(cfac.T, y, lower=False)
+    t['fit'] = t_A + t_chol + (time.perf_counter() - t0) * (ng / n3)
+    del cfac, B, y
+    # stage 4: FFT + coulG + inverse FFT of 16 aux functions on the whole mesh; metric product on a slab
+    nvec = min(16, npts)
+    zfull = rng.standard_normal((nvec, ng))
     t0 = time.perf_counter()
-    W = oracle.build_W(zeta, a, mesh, V=V)
-    t['wgemm'] = time.perf_counter() - t0
-    from pyscf_isdf_b200.workloads import synthetic_dm
+    isdf_ref.build_V(zfull, a, mesh)
+    t['fft'] = (time.perf_counter() - t0) * (npts / nvec)
+    del zfull
+    V_s = rng.standard_normal(zeta_s.shape)
+    t0 = time.perf_counter()
+    W = (cell.vol / ng) * zeta_s.dot(V_s.T)
+    t['wgemm'] = (time.perf_counter() - t0) * (ng / n3)
+    del zeta_s, V_s
+    # stage 5 in full
+    W = W + W.T
     dm = synthetic_dm(nao)
-    X = np.ascontiguousarray(phi[:, ip])
     t0 = time.perf_counter()
-    for _ in range(5):
-        oracle.isdf_get_jk(X, W, dm)
-    t['jk'] = (time.perf_counter() - t0) / 5
-    dims = dict(nao=nao, ng=ng, npts=len(ip), mesh=mesh)
-    return t, dims
+    oracle.isdf_get_jk(X, W, dm)
+    t['jk'] = time.perf_counter() - t0
+    desc = ('NumPy/SciPy oracle on slabs of the workload itself: AO on ng/64 (%d points), 12 pivot steps '
+            'at k=Np/8..7Np/8 on ng/16 (%d points) and ng/32 (slope in the grid size extended to ng), full A=(X^T X)^2 + Cholesky (Np=%d), triangular solves '
+            'and metric product on ng/256 (%d points), FFT+coulG+iFFT of %d aux functions, one full J/K; '
+            'other slab times multiplied by the slab count' % (ngs, ngsel, npts, n3, nvec))
+    return t, desc
 
 
-def cpu_work(nao, ng, npts):
-    """Work units of the CPU port per stage (what its time scales with)."""
-    return {
-        'ao': 1.0 * ng * nao,
-        'select': 2.0 * ng * nao * npts + 1.0 * ng * npts ** 2,
-        'fit': 2.0 * npts * nao * ng + 2.0 * npts ** 2 * nao + npts ** 3 / 3.0 + 2.0 * npts ** 2 * ng,
-        'fft': 2.0 * 5.0 * npts * ng * np.log2(ng),
-        'wgemm': 2.0 * npts ** 2 * ng,
-        'jk': 4.0 * npts ** 2 * nao + 6.0 * npts * nao ** 2 + 2.0 * npts ** 2,
-    }
-
-
-def cpu_extrapolate(t, dims, nao, ng, npts):
-    """Scale the sample's per-stage times to the target workload by the stage's work model."""
-    ws = cpu_work(dims['nao'], dims['ng'], dims['npts'])
-    wt = cpu_work(nao, ng, npts)
-    per = {k: t[k] * wt[k] / ws[k] for k in t}
-    build = per['ao'] + per['select'] + per['fit'] + per['fft'] + per['wgemm']
-    return build + per['jk'], build, per['jk'], per
+def cpu_baseline_run(cell, npts):
+    """(total s, build s, J/K s, per-stage s, description, cores) of one bounded CPU sample."""
+    from oracle import pbc_tools
+    ncores = os.cpu_count() or 1
+    pbc_tools.FFT_WORKERS = ncores          # BLAS already uses every core; give the FFTs the same
+    try:
+        t, desc = cpu_sample_target(cell, npts)
+    finally:
+        pbc_tools.FFT_WORKERS = 1
+    build = t['ao'] + t['select'] + t['fit'] + t['fft'] + t['wgemm']
+    return build + t['jk'], build, t['jk'], t, desc, ncores
 
 
 def target_dims(args):
@@ -182,22 +243,18 @@ def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return 0
-    ncores = os.cpu_count() or 1
     from pyscf_isdf_b200 import workloads
     name, cell, nao, ng, npts = target_dims(args)
     for _ in range(args.warmup):
-        cpu_sample_step(ncores)
+        cpu_baseline_run(cell, npts)
     tot = []
     last = None
     for _ in range(args.steps):
-        t, dims = cpu_sample_step(ncores)
-        v, b, j, per = cpu_extrapolate(t, dims, nao, ng, npts)
+        v, b, j, per, desc, ncores = cpu_baseline_run(cell, npts)
         tot.append(v)
-        last = (t, b, j, per)
+        last = (desc, b, j, per)
     val = float(np.mean(tot))
-    sample = ('C8 diamond mesh 35^3 c=8 (AO on 1/4 grid) through the NumPy/SciPy oracle: measured %.1f s; '
-              'per-stage times scaled by the stage work model to %s nao=%d Ng=%d Np=%d (EXTRAPOLATED)'
-              % (sum(last[0].values()), name, nao, ng, npts))
+    sample = last[0] + ' (%s, nao=%d Ng=%d Np=%d)' % (name, nao, ng, npts)
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 's', 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': val * 1e3,
@@ -380,14 +437,9 @@ def run_b200(args):
                             'achieved_pops': ops / (stages_ms['wgemm_ms'] * 1e-3) / 1e15,
                             'fp64_equivalent_tflops': fm['coulomb_gemm'] / world / (stages_ms['wgemm_ms'] * 1e-3) / 1e12}
     if world == 1 and not args.no_cpu_baseline:
-        ncores = os.cpu_count() or 1
-        t, dims = cpu_sample_step(ncores)
-        v, b, j, per = cpu_extrapolate(t, dims, nao, ng, int(mydf.n_ip))
-        line['cpu_baseline'] = {
-            'value': v, 'unit': 's', 'cores': ncores, 'kind': 'port',
-            'sample': 'C8 diamond mesh 35^3 c=8 (AO on 1/4 grid) through the NumPy/SciPy oracle: measured %.1f s; '
-                      'per-stage times scaled by the stage work model to this workload (EXTRAPOLATED)' % sum(t.values()),
-            'build_s': b, 'jk_s': j}
+        v, b, j, per, desc, ncores = cpu_baseline_run(cell, int(mydf.n_ip))
+        line['cpu_baseline'] = {'value': v, 'unit': 's', 'cores': ncores, 'kind': 'port', 'sample': desc,
+                                'build_s': b, 'jk_s': j, 'stages_s': per}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

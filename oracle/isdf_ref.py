@@ -43,21 +43,27 @@ def select_ip(aoR, npts, tol=-1.0, return_factor=False):
         p = int(np.argmax(d))
         if d[p] <= tol:
             break
-        col = aoR.T.dot(aoR[:, p])
-        col = col * col
-        if k:
-            col -= Lt[:k].T.dot(Lt[:k, p])
-        piv = np.sqrt(d[p])
-        Lt[k] = col / piv
         resid.append(d[p])
         ip.append(p)
-        d -= Lt[k] ** 2
-        d[p] = -1.0
+        pivot_step(aoR, Lt, d, k, p)
     ip = np.array(ip, dtype=np.int64)
     resid = np.array(resid)
     if return_factor:
         return ip, resid, Lt[:len(ip)]
     return ip, resid
+
+
+def pivot_step(aoR, Lt, d, k, p):
+    """Step k of the pivoted Cholesky with pivot p: new factor row, residual update
+    (pyscf/lib/scipy_helper.py:97-104).  Also what bench.py times per pivot on a slab."""
+    col = aoR.T.dot(aoR[:, p])
+    col = col * col
+    if k:
+        col -= Lt[:k].T.dot(Lt[:k, p])
+    piv = np.sqrt(d[p])
+    Lt[k] = col / piv
+    d -= Lt[k] ** 2
+    d[p] = -1.0
 
 
 def fit_aux(aoR, ip):

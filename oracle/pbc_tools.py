@@ -15,12 +15,32 @@ def fp(a):
     return np.dot(np.cos(np.arange(a.size)), a.ravel())
 
 
+# Threads for the batched transforms: 1 = numpy.fft (what pyscf/pbc/tools/pbc.py:114-118 calls);
+# bench.py sets it to the host's core count for the timed CPU baseline, which switches to
+# scipy.fft (the same pocketfft algorithm, run on `workers` threads over the batch).
+FFT_WORKERS = 1
+
+
+def _fftn(x):
+    if FFT_WORKERS > 1:
+        import scipy.fft
+        return scipy.fft.fftn(x, axes=(1, 2, 3), workers=FFT_WORKERS)
+    return np.fft.fftn(x, axes=(1, 2, 3))
+
+
+def _ifftn(x):
+    if FFT_WORKERS > 1:
+        import scipy.fft
+        return scipy.fft.ifftn(x, axes=(1, 2, 3), workers=FFT_WORKERS)
+    return np.fft.ifftn(x, axes=(1, 2, 3))
+
+
 def fft(f, mesh):
     f = np.asarray(f)
     if f.size == 0:
         return np.zeros_like(f)
     f3d = f.reshape(-1, *mesh)
-    g3d = np.fft.fftn(f3d, axes=(1, 2, 3))
+    g3d = _fftn(f3d)
     ngrids = int(np.prod(mesh))
     return g3d.ravel() if f.ndim == 1 else g3d.reshape(-1, ngrids)
 
@@ -30,7 +50,7 @@ def ifft(g, mesh):
     if g.size == 0:
         return np.zeros_like(g)
     g3d = g.reshape(-1, *mesh)
-    f3d = np.fft.ifftn(g3d, axes=(1, 2, 3))
+    f3d = _ifftn(g3d)
     ngrids = int(np.prod(mesh))
     return f3d.ravel() if g.ndim == 1 else f3d.reshape(-1, ngrids)
 
