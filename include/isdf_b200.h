@@ -86,6 +86,13 @@ int isdf_select_ip(isdf_handle* h, const double* phi, int nao, long long ng, lon
 typedef struct isdf_select_plan isdf_select_plan;
 int isdf_select_max_rows(void);
 int isdf_select_panel_width(void);
+/* Which form of the pivot kernel the last isdf_select_panel call launched: 0 = cooperative grid
+ * (global-memory exchange, atomic barrier; the default), 1 = one 16-CTA cluster with DSMEM reads and
+ * the cluster barrier, 2 = one 16-CTA cluster with st.async pushes and mbarriers.  1 and 2 are
+ * requested with the environment variable ISDF_PANEL_CLUSTER and fall back to 0 when the candidate
+ * set is too large for their shared-memory layout or the device cannot host the cluster.  All three
+ * produce bit-identical pivots. */
+int isdf_select_last_panel_mode(void);
 int isdf_select_row_len(int nao, int k0);
 int isdf_select_first_quota(int nranks);
 int isdf_select_next_quota(int quota, int nb, int nbmax, int nranks);

@@ -32,6 +32,7 @@ SIGNATURES = {
                                c_vp, c_vp, c_vp, c_vp, c_sz]),
     'isdf_select_max_rows': (c_int, []),
     'isdf_select_panel_width': (c_int, []),
+    'isdf_select_last_panel_mode': (c_int, []),
     'isdf_select_row_len': (c_int, [c_int, c_int]),
     'isdf_select_first_quota': (c_int, [c_int]),
     'isdf_select_next_quota': (c_int, [c_int, c_int, c_int, c_int]),
@@ -173,6 +174,12 @@ class Handle:
         """float64 [m, 2n] (contiguous rows) -> complex128 view [m, n] (same memory)"""
         import torch
         return torch.view_as_complex(t.view(t.shape[0], t.shape[1] // 2, 2))
+
+    def from_host(self, arr):
+        """float64 host array -> device tensor (through pinned memory, asynchronous on the current stream)."""
+        import torch
+        t = torch.from_numpy(np.ascontiguousarray(arr, dtype=np.float64))
+        return t.pin_memory().to(self.torch_device, non_blocking=True)
 
     def index(self, idx):
         import torch

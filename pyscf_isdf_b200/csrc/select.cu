@@ -25,6 +25,8 @@
 #include <vector>
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
+#include <cooperative_groups.h>
 
 namespace {
 
@@ -391,6 +393,241 @@ panel_kernel(SelState* st, const double* __restrict__ T, long long ldT,
     if (gtid == 0) { st->nb_eff = kk; st->stop = stop; }
 }
 
+// Same panel factorisation with the PANEL_CTAS CTAs launched as ONE thread-block cluster
+// (opt-in cluster size 16): the per-pivot exchange goes through distributed shared memory
+// and the hardware cluster barrier instead of global memory and an atomic spin barrier.
+//   * every CTA pushes its local best into slot [parity][rank] of EVERY CTA's table, so after
+//     the barrier the reduction over CTAs is a local shared-memory loop that all threads run
+//     redundantly (same data, same order -> same winner in every CTA);
+//   * the winner's earlier panel columns (what the FMA chain multiplies by) are read from the
+//     owning CTA's shared-memory copy of its factor columns (DSMEM) -- needs the shared-memory
+//     layout, i.e. cpb <= 192 candidates per CTA (the host falls back to panel_kernel otherwise);
+//   * residuals of the owned candidate live in a register.
+// The arithmetic (argmax rule, tie-break, FMA chain order, division) is that of panel_kernel,
+// statement for statement, so the pivots and LppT are bit-identical.  Opt-in: ISDF_PANEL_CLUSTER=1.
+__global__ void __launch_bounds__(PANEL_THREADS)
+panel_cluster_kernel(SelState* st, const double* __restrict__ T, long long ldT,
+                     const int* __restrict__ cand, double* __restrict__ dC,
+                     double* __restrict__ LppT, int* __restrict__ piv_local,
+                     double* __restrict__ resid_out, int k0, int nbmax)
+{
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    extern __shared__ double s_lpp[];          // [NB][cpb]: this CTA's columns of the panel factor
+    __shared__ double s_row[NB];
+    __shared__ Partial s_part[PANEL_THREADS / 32];
+    __shared__ Partial s_all[2][PANEL_CTAS];   // [parity][cluster rank]: filled remotely by every CTA
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const unsigned int crank = cluster.block_rank();          // == blockIdx.x (one cluster spans the grid)
+    const int m = st->m;
+    const int cpb = (((m + PANEL_CTAS - 1) / PANEL_CTAS) + 31) & ~31;
+    const int myc = (tid < cpb && (int)crank * cpb + tid < m) ? (int)crank * cpb + tid : -1;
+    const double tol = st->tol;
+    const double theta = st->theta_key ? __longlong_as_double((long long)st->theta_key) : 0.0;
+    double myd = myc >= 0 ? dC[myc] : 0.0;
+    const int myg = myc >= 0 ? cand[myc] : 0x7fffffff;
+    int kk = 0;
+    int stop = 0;
+    cluster.sync();                              // every CTA of the cluster is resident before the first remote store
+    for (; kk < nbmax; ++kk) {
+        // ---- argmax over owned candidates (ties -> lowest grid index) ----
+        double bv = -1e300; int bg = 0x7fffffff, bc = -1;
+        if (myc >= 0 && better(myd, myg, bv, bg)) { bv = myd; bg = myg; bc = myc; }
+        for (int o = 16; o > 0; o >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int og = __shfl_xor_sync(0xffffffffu, bg, o);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            if (better(ov, og, bv, bg)) { bv = ov; bg = og; bc = oc; }
+        }
+        if (lane == 0) { s_part[wid].v = bv; s_part[wid].gidx = bg; s_part[wid].cidx = bc; }
+        __syncthreads();
+        if (wid == 0) {
+            // every lane folds the warp partials in the same order, lane r < PANEL_CTAS pushes the
+            // CTA's best into CTA r's table
+            bv = s_part[0].v; bg = s_part[0].gidx; bc = s_part[0].cidx;
+            for (int w = 1; w < PANEL_THREADS / 32; ++w)
+                if (better(s_part[w].v, s_part[w].gidx, bv, bg)) { bv = s_part[w].v; bg = s_part[w].gidx; bc = s_part[w].cidx; }
+            if (lane < PANEL_CTAS) {
+                Partial* remote = cluster.map_shared_rank(&s_all[kk & 1][crank], lane);
+                Partial p; p.v = bv; p.gidx = bg; p.cidx = bc;
+                *remote = p;
+            }
+        }
+        cluster.sync();                          // release/acquire: the remote stores are visible
+        double sv = s_all[kk & 1][0].v; int sg = s_all[kk & 1][0].gidx, sc = s_all[kk & 1][0].cidx;
+        for (int b = 1; b < PANEL_CTAS; ++b) {
+            const Partial q = s_all[kk & 1][b];
+            if (better(q.v, q.gidx, sv, sg)) { sv = q.v; sg = q.gidx; sc = q.cidx; }
+        }
+        if (sc < 0 || !(sv > tol)) { stop = 1; break; }
+        if (kk > 0 && !(sv > theta)) break;       // certificate failed: end the panel
+        const double piv = sqrt(sv);
+        // the pivot's earlier columns of this panel, from the owning CTA's shared memory
+        const int owner = sc / cpb, oc = sc - owner * cpb;
+        const double* rl = cluster.map_shared_rank(s_lpp, owner);
+        double acc = 0.0;
+        if (myc >= 0) acc = T[(long long)sc * ldT + myc];
+        for (int j = tid; j < kk; j += blockDim.x) s_row[j] = rl[j * cpb + oc];
+        __syncthreads();
+        if (myc >= 0) {
+            for (int j = 0; j < kk; ++j) acc = fma(-s_lpp[j * cpb + tid], s_row[j], acc);
+            const double L = acc / piv;
+            LppT[(long long)kk * MCAP + myc] = L;
+            s_lpp[kk * cpb + tid] = L;
+            double dn = fma(-L, L, myd);
+            if (myc == sc) dn = -1.0;
+            myd = dn;
+        }
+        if (crank == 0 && tid == 0) { piv_local[kk] = sc; resid_out[k0 + kk] = sv; }
+        // s_row / s_part are rewritten only after the next iteration's __syncthreads / cluster.sync
+    }
+    if (myc >= 0) dC[myc] = myd;
+    if (crank == 0 && tid == 0) { st->nb_eff = kk; st->stop = stop; }
+    cluster.sync();                              // no CTA leaves while its shared memory may still be read
+}
+
+// ---- third form of the panel kernel: cluster + one-way pushes (ISDF_PANEL_CLUSTER=2) -----------
+// cluster.sync() costs a GPU-scope memory barrier per pivot (MEMBAR.ALL.GPU + L1 invalidate in SASS).
+// Here nothing is pulled and nothing is fenced: before the exchange a CTA does not know the winner, so
+// it pushes its local best (16 bytes) AND that candidate's earlier panel columns (8*kk bytes) into every
+// CTA's shared memory with st.async, each store completing bytes on the receiver's mbarrier.  A receiver
+// arms the barrier with the byte count it expects (16 senders), waits for the phase, scans the 16
+// entries and reads the winner's columns from its own shared memory.  Two buffers / two barriers
+// alternate by pivot parity; a sender can run at most one pivot ahead of the slowest CTA (it needs that
+// CTA's push of pivot kk+1, issued after the CTA's end-of-pivot __syncthreads), so a buffer is never
+// overwritten while it is still being read.  Same arithmetic as panel_kernel, statement for statement.
+constexpr int PUSH_CPB_MAX = 160;                 // factor columns [NB][cpb] + push buffers must fit 227 KB
+
+__device__ __forceinline__ unsigned int sel_smem_u32(const void* p) { return (unsigned int)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned int sel_mapa(unsigned int addr, unsigned int rank)
+{
+    unsigned int r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void sel_st_async_f64(unsigned int raddr, double v, unsigned int rbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];"
+                 :: "r"(raddr), "d"(v), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void sel_st_async_2xb64(unsigned int raddr, unsigned long long a, unsigned long long b, unsigned int rbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b64 [%0], {%1, %2}, [%3];"
+                 :: "r"(raddr), "l"(a), "l"(b), "r"(rbar) : "memory");
+}
+__device__ __forceinline__ void sel_mbar_wait(unsigned int bar, unsigned int parity)
+{
+    unsigned int ok = 0;
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) break;
+        if (clock64() - t0 > 4000000000LL) __trap();       // never hang the device on a protocol bug
+    }
+}
+
+__global__ void __launch_bounds__(PANEL_THREADS)
+panel_push_kernel(SelState* st, const double* __restrict__ T, long long ldT,
+                  const int* __restrict__ cand, double* __restrict__ dC,
+                  double* __restrict__ LppT, int* __restrict__ piv_local,
+                  double* __restrict__ resid_out, int k0, int nbmax)
+{
+    extern __shared__ double s_lpp[];                        // [NB][cpb]: this CTA's columns of the panel factor
+    __shared__ __align__(16) Partial s_tab[2][PANEL_CTAS];   // [parity][sender]
+    __shared__ __align__(16) double s_rows[2][PANEL_CTAS][NB];   // [parity][sender][earlier panel columns of its best]
+    __shared__ __align__(8) unsigned long long s_bar[2];
+    __shared__ Partial s_part[PANEL_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    unsigned int crank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+    const int m = st->m;
+    const int cpb = (((m + PANEL_CTAS - 1) / PANEL_CTAS) + 31) & ~31;
+    const int myc = (tid < cpb && (int)crank * cpb + tid < m) ? (int)crank * cpb + tid : -1;
+    const double tol = st->tol;
+    const double theta = st->theta_key ? __longlong_as_double((long long)st->theta_key) : 0.0;
+    double myd = myc >= 0 ? dC[myc] : 0.0;
+    const int myg = myc >= 0 ? cand[myc] : 0x7fffffff;
+    if (tid == 0) {
+        for (int i = 0; i < 2; ++i)
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(sel_smem_u32(&s_bar[i])), "r"(1) : "memory");
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");     // peers' barriers are initialised
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    int kk = 0;
+    int stop = 0;
+    for (; kk < nbmax; ++kk) {
+        const int par = kk & 1;
+        // ---- argmax over owned candidates (ties -> lowest grid index) ----
+        double bv = -1e300; int bg = 0x7fffffff, bc = -1;
+        if (myc >= 0 && better(myd, myg, bv, bg)) { bv = myd; bg = myg; bc = myc; }
+        for (int o = 16; o > 0; o >>= 1) {
+            const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int og = __shfl_xor_sync(0xffffffffu, bg, o);
+            const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+            if (better(ov, og, bv, bg)) { bv = ov; bg = og; bc = oc; }
+        }
+        if (lane == 0) { s_part[wid].v = bv; s_part[wid].gidx = bg; s_part[wid].cidx = bc; }
+        __syncthreads();
+        // every thread folds the warp partials in the same order: the CTA's best
+        bv = s_part[0].v; bg = s_part[0].gidx; bc = s_part[0].cidx;
+        for (int w = 1; w < PANEL_THREADS / 32; ++w)
+            if (better(s_part[w].v, s_part[w].gidx, bv, bg)) { bv = s_part[w].v; bg = s_part[w].gidx; bc = s_part[w].cidx; }
+        // ---- push the CTA's best and its earlier panel columns to all CTAs ----
+        const unsigned int bar_local = sel_smem_u32(&s_bar[par]);
+        if (tid == 0)
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                         :: "r"(bar_local), "r"((unsigned int)(PANEL_CTAS * (16 + 8 * kk))) : "memory");
+        if (tid < PANEL_CTAS) {
+            const unsigned int dst = sel_mapa(sel_smem_u32(&s_tab[par][crank]), (unsigned int)tid);
+            const unsigned int rbar = sel_mapa(bar_local, (unsigned int)tid);
+            const unsigned long long w0 = (unsigned long long)__double_as_longlong(bv);
+            const unsigned long long w1 = ((unsigned long long)(unsigned int)bc << 32) | (unsigned long long)(unsigned int)bg;   // {gidx, cidx}
+            sel_st_async_2xb64(dst, w0, w1, rbar);
+        }
+        {
+            const int tb = bc >= 0 ? bc - (int)crank * cpb : 0;
+            for (int idx = tid; idx < PANEL_CTAS * kk; idx += PANEL_THREADS) {
+                const int r = idx & (PANEL_CTAS - 1), j = idx / PANEL_CTAS;
+                const double v = bc >= 0 ? s_lpp[j * cpb + tb] : 0.0;
+                sel_st_async_f64(sel_mapa(sel_smem_u32(&s_rows[par][crank][j]), (unsigned int)r), v,
+                                 sel_mapa(bar_local, (unsigned int)r));
+            }
+        }
+        sel_mbar_wait(bar_local, (unsigned int)((kk >> 1) & 1));
+        // ---- all 16 entries are here: the winner, identically in every CTA ----
+        double sv = s_tab[par][0].v; int sg = s_tab[par][0].gidx, sc = s_tab[par][0].cidx, sb = 0;
+        for (int b = 1; b < PANEL_CTAS; ++b) {
+            const Partial q = s_tab[par][b];
+            if (better(q.v, q.gidx, sv, sg)) { sv = q.v; sg = q.gidx; sc = q.cidx; sb = b; }
+        }
+        if (sc < 0 || !(sv > tol)) { stop = 1; break; }
+        if (kk > 0 && !(sv > theta)) break;       // certificate failed: end the panel
+        const double piv = sqrt(sv);
+        if (myc >= 0) {
+            double acc = T[(long long)sc * ldT + myc];
+            const double* row = s_rows[par][sb];
+            for (int j = 0; j < kk; ++j) acc = fma(-s_lpp[j * cpb + tid], row[j], acc);
+            const double L = acc / piv;
+            LppT[(long long)kk * MCAP + myc] = L;
+            s_lpp[kk * cpb + tid] = L;
+            double dn = fma(-L, L, myd);
+            if (myc == sc) dn = -1.0;
+            myd = dn;
+        }
+        if (crank == 0 && tid == 0) { piv_local[kk] = sc; resid_out[k0 + kk] = sv; }
+        __syncthreads();          // the CTA is done with this pivot's buffers before any of its threads pushes the next
+    }
+    if (myc >= 0) dC[myc] = myd;
+    if (crank == 0 && tid == 0) { st->nb_eff = kk; st->stop = stop; }
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");     // no CTA leaves while peers may still push to it
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // LppP[k][j] = LppT[j][piv_local[k]]  (within-panel factor rows of the chosen pivots)
 __global__ void gather_lpp_kernel(const double* __restrict__ LppT, const int* __restrict__ piv_local,
                                   int nb, double* __restrict__ LppP)
@@ -615,6 +852,8 @@ extern "C" size_t isdf_select_ip_ws_bytes(int nao, long long ng, int npts)
 
 extern "C" int isdf_select_max_rows(void) { return MCAP; }
 extern "C" int isdf_select_panel_width(void) { return NB; }
+static int g_last_panel_mode = 0;
+extern "C" int isdf_select_last_panel_mode(void) { return g_last_panel_mode; }
 extern "C" int isdf_select_row_len(int nao, int k0) { return row_len(nao, k0); }
 
 // ---- stepwise interface (one slab of grid points per rank) -----------------------------------
@@ -769,8 +1008,51 @@ extern "C" int isdf_select_panel(isdf_select_plan* pl, const double* blocks, int
             CUDA_TRY(cudaFuncSetAttribute(panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * NB * 192)));
             psmem_cfg = sizeof(double) * NB * 192;
         }
-        void* args[] = {&st, &T, &ldT, &cand, &dC, &LppT, &pvl, &rs, &pa, &k0a, &nbm, &use_smem};
-        CUDA_TRY(cudaLaunchCooperativeKernel((void*)panel_kernel, dim3(PANEL_CTAS), dim3(PANEL_THREADS), args, psmem, s));
+        // opt-in: the same factorisation as one 16-CTA thread-block cluster (DSMEM exchange, hardware barrier)
+        // (the variable is read at every panel so that one process can compare the forms)
+        static int cluster_ok = -1;              // -1 attributes not set yet, 0 unavailable on this device, 1 usable
+        int cluster_mode = 0;                    // 1: DSMEM reads + cluster barrier, 2: st.async pushes + mbarrier
+        {
+            const char* e = getenv("ISDF_PANEL_CLUSTER");
+            cluster_mode = e ? atoi(e) : 0;
+            if (cluster_mode < 0 || cluster_mode > 2) cluster_mode = 0;
+        }
+        if (cluster_mode && cluster_ok < 0) {
+            cudaError_t e1 = cudaFuncSetAttribute(panel_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaError_t e2 = cudaFuncSetAttribute(panel_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  (int)(sizeof(double) * NB * 192));
+            cudaError_t e3 = cudaFuncSetAttribute(panel_push_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaError_t e4 = cudaFuncSetAttribute(panel_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  (int)(sizeof(double) * NB * PUSH_CPB_MAX));
+            cluster_ok = (e1 == cudaSuccess && e2 == cudaSuccess && e3 == cudaSuccess && e4 == cudaSuccess) ? 1 : 0;
+            if (!cluster_ok) cudaGetLastError();
+        }
+        if (cluster_ok != 1) cluster_mode = 0;
+        bool launched = false;
+        if (cluster_mode >= 1 && use_smem && (cluster_mode == 1 || cpb <= PUSH_CPB_MAX)) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(PANEL_CTAS); cfg.blockDim = dim3(PANEL_THREADS);
+            cfg.dynamicSmemBytes = psmem; cfg.stream = s;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = PANEL_CTAS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            int nclusters = 0;
+            auto kern = cluster_mode == 2 ? panel_push_kernel : panel_cluster_kernel;
+            if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) == cudaSuccess && nclusters >= 1) {
+                CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, st, T, ldT, cand, dC, LppT, pvl, rs, k0a, nbm));
+                launched = true;
+                g_last_panel_mode = cluster_mode;
+            } else {
+                cudaGetLastError();
+                cluster_ok = 0;                  // a 16-CTA cluster does not fit on this device: stay on the grid-barrier kernel
+            }
+        }
+        if (!launched) {
+            void* args[] = {&st, &T, &ldT, &cand, &dC, &LppT, &pvl, &rs, &pa, &k0a, &nbm, &use_smem};
+            CUDA_TRY(cudaLaunchCooperativeKernel((void*)panel_kernel, dim3(PANEL_CTAS), dim3(PANEL_THREADS), args, psmem, s));
+            g_last_panel_mode = 0;
+        }
         h->other_launches++;
     }
     SelState* hst = (SelState*)h->h_pinned;

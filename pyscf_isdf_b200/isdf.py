@@ -356,7 +356,6 @@ class ISDF:
         """V = Phi diag(vR) Phi^T for a host vector vR[ng] (the contraction of
         pyscf/pbc/df/fft.py:55-56 and :79-81) as a device tensor [nao, nao]; with a sharded grid every
         rank contracts its slab and the partial matrices are summed."""
-        import torch
         h = self.handle
         phi, ld = self._ao_on_grid()
         nao = phi.shape[0]
@@ -366,7 +365,7 @@ class ISDF:
         ngp = _lib.pad8(ngl)
         v = np.zeros((1, ngp))
         v[0, :ngl] = np.asarray(vR, dtype=np.float64).reshape(-1)[g0:g1]
-        d_v = torch.from_numpy(v).pin_memory().to(h.torch_device, non_blocking=True)
+        d_v = h.from_host(v)
         out = h.empty((1, nao, nao))
         h.j_from_potential(phi, ld, nao, ngl, d_v, ngp, 1, 1.0, out)
         if self.comm is not None and self.comm.size > 1:

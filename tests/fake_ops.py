@@ -155,6 +155,14 @@ class FakeOps:
     def as_complex(t):
         return torch.view_as_complex(t.view(t.shape[0], t.shape[1] // 2, 2))
 
+    def from_host(self, arr):
+        return torch.from_numpy(np.ascontiguousarray(arr, dtype=np.float64))
+
+    def j_from_potential(self, phi, ldphi, nao, ngl, vR, ldv, nset, weight, vj, ws=None):
+        P = _np(phi)[:nao, :ngl]
+        for i in range(nset):
+            vj[i] = torch.from_numpy(weight * (P * _np(vR)[i, :ngl]).dot(P.T))
+
     def index(self, idx):
         return torch.as_tensor(np.asarray(idx, dtype=np.int64))
 

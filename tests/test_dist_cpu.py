@@ -41,7 +41,9 @@ def _run_rank(comm, out=None, fit='implicit'):
     mydf.build()
     dm = rand_dm(cell.nao)
     vj, vk = dist.get_jk_device(mydf, comm, torch.from_numpy(dm[None].copy()))
-    res = dict(ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(),
+    vpp = mydf.get_pp_loc()                    # hcore local part on the rank's grid slab, summed over ranks
+    vne = mydf.get_nuc()
+    res = dict(ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(), vpp=vpp, vne=vne,
                p0=int(mydf._part.ip_off[comm.rank]),
                vj=vj.numpy()[0].copy(), vk=vk.numpy()[0].copy(), slab=mydf._slab,
                panels=mydf.timings['select_panels'])
@@ -60,6 +62,18 @@ def _check(res, tol=1e-9):
     assert abs(res['W'] - Wref).max() < 1e-8 * abs(ref['W']).max()
     assert abs(res['vj'] - vj).max() < tol * abs(vj).max()
     assert abs(res['vk'] - vk).max() < tol * abs(vk).max()
+    # local one-electron potentials (pyscf/pbc/df/fft.py:39-84) against the per-atom restatement
+    from oracle import pseudo as opp
+    from util import oracle_phi
+    coords = cell.atom_coords()
+    charges = [float(z) for z in cell.atom_charges()]
+    pps = [cell._pseudo_for(cell.atom_symbol(i)) for i in range(cell.natm)]
+    ao = oracle_phi(cell).T
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    vpp0 = opp.potential_matrix(ao, opp.pp_loc_on_grid(a, mesh, coords, charges, pps))
+    vne0 = opp.potential_matrix(ao, opp.nuc_on_grid(a, mesh, coords, charges))
+    assert abs(res['vpp'] - vpp0).max() < 1e-10
+    assert abs(res['vne'] - vne0).max() < 1e-10
 
 
 def test_partition():
