@@ -1,10 +1,12 @@
 #!/bin/bash
 # First GPU call of round 2: (1) the regular GPU suite incl. the hcore tests written at the end of
 # round 1, (2) the opt-in pivot-kernel forms (ISDF_PANEL_CLUSTER=1/2) for bit-exactness, (3) C64 bench
-# lines for form 0 / 1 / 2 with the selection breakdown, so the default can be switched on evidence.
+# lines for form 0 / 1 / 2 with the selection breakdown, (4) the fused Rader FFT (ISDF_FFT_FUSED=1): tests
+# and a C64 bench line -- so the defaults can be switched on evidence.
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_panel_forms_gpu.py -m gpu -q > gpurun_out/pytest_forms.log 2>&1; echo "forms rc=$?"; tail -15 gpurun_out/pytest_forms.log
+ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_fft_fused_gpu.py -m gpu -q > gpurun_out/pytest_fftfused.log 2>&1; echo "fft fused rc=$?"; tail -15 gpurun_out/pytest_fftfused.log
 for mode in 0 1 2; do
   ISDF_PANEL_CLUSTER=$mode ISDF_PROFILE_SELECT=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
       > gpurun_out/bench_panel$mode.json 2> gpurun_out/bench_panel$mode.err; echo "bench mode $mode rc=$?"
@@ -17,3 +19,13 @@ except Exception as e:
     print('mode $mode: no line', e)
 PY
 done
+ISDF_FFT_FUSED=1 ISDF_PROFILE_SELECT=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
+    > gpurun_out/bench_fftfused.json 2> gpurun_out/bench_fftfused.err; echo "bench fft fused rc=$?"
+python - <<PY
+import json
+try:
+    d = json.loads(open('gpurun_out/bench_fftfused.json').read().strip().splitlines()[-1])
+    print('fft fused step %.3f s' % d['value'], {k: round(v, 1) for k, v in d['stages_ms'].items()})
+except Exception as e:
+    print('fft fused: no line', e)
+PY
