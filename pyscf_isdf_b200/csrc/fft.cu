@@ -77,7 +77,7 @@ int set_smem(K kern, size_t smem)
     return ISDF_OK;
 }
 
-// launch the FUSED = false instantiation, or hand a fused plan (FftPlan::rader == 2) to fft_fused.cu
+// launch the FUSED = false instantiation, or hand a fused plan (FftPlan::rader >= 2) to fft_fused.cu
 #define FFT_RUN_Z(fused_, K_, FK_, grid_, smem_, stream_, ...)                                               \
     do {                                                                                                     \
         int rc_;                                                                                             \
@@ -141,14 +141,14 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
         const int LB = pick_lb(P.ax[2].lalloc(), fft_smem_budget(true));
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         dim3 grid((nx * ny + 2 * LB - 1) / (2 * LB), nvec);
-        FFT_RUN_Z((P.ax[2].rader == 2), fft_z_r2c_kernel, fused_z_r2c, grid, smem, s, in, ldin, spec, lds, P.ax[2], nx * ny, LB);
+        FFT_RUN_Z((P.ax[2].rader >= 2), fft_z_r2c_kernel, fused_z_r2c, grid, smem, s, in, ldin, spec, lds, P.ax[2], nx * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
     {
         const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
         dim3 grid((nzh + CH - 1) / CH, nx, nvec);
-        FFT_RUN_COLS((P.ax[1].rader == 2), 0, grid, smem, s, spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
+        FFT_RUN_COLS((P.ax[1].rader >= 2), 0, grid, smem, s, spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
         CUDA_TRY(cudaGetLastError());
     }
     {
@@ -156,9 +156,9 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
         const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncols);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
         dim3 grid((ncols + CH - 1) / CH, 1, nvec);
-        if (xmode == 1) FFT_RUN_COLS((P.ax[0].rader == 2), 1, grid, smem, s, spec, lds, 0, P.ax[0], ncols, CH, geo);
-        else if (xmode == 2) FFT_RUN_COLS((P.ax[0].rader == 2), 2, grid, smem, s, spec, lds, 0, P.ax[0], ncols, CH, geo);
-        else FFT_RUN_COLS((P.ax[0].rader == 2), 0, grid, smem, s, spec, lds, 0, P.ax[0], ncols, CH, geo);
+        if (xmode == 1) FFT_RUN_COLS((P.ax[0].rader >= 2), 1, grid, smem, s, spec, lds, 0, P.ax[0], ncols, CH, geo);
+        else if (xmode == 2) FFT_RUN_COLS((P.ax[0].rader >= 2), 2, grid, smem, s, spec, lds, 0, P.ax[0], ncols, CH, geo);
+        else FFT_RUN_COLS((P.ax[0].rader >= 2), 0, grid, smem, s, spec, lds, 0, P.ax[0], ncols, CH, geo);
         CUDA_TRY(cudaGetLastError());
     }
     h->other_launches += 3;
@@ -176,14 +176,14 @@ int inverse_yz(isdf_handle* h, const Plans& P, const int* mesh, double2* spec, l
         const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
         dim3 grid((nzh + CH - 1) / CH, nx, nvec);
-        FFT_RUN_COLS((P.ax[1].rader == 2), 3, grid, smem, s, spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
+        FFT_RUN_COLS((P.ax[1].rader >= 2), 3, grid, smem, s, spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
         CUDA_TRY(cudaGetLastError());
     }
     {
         const int LB = pick_lb(P.ax[2].lalloc(), budget);
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         dim3 grid((nx * ny + LB - 1) / LB, nvec);
-        FFT_RUN_Z((P.ax[2].rader == 2), fft_z_c2r_kernel, fused_z_c2r, grid, smem, s, spec, lds, out, ldout, P.ax[2], nx * ny, LB);
+        FFT_RUN_Z((P.ax[2].rader >= 2), fft_z_c2r_kernel, fused_z_c2r, grid, smem, s, spec, lds, out, ldout, P.ax[2], nx * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
     h->other_launches += 2;
@@ -313,14 +313,14 @@ extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int
         const int LB = pick_lb(P.ax[2].lalloc(), fft_smem_budget(true));
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         dim3 grid((nxl * ny + 2 * LB - 1) / (2 * LB), nvec);
-        FFT_RUN_Z((P.ax[2].rader == 2), fft_z_r2c_kernel, fused_z_r2c, grid, smem, s, in, ldin, (double2*)spec, lds, P.ax[2], nxl * ny, LB);
+        FFT_RUN_Z((P.ax[2].rader >= 2), fft_z_r2c_kernel, fused_z_r2c, grid, smem, s, in, ldin, (double2*)spec, lds, P.ax[2], nxl * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
     {
         const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
         dim3 grid((nzh + CH - 1) / CH, nxl, nvec);
-        FFT_RUN_COLS((P.ax[1].rader == 2), 0, grid, smem, s, (double2*)spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
+        FFT_RUN_COLS((P.ax[1].rader >= 2), 0, grid, smem, s, (double2*)spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
         CUDA_TRY(cudaGetLastError());
     }
     h->other_launches += 2;
@@ -379,7 +379,7 @@ extern "C" int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nv
     const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncl);
     const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
     dim3 grid((ncl + CH - 1) / CH, 1, nvec);
-    FFT_RUN_COLS((P.ax[0].rader == 2), 1, grid, smem, h->stream, (double2*)Y, ldy, 0, P.ax[0], ncl, CH, geo);
+    FFT_RUN_COLS((P.ax[0].rader >= 2), 1, grid, smem, h->stream, (double2*)Y, ldy, 0, P.ax[0], ncl, CH, geo);
     CUDA_TRY(cudaGetLastError());
     h->other_launches++;
     CUDA_TRY(cudaFreeAsync(P.d_tw, h->stream));

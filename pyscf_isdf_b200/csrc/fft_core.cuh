@@ -26,8 +26,9 @@ struct Radix {
 // cyclic convolution of length n-1 (composite), done with two sub-FFTs.
 struct FftPlan {
     Radix main;
-    int rader;              // 1: main.n is prime, use sub / perm / bhat;  2: the same through rader_fused_smem
-                            //    (sub is then factorised with radix 10 first; only FUSED kernels may run such a plan)
+    int rader;              // 1: main.n is prime, use sub / perm / bhat;  2: the same through rader_fused_smem (sub
+                            //    factorised by factorize_wide);  3: composite n factorised by factorize_wide.  Plans
+                            //    with rader >= 2 may only run on the FUSED kernels (fft_fused.cu)
     Radix sub;              // length n-1
     const int* perm;        // g^p mod n,      p < n-1
     const int* iperm;       // g^-q mod n,     q < n-1
@@ -59,7 +60,11 @@ __device__ __forceinline__ double2 twid(const double2* tw, int idx)
     return w;
 }
 
-// In-place small DFT of u[0..R) (R <= 7), sign SIGN
+template <int R1, int R2, int SIGN>
+__device__ __forceinline__ void dft_pair(double2* u, const double2* tw, int n);
+
+// In-place small DFT of u[0..R), sign SIGN: hand-written butterflies for R = 2, 3, 4, 5, 7, 10, two-level
+// butterflies (dft_pair) for R = 6, 8, 9, 12 (only the FUSED kernels use those), a direct sum otherwise
 template <int R, int SIGN>
 __device__ __forceinline__ void dft_small(double2* u, const double2* tw, int n)
 {
@@ -111,6 +116,14 @@ __device__ __forceinline__ void dft_small(double2* u, const double2* tw, int n)
         u[1] = cadd(m1, n1); u[6] = csub(m1, n1);
         u[2] = cadd(m2, n2); u[5] = csub(m2, n2);
         u[3] = cadd(m3, n3); u[4] = csub(m3, n3);
+    } else if (R == 6) {
+        dft_pair<2, 3, SIGN>(u, tw, n);
+    } else if (R == 8) {
+        dft_pair<2, 4, SIGN>(u, tw, n);
+    } else if (R == 9) {
+        dft_pair<3, 3, SIGN>(u, tw, n);
+    } else if (R == 12) {
+        dft_pair<3, 4, SIGN>(u, tw, n);
     } else if (R == 10) {
         // 10 = 2 x 5: two radix-5 butterflies on the even / odd inputs, then X[k], X[k+5] = E[k] +- W10^k O[k]
         double2 e[5], o[5];
@@ -141,6 +154,33 @@ __device__ __forceinline__ void dft_small(double2* u, const double2* tw, int n)
         }
 #pragma unroll
         for (int q = 0; q < R; ++q) u[q] = v[q];
+    }
+}
+
+// DFT of size R = R1 R2 in registers (Cooley-Tukey): with s = R1 j + s1 and k = k2 + R2 k1,
+//   X[k2 + R2 k1] = sum_s1 W_R1^(s1 k1) [ W_R^(s1 k2) sum_j u[R1 j + s1] W_R2^(j k2) ]
+// i.e. R1 butterflies of size R2, a twiddle from the stage's table (R divides n), R2 butterflies of size R1.
+template <int R1, int R2, int SIGN>
+__device__ __forceinline__ void dft_pair(double2* u, const double2* tw, int n)
+{
+    constexpr int R = R1 * R2;
+    double2 y[R1][R2];
+#pragma unroll
+    for (int s1 = 0; s1 < R1; ++s1) {
+#pragma unroll
+        for (int j = 0; j < R2; ++j) y[s1][j] = u[R1 * j + s1];
+        dft_small<R2, SIGN>(y[s1], tw, n);
+    }
+    const int step = n / R;
+#pragma unroll
+    for (int k2 = 0; k2 < R2; ++k2) {
+        double2 v[R1];
+#pragma unroll
+        for (int s1 = 0; s1 < R1; ++s1)
+            v[s1] = (s1 == 0 || k2 == 0) ? y[s1][k2] : cmul(y[s1][k2], twid<SIGN>(tw, s1 * k2 * step));
+        dft_small<R1, SIGN>(v, tw, n);
+#pragma unroll
+        for (int k1 = 0; k1 < R1; ++k1) u[k2 + R2 * k1] = v[k1];
     }
 }
 
@@ -227,6 +267,36 @@ __device__ double2* fft_radix_smem(double2* a, double2* b, const Radix& pl, int 
         case 5: stage_small<5, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
         case 7: stage_small<7, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
         default: stage_big<SIGN, TAG>(a, b, pl, r, p, nlines, line_stride, elem_stride, line_fast); break;
+        }
+        __syncthreads();
+        double2* tmp = a; a = b; b = tmp;
+        p *= r;
+    }
+    return a;
+}
+
+// The same driver with the wider radix set (6, 8, 9, 10, 12 on top of 2, 3, 4, 5, 7): composite lengths
+// under the FUSED kernels (plans with rader == 3, built by factorize_wide): 96 = 12 x 8 and 108 = 12 x 9
+// are two passes over shared memory instead of four.
+template <int SIGN>
+__device__ double2* fft_radix_wide_smem(double2* a, double2* b, const Radix& pl, int nlines,
+                                        int line_stride, int elem_stride, bool line_fast)
+{
+    int p = 1;
+    for (int s = 0; s < pl.nrad; ++s) {
+        const int r = pl.rad[s];
+        switch (r) {
+        case 2: stage_small<2, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 3: stage_small<3, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 4: stage_small<4, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 5: stage_small<5, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 6: stage_small<6, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 7: stage_small<7, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 8: stage_small<8, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 9: stage_small<9, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 10: stage_small<10, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        case 12: stage_small<12, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
+        default: stage_big<SIGN, 1>(a, b, pl, r, p, nlines, line_stride, elem_stride, line_fast); break;
         }
         __syncthreads();
         double2* tmp = a; a = b; b = tmp;
@@ -355,7 +425,11 @@ __device__ double2* subfft_fused(double2* a, double2* b, double2* a0, const FftP
         case 3: ISDF_FUSED_STAGE(3); break;
         case 4: ISDF_FUSED_STAGE(4); break;
         case 5: ISDF_FUSED_STAGE(5); break;
+        case 6: ISDF_FUSED_STAGE(6); break;
         case 7: ISDF_FUSED_STAGE(7); break;
+        case 8: ISDF_FUSED_STAGE(8); break;
+        case 9: ISDF_FUSED_STAGE(9); break;
+        case 12: ISDF_FUSED_STAGE(12); break;
         default: ISDF_FUSED_STAGE(10); break;
         }
 #undef ISDF_FUSED_STAGE
@@ -384,8 +458,8 @@ __device__ __forceinline__ double2* fft_smem(double2* a, double2* b, const FftPl
                                              int line_stride, int elem_stride, bool line_fast)
 {
     if constexpr (FUSED) {
-        if (pl.rader) return rader_fused_smem<SIGN>(a, b, pl, nlines, line_stride, elem_stride, line_fast);
-        return fft_radix_smem<SIGN, 1>(a, b, pl.main, nlines, line_stride, elem_stride, line_fast);
+        if (pl.rader == 2) return rader_fused_smem<SIGN>(a, b, pl, nlines, line_stride, elem_stride, line_fast);
+        return fft_radix_wide_smem<SIGN>(a, b, pl.main, nlines, line_stride, elem_stride, line_fast);
     }
     if (pl.rader) return rader_smem<SIGN>(a, b, pl, nlines, line_stride, elem_stride, line_fast);
     return fft_radix_smem<SIGN>(a, b, pl.main, nlines, line_stride, elem_stride, line_fast);
@@ -401,13 +475,48 @@ inline int factorize(int n, int* rad)
     return k;
 }
 
-// factorisation for the fused Rader path: radix 10 first, then 4/2/3/5/7; -1 if another prime factor remains
-inline int factorize_fused(int n, int* rad)
+// Factorisation for the FUSED kernels: fewest stages with radices from {12, 10, 9, 8, 7, 6, 5, 4, 3, 2}
+// (ties: the smaller largest radix, i.e. fewer registers), larger primes <= BIG_RADIX_MAX appended for the
+// direct-DFT stage.  Returns the number of stages, or -1.  `small_only`: fail instead of appending primes.
+inline int factorize_wide(int n, int* rad, bool small_only)
 {
+    int big[MAX_RAD], nbig = 0;
+    int m = n;
+    for (int p = 11; p <= m; p += 2) {
+        bool prime = true;
+        for (int q = 3; q * q <= p; q += 2) if (p % q == 0) { prime = false; break; }
+        if (!prime) continue;
+        while (m % p == 0) { if (small_only || p > BIG_RADIX_MAX || nbig >= MAX_RAD) return -1; big[nbig++] = p; m /= p; }
+    }
+    // m is now 2^a 3^b 5^c 7^d: depth-first search over the radix set (m <= 1024: tiny)
+    const int cand[10] = {12, 10, 9, 8, 7, 6, 5, 4, 3, 2};
+    int best[MAX_RAD], nbest = MAX_RAD + 1, bestmax = 1 << 30;
+    int cur[MAX_RAD];
+    struct Rec {
+        static void go(int m, int depth, int from, int curmax, int* cur, const int* cand, int* best, int& nbest, int& bestmax)
+        {
+            if (m == 1) {
+                if (depth < nbest || (depth == nbest && curmax < bestmax)) {
+                    nbest = depth; bestmax = curmax;
+                    for (int i = 0; i < depth; ++i) best[i] = cur[i];
+                }
+                return;
+            }
+            if (depth + 1 > nbest || depth >= MAX_RAD) return;
+            for (int c = from; c < 10; ++c)
+                if (m % cand[c] == 0) {
+                    cur[depth] = cand[c];
+                    go(m / cand[c], depth + 1, c, curmax > cand[c] ? curmax : cand[c], cur, cand, best, nbest, bestmax);
+                }
+        }
+    };
+    if (m > 1) Rec::go(m, 0, 0, 0, cur, cand, best, nbest, bestmax);
+    else nbest = 0;
+    if (nbest > MAX_RAD || nbest + nbig > MAX_RAD) return -1;
     int k = 0;
-    const int small[6] = {10, 4, 2, 3, 5, 7};
-    for (int f : small) while (n % f == 0 && k < MAX_RAD) { rad[k++] = f; n /= f; }
-    return n == 1 ? k : -1;
+    for (int i = 0; i < nbest; ++i) rad[k++] = best[i];
+    for (int i = 0; i < nbig; ++i) rad[k++] = big[i];
+    return k;
 }
 
 inline bool is_prime(int n)
@@ -448,8 +557,9 @@ inline void push_twiddles(std::vector<double2>& tw, int n)
 
 
 // Appends the tables of an n-point axis to tw / iv and fills everything of `pl` except the pointers.
-// Returns 0, or -1 if n has a prime factor the kernels do not support.  `fused` requests the fused
-// Rader path where it applies (prime n > 7 whose n-1 factors into 10/4/2/3/5/7).
+// Returns 0, or -1 if n has a prime factor the kernels do not support.  `fused` requests the plans of
+// the FUSED kernels where they apply: prime n > 7 whose n-1 is 2^a 3^b 5^c 7^d (rader = 2), composite n
+// that needs fewer passes with the wide radix set (rader = 3).
 inline int build_axis_tables(int n, int fused, FftPlan& pl, std::vector<double2>& tw, std::vector<int>& iv, AxisOffsets& off)
 {
     memset(&pl, 0, sizeof(pl));
@@ -467,7 +577,7 @@ inline int build_axis_tables(int n, int fused, FftPlan& pl, std::vector<double2>
         pl.sub.n = m; pl.sub.nrad = sub_nrad;
         for (int i = 0; i < sub_nrad; ++i) pl.sub.rad[i] = sub_rad[i];
         int frad[MAX_RAD];
-        const int fn = fused ? factorize_fused(m, frad) : -1;
+        const int fn = fused ? factorize_wide(m, frad, true) : -1;
         if (fn > 0) {
             pl.rader = 2;
             pl.sub.nrad = fn;
@@ -495,6 +605,15 @@ inline int build_axis_tables(int n, int fused, FftPlan& pl, std::vector<double2>
     } else {
         pl.main.nrad = factorize(n, pl.main.rad);
         if (pl.main.nrad < 0) return -1;
+        if (fused) {
+            int frad[MAX_RAD];
+            const int fn = factorize_wide(n, frad, false);
+            if (fn >= 0 && fn < pl.main.nrad) {          // fewer passes with the wide radix set
+                pl.rader = 3;
+                pl.main.nrad = fn;
+                for (int i = 0; i < fn; ++i) pl.main.rad[i] = frad[i];
+            }
+        }
     }
     return 0;
 }

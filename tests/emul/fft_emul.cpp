@@ -31,7 +31,7 @@ void run_cta(double2* a, double2* b, const FftPlan& pl, int nlines, int ls, int 
 // in / out: [nlines][n] complex (interleaved re, im).  sign -1 forward, +1 unnormalised inverse.
 // line_fast 0: every line contiguous (the z pass: stride lalloc, element stride 1);
 // line_fast 1: lines are columns of an [lalloc][nlines] matrix (the y / x passes).
-// Returns 0, -1 for an unsupported length; *used_fused = 1 if the plan took the fused Rader path.
+// Returns 0, -1 for an unsupported length; *used_fused = 2 / 3 if the plan took the fused Rader / wide-radix path.
 extern "C" int emul_fft(int n, int nlines, int sign, int fused, int line_fast, int nthreads,
                         const double* in, double* out, int* used_fused)
 {
@@ -41,7 +41,7 @@ extern "C" int emul_fft(int n, int nlines, int sign, int fused, int line_fast, i
     AxisOffsets off;
     if (build_axis_tables(n, fused, pl, tw, iv, off)) return -1;
     bind_axis_tables(pl, tw.data(), iv.data(), off);
-    *used_fused = pl.rader == 2;
+    *used_fused = pl.rader >= 2 ? pl.rader : 0;
     const int LS = pl.lalloc();
     const int ls = line_fast ? 1 : LS, es = line_fast ? nlines : 1;
     std::vector<double2> A((size_t)LS * nlines, double2{1e300, 1e300}), B((size_t)LS * nlines, double2{-1e300, 1e300});
@@ -49,7 +49,7 @@ extern "C" int emul_fft(int n, int nlines, int sign, int fused, int line_fast, i
         for (int e = 0; e < n; ++e)
             A[(size_t)l * ls + (size_t)e * es] = double2{in[2 * ((size_t)l * n + e)], in[2 * ((size_t)l * n + e) + 1]};
     double2* r = nullptr;
-    fused = pl.rader == 2;            // the host dispatch of fft.cu: FUSED kernels run fused plans only
+    fused = pl.rader >= 2;            // the host dispatch of fft.cu: FUSED kernels run fused plans only
     if (sign < 0) {
         if (fused) run_cta<-1, true>(A.data(), B.data(), pl, nlines, ls, es, line_fast != 0, nthreads, &r);
         else run_cta<-1, false>(A.data(), B.data(), pl, nlines, ls, es, line_fast != 0, nthreads, &r);
