@@ -28,6 +28,7 @@
 //   warps 2-5          epilogue: tcgen05.ld -> int32 -> FP64, scale, C += in global memory
 #include "common.cuh"
 #include "../../include/isdf_b200.h"
+#include "crt_core.cuh"
 #include <cmath>
 #include <vector>
 #include <algorithm>
@@ -161,7 +162,15 @@ struct SyrkArgs {
     double* C; long long ldc;
     const double* sc;                  // row scales 2^e_i of this chunk
     double alpha;
+    // CRT form only (syrk_i8_kernel2<true>): S = number of moduli, unit u multiplies residue plane u with
+    // itself and stores the centred residues of the int32 products as int8, R[u][row][col]
+    int8_t* R; long long ldr, res_stride;
 };
+
+// moduli and their reciprocals for the CRT form (crt_core.cuh)
+__constant__ int c_mod[isdf_crt::NM_MAX];
+__constant__ double c_invp[isdf_crt::NM_MAX];
+
 
 // CL = cluster size: the CL CTAs of a cluster own CL vertically adjacent 128x256 tiles; each
 // loads its own A block and 1/CL of the common B block, which is multicast to the whole cluster
@@ -339,6 +348,10 @@ constexpr int SMEM2 = NST2 * STAGE2 + 1024;
 constexpr int NTHREADS2 = 320;                            // producer, MMA, 8 epilogue warps
 constexpr int CT = 512;                                   // cluster tile
 
+// CRT = true: the residue form (crt_core.cuh): unit g multiplies residue plane g with itself over the
+// chunk (one product per modulus instead of g+1 per digit weight) and the epilogue stores the int32
+// accumulators reduced modulo the g-th modulus; everything else -- schedule, copies, barriers -- is shared.
+template <bool CRT>
 __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(NTHREADS2, 1)
 syrk_i8_kernel2(const SyrkArgs a)
 {
@@ -380,9 +393,9 @@ syrk_i8_kernel2(const SyrkArgs a)
                 const int8_t* arow = a.planes + (long long)(4 * tl.x + 2 * r + c) * a.rb_stride;
                 const int8_t* brow = a.planes + (long long)(4 * tl.y + 2 * c + r) * a.rb_stride;
                 for (int g = a.S - 1; g >= 0; --g)
-                    for (int s = 0; s <= g; ++s) {
+                    for (int s = CRT ? g : 0; s <= g; ++s) {
                         const int8_t* pa = arow + (long long)s * a.plane_stride;
-                        const int8_t* pb = brow + (long long)(g - s) * a.plane_stride;
+                        const int8_t* pb = brow + (long long)(CRT ? s : g - s) * a.plane_stride;
                         for (int kb = 0; kb < a.nkb; ++kb) {
                             mbar_wait(smem_u32(&bar_empty[st]), ph ^ 1);
                             const uint32_t full = smem_u32(&bar_full[st]);
@@ -407,7 +420,7 @@ syrk_i8_kernel2(const SyrkArgs a)
                 for (int g = a.S - 1; g >= 0; --g, ++unit) {
                     mbar_wait(smem_u32(&bar_tempty), (unit & 1) ^ 1);
                     tc_fence_after();
-                    const int niter = (g + 1) * a.nkb;
+                    const int niter = (CRT ? 1 : g + 1) * a.nkb;
                     for (int it = 0; it < niter; ++it) {
                         mbar_wait(smem_u32(&bar_full[st]), ph);
                         tc_fence_after();
@@ -454,6 +467,20 @@ syrk_i8_kernel2(const SyrkArgs a)
                             if (lane == 0) mbar_arrive(smem_u32(&bar_tempty));
                         }
                         const int col0 = colt + cc * 16;
+                        if constexpr (CRT) {
+                            // residues of the 16 accumulators modulo the unit's modulus, one 16-byte store
+                            // (ldr is a multiple of 16 >= n, so a chunk that starts inside the matrix fits the row)
+                            if (row < a.n && col0 + 15 >= row && col0 < a.n) {
+                                const int pm = c_mod[g];
+                                const double ipm = c_invp[g];
+                                uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+                                for (int j = 0; j < 16; ++j)
+                                    w[j >> 2] |= ((uint32_t)isdf_crt::centred_mod_rt(v[j], pm, ipm) & 0xffu) << (8 * (j & 3));
+                                *reinterpret_cast<uint4*>(a.R + (long long)g * a.res_stride + (long long)row * a.ldr + col0) =
+                                    make_uint4(w[0], w[1], w[2], w[3]);
+                            }
+                        } else
                         if (row < a.n && col0 + 15 >= row && col0 < a.n) {
                             if (col0 >= row && col0 + 16 <= a.n) {
                                 double cv[16];
@@ -600,6 +627,54 @@ __global__ void i8_split_kernel(const double* __restrict__ A, long long lda, int
     }
 }
 
+// ---- CRT form: residue planes and reconstruction (crt_core.cuh) --------------------------------
+// Residue plane m of rint(A[i, k0+k] / sc[i] * 2^bits) modulo modulus(m), same pre-tiled SWIZZLE_128B
+// layout as the digit planes (16 consecutive k per thread, one 16-byte store per plane).
+__global__ void i8_split_crt_kernel(const double* __restrict__ A, long long lda, int n, int nrows_pad, long long k0,
+                                    int kc, int kcpad, const double* __restrict__ sc, int8_t* __restrict__ planes,
+                                    long long rb_stride, long long plane_stride, int nm, int bits)
+{
+    const int groups = kcpad / 16;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)nrows_pad * groups) return;
+    const int i = (int)(idx / groups), kg = (int)(idx - (long long)i * groups) * 16;
+    uint32_t w[isdf_crt::NM_MAX][4];
+#pragma unroll
+    for (int m = 0; m < isdf_crt::NM_MAX; ++m) { w[m][0] = 0u; w[m][1] = 0u; w[m][2] = 0u; w[m][3] = 0u; }
+    if (i < n) {
+        const double mult = ldexp(1.0, bits) / sc[i];       // exact: powers of two
+        const double* src = A + (long long)i * lda + k0 + kg;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const long long x = (kg + j < kc) ? __double2ll_rn(src[j] * mult) : 0ll;
+            int8_t r[isdf_crt::NM_MAX];
+            isdf_crt::residues(x, r, isdf_crt::NM_MAX);
+#pragma unroll
+            for (int m = 0; m < isdf_crt::NM_MAX; ++m) w[m][j >> 2] |= ((uint32_t)r[m] & 0xffu) << (8 * (j & 3));
+        }
+    }
+    const int r = i & 127, c = (kg & 127) >> 4;
+    int8_t* dst = planes + (long long)(i >> 7) * rb_stride + (long long)(kg >> 7) * A_BYTES + r * 128 + ((c ^ (r & 7)) << 4);
+#pragma unroll
+    for (int m = 0; m < isdf_crt::NM_MAX; ++m)
+        if (m < nm) *reinterpret_cast<uint4*>(dst + m * plane_stride) = make_uint4(w[m][0], w[m][1], w[m][2], w[m][3]);
+}
+
+// C[row, col] += alpha sc[row] sc[col] 2^(-2 bits) x(row, col) for col >= row, x rebuilt from its nm residues
+__global__ void crt_reconstruct_kernel(const int8_t* __restrict__ R, long long ldr, long long res_stride, int nm,
+                                       int n, const double* __restrict__ sc, double f, double* __restrict__ C, long long ldc)
+{
+    const int row = blockIdx.y;
+    const int col = blockIdx.x * blockDim.x + threadIdx.x;
+    if (col >= n || col < row) return;
+    int r[isdf_crt::NM_MAX];
+    const int8_t* src = R + (long long)row * ldr + col;
+#pragma unroll
+    for (int m = 0; m < isdf_crt::NM_MAX; ++m) r[m] = m < nm ? (int)src[m * res_stride] : 0;
+    const double x = isdf_crt::reconstruct(r, nm);
+    C[(long long)row * ldc + col] += x * (f * sc[row] * sc[col]);
+}
+
 struct Chunks { int nchunks, kc_full; };
 
 Chunks plan_chunks(long long K)
@@ -636,16 +711,27 @@ int kernel_variant()
     return v;
 }
 
+// ISDF_SYRK_CRT=<moduli> (8..16, opt-in): the residue form of the product (crt_core.cuh); 0 / unset: digit planes.
+// Needs the 256x256 kernel (variant 2).
+int crt_moduli()
+{
+    const char* e = getenv("ISDF_SYRK_CRT");
+    int nm = e ? atoi(e) : 0;
+    if (nm <= 0 || kernel_variant() != 2) return 0;
+    return std::max(8, std::min(nm, (int)isdf_crt::NM_MAX));
+}
+
 int rows_padded(int n, int cl)
 {
     if (kernel_variant() == 2) return (int)align_up((size_t)n, (size_t)CT);
     return (int)align_up((size_t)n, (size_t)std::max(TN, TM * cl));
 }
 
+template <bool CRT>
 int launch_syrk2(isdf_handle* h, const SyrkArgs& a, int& nclusters)
 {
     if (nclusters == 0) {
-        CUDA_TRY(cudaFuncSetAttribute(syrk_i8_kernel2, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
+        CUDA_TRY(cudaFuncSetAttribute(syrk_i8_kernel2<CRT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
         int fit = h->num_sms / 4;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(h->num_sms / 4 * 4); cfg.blockDim = dim3(NTHREADS2); cfg.dynamicSmemBytes = SMEM2;
@@ -653,11 +739,11 @@ int launch_syrk2(isdf_handle* h, const SyrkArgs& a, int& nclusters)
         at.val.clusterDim.x = 4; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
         cfg.attrs = &at; cfg.numAttrs = 1;
         int nmax = 0;
-        if (cudaOccupancyMaxActiveClusters(&nmax, syrk_i8_kernel2, &cfg) == cudaSuccess && nmax > 0) fit = std::min(fit, nmax);
+        if (cudaOccupancyMaxActiveClusters(&nmax, syrk_i8_kernel2<CRT>, &cfg) == cudaSuccess && nmax > 0) fit = std::min(fit, nmax);
         else (void)cudaGetLastError();
         nclusters = std::max(1, std::min(fit, a.ntiles));
     }
-    syrk_i8_kernel2<<<nclusters * 4, NTHREADS2, SMEM2, h->stream>>>(a);
+    syrk_i8_kernel2<CRT><<<nclusters * 4, NTHREADS2, SMEM2, h->stream>>>(a);
     return ISDF_OK;
 }
 
@@ -694,7 +780,9 @@ extern "C" size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices)
     const Chunks c = plan_chunks(K);
     const int cl = cluster_size();
     const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
-    return align_up((size_t)nslices * (size_t)rows_padded(n, cl) * ((c.kc_full / BKB | 1) * BKB), 1024) +
+    const int nm = crt_moduli();
+    const size_t crt_extra = nm ? align_up((size_t)nm * (size_t)n * align_up((size_t)n, 16), 1024) : 0;    // residues of the products
+    return crt_extra + align_up((size_t)std::max(nslices, nm) * (size_t)rows_padded(n, cl) * ((c.kc_full / BKB | 1) * BKB), 1024) +
            align_up((size_t)(c.nchunks + 1) * n * sizeof(double), 256) + align_up((size_t)c.nchunks * sizeof(double), 256) +
            align_up((size_t)tr * tc * sizeof(int2), 256) + 2048;
 }
@@ -718,8 +806,13 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     const long long rb_stride = (long long)(ch.kc_full / BKB | 1) * A_BYTES;
     const long long plane_stride = rb_stride * (nrows_pad / TM);
     char* base = (char*)align_up((size_t)ws, 1024);
+    const int nm_max = crt_moduli();
     int8_t* planes = (int8_t*)base;
-    base += align_up((size_t)nslices * plane_stride, 1024);
+    base += align_up((size_t)std::max(nslices, nm_max) * plane_stride, 1024);
+    const long long ldr = (long long)align_up((size_t)n, 16);
+    const long long res_stride = (long long)n * ldr;
+    int8_t* resid = (int8_t*)base;                         // [nm][n][ldr] residues of one chunk's products (CRT form)
+    if (nm_max) base += align_up((size_t)nm_max * res_stride, 1024);
     double* sc_all = (double*)base;                        // [nchunks][n] row scales, then [n] row norms
     double* nrm = sc_all + (size_t)ch.nchunks * n;
     base += align_up((size_t)(ch.nchunks + 1) * n * sizeof(double), 256);
@@ -779,6 +872,17 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     }
     g_last_ops = 0.0;
     int nclusters = 0;
+    if (nm_max) {
+        static bool tables = false;
+        if (!tables) {
+            int hm[isdf_crt::NM_MAX]; double hi[isdf_crt::NM_MAX];
+            for (int k = 0; k < isdf_crt::NM_MAX; ++k) { hm[k] = isdf_crt::modulus(k); hi[k] = 1.0 / (double)hm[k]; }
+            CUDA_TRY(cudaMemcpyToSymbolAsync(c_mod, hm, sizeof(hm), 0, cudaMemcpyHostToDevice, h->stream));
+            CUDA_TRY(cudaMemcpyToSymbolAsync(c_invp, hi, sizeof(hi), 0, cudaMemcpyHostToDevice, h->stream));
+            CUDA_TRY(cudaStreamSynchronize(h->stream));    // the host copies are locals
+            tables = true;
+        }
+    }
     for (int c = 0; c < ch.nchunks; ++c) {
         const long long k0 = (long long)c * ch.kc_full;
         if (k0 >= K) break;
@@ -788,14 +892,36 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
         if (S == 0) continue;                              // below the accuracy target altogether
         const double* sc = sc_all + (size_t)c * n;
         const long long items = (long long)nrows_pad * (kcpad / 16);
+        if (nm_max) {
+            // the chunk's digit-plane count S stands for 7 S - 6 accurate bits; take the fewest moduli that carry them
+            int nm = 8;
+            while (nm < nm_max && isdf_crt::input_bits(nm) < 7 * S - 5) ++nm;
+            const int bits = isdf_crt::input_bits(nm);
+            i8_split_crt_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(
+                A, lda, n, nrows_pad, k0, kc, kcpad, sc, planes, rb_stride, plane_stride, nm, bits);
+            SyrkArgs a;
+            a.planes = planes; a.plane_stride = plane_stride; a.rb_stride = rb_stride;
+            a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = kcpad / BKB; a.S = nm;
+            a.C = C; a.ldc = ldc; a.sc = sc; a.alpha = alpha;
+            a.R = resid; a.ldr = ldr; a.res_stride = res_stride;
+            int rc;
+            if ((rc = launch_syrk2<true>(h, a, nclusters)) != ISDF_OK) return rc;
+            dim3 rg((unsigned)((n + 127) / 128), (unsigned)n);
+            crt_reconstruct_kernel<<<rg, 128, 0, h->stream>>>(resid, ldr, res_stride, nm, n, sc,
+                                                              alpha * ldexp(1.0, -2 * bits), C, ldc);
+            g_last_ops += 2.0 * nm * (double)ntiles * (double)CT * CT * (double)kcpad;
+            h->other_launches += 3;
+            continue;
+        }
         i8_split_kernel<<<(unsigned)((items + 255) / 256), 256, 0, h->stream>>>(
             A, lda, n, nrows_pad, k0, kc, kcpad, sc, planes, rb_stride, plane_stride, S);
         SyrkArgs a;
         a.planes = planes; a.plane_stride = plane_stride; a.rb_stride = rb_stride;
         a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = kcpad / BKB; a.S = S;
         a.C = C; a.ldc = ldc; a.sc = sc; a.alpha = alpha;
+        a.R = nullptr; a.ldr = 0; a.res_stride = 0;
         int rc;
-        if (variant == 2) rc = launch_syrk2(h, a, nclusters);
+        if (variant == 2) rc = launch_syrk2<false>(h, a, nclusters);
         else switch (cl) {
         case 1: rc = launch_syrk<1>(h, a, nclusters); break;
         case 2: rc = launch_syrk<2>(h, a, nclusters); break;

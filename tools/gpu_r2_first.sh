@@ -1,11 +1,12 @@
 #!/bin/bash
 # First GPU call of round 2: (1) the regular GPU suite incl. the hcore tests written at the end of
 # round 1, (2) the opt-in pivot-kernel forms (ISDF_PANEL_CLUSTER=1/2) for bit-exactness, (3) C64 bench
-# lines for form 0 / 1 / 2 with the selection breakdown, (4) the fused Rader FFT (ISDF_FFT_FUSED=1): tests
-# and a C64 bench line -- so the defaults can be switched on evidence.
+# lines for form 0 / 1 / 2 with the selection breakdown, (4) the fused Rader FFT (ISDF_FFT_FUSED=1) and (5) the CRT form of the int8
+# metric product (ISDF_SYRK_CRT=16): tests and a C64 bench line each -- so the defaults can be switched on evidence.
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_panel_forms_gpu.py -m gpu -q > gpurun_out/pytest_forms.log 2>&1; echo "forms rc=$?"; tail -15 gpurun_out/pytest_forms.log
+ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_syrk_crt_gpu.py -m gpu -q > gpurun_out/pytest_crt.log 2>&1; echo "crt rc=$?"; tail -15 gpurun_out/pytest_crt.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_fft_fused_gpu.py -m gpu -q > gpurun_out/pytest_fftfused.log 2>&1; echo "fft fused rc=$?"; tail -15 gpurun_out/pytest_fftfused.log
 for mode in 0 1 2; do
   ISDF_PANEL_CLUSTER=$mode ISDF_PROFILE_SELECT=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
@@ -28,4 +29,14 @@ try:
     print('fft fused step %.3f s' % d['value'], {k: round(v, 1) for k, v in d['stages_ms'].items()})
 except Exception as e:
     print('fft fused: no line', e)
+PY
+ISDF_SYRK_CRT=16 ISDF_SYRK_VERBOSE=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
+    > gpurun_out/bench_crt.json 2> gpurun_out/bench_crt.err; echo "bench crt rc=$?"; grep -m2 isdf_syrk gpurun_out/bench_crt.err
+python - <<PY
+import json
+try:
+    d = json.loads(open('gpurun_out/bench_crt.json').read().strip().splitlines()[-1])
+    print('crt step %.3f s' % d['value'], {k: round(v, 1) for k, v in d['stages_ms'].items()}, d.get('wgemm_i8'))
+except Exception as e:
+    print('crt: no line', e)
 PY
