@@ -122,4 +122,69 @@ __host__ __device__ inline double reconstruct(const int* r, int nm)
     return s;
 }
 
+// ---- the two element-wise kernels of the CRT form, as per-item routines (kernels in syrk_i8.cu) ----
+// Operand blocks are stored pre-tiled in the SWIZZLE_128B order the tensor-core descriptors expect:
+// block (i / 128, k / 128) is 16 KiB contiguous, row r of a block at r * 128 bytes, its 16-byte chunk c
+// at position c ^ (r & 7)  (same layout as the digit planes of i8_split_kernel).
+constexpr int BLOCK_BYTES = 128 * 128;
+
+// residue plane K-1 of 16 scaled integers: four packed words, one 16-byte store (planes one after the
+// other, so that only the 16 integers stay live)
+template <int K>
+struct PlaneLoop {
+    __host__ __device__ static inline void run(const long long* x, int8_t* dst, long long plane_stride, int nm)
+    {
+        PlaneLoop<K - 1>::run(x, dst, plane_stride, nm);
+        if (K - 1 < nm) {
+            uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                w[j >> 2] |= ((uint32_t)centred_mod<modulus(K - 1)>(x[j]) & 0xffu) << (8 * (j & 3));
+            uint32_t* o = reinterpret_cast<uint32_t*>(dst + (long long)(K - 1) * plane_stride);     // 16-byte aligned
+            o[0] = w[0]; o[1] = w[1]; o[2] = w[2]; o[3] = w[3];
+        }
+    }
+};
+template <>
+struct PlaneLoop<0> {
+    __host__ __device__ static inline void run(const long long*, int8_t*, long long, int) {}
+};
+
+// item idx = (row i, group of 16 consecutive k): residue plane m of rint(A[i, k0+k] / sc[i] * 2^bits)
+// modulo modulus(m); rows >= n and columns >= kc are written as zeros
+__host__ __device__ inline void split_item(long long idx, const double* A, long long lda, int n, int nrows_pad,
+                                           long long k0, int kc, int kcpad, const double* sc, int8_t* planes,
+                                           long long rb_stride, long long plane_stride, int nm, int bits)
+{
+    const int groups = kcpad / 16;
+    if (idx >= (long long)nrows_pad * groups) return;
+    const int i = (int)(idx / groups), kg = (int)(idx - (long long)i * groups) * 16;
+    long long x[16];
+    if (i < n) {
+        const double mult = ldexp(1.0, bits) / sc[i];       // exact: powers of two
+        const double* src = A + (long long)i * lda + k0 + kg;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) x[j] = (kg + j < kc) ? llrint(src[j] * mult) : 0ll;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) x[j] = 0ll;
+    }
+    const int r = i & 127, c = (kg & 127) >> 4;
+    int8_t* dst = planes + (long long)(i >> 7) * rb_stride + (long long)(kg >> 7) * BLOCK_BYTES + r * 128 + ((c ^ (r & 7)) << 4);
+    PlaneLoop<NM_MAX>::run(x, dst, plane_stride, nm);
+}
+
+// item (row, col), col >= row: C[row, col] += f sc[row] sc[col] x, x rebuilt from R[m][row][col]
+__host__ __device__ inline void reconstruct_item(int row, int col, const int8_t* R, long long ldr, long long res_stride,
+                                                 int nm, int n, const double* sc, double f, double* C, long long ldc)
+{
+    if (col >= n || col < row) return;
+    int r[NM_MAX];
+    const int8_t* src = R + (long long)row * ldr + col;
+#pragma unroll
+    for (int m = 0; m < NM_MAX; ++m) r[m] = m < nm ? (int)src[m * res_stride] : 0;
+    const double x = reconstruct(r, nm);
+    C[(long long)row * ldc + col] += x * (f * sc[row] * sc[col]);
+}
+
 }  // namespace isdf_crt

@@ -630,49 +630,19 @@ __global__ void i8_split_kernel(const double* __restrict__ A, long long lda, int
 // ---- CRT form: residue planes and reconstruction (crt_core.cuh) --------------------------------
 // Residue plane m of rint(A[i, k0+k] / sc[i] * 2^bits) modulo modulus(m), same pre-tiled SWIZZLE_128B
 // layout as the digit planes (16 consecutive k per thread, one 16-byte store per plane).
-__global__ void i8_split_crt_kernel(const double* __restrict__ A, long long lda, int n, int nrows_pad, long long k0,
+__global__ void __launch_bounds__(256, 3) i8_split_crt_kernel(const double* __restrict__ A, long long lda, int n, int nrows_pad, long long k0,
                                     int kc, int kcpad, const double* __restrict__ sc, int8_t* __restrict__ planes,
                                     long long rb_stride, long long plane_stride, int nm, int bits)
 {
-    const int groups = kcpad / 16;
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= (long long)nrows_pad * groups) return;
-    const int i = (int)(idx / groups), kg = (int)(idx - (long long)i * groups) * 16;
-    uint32_t w[isdf_crt::NM_MAX][4];
-#pragma unroll
-    for (int m = 0; m < isdf_crt::NM_MAX; ++m) { w[m][0] = 0u; w[m][1] = 0u; w[m][2] = 0u; w[m][3] = 0u; }
-    if (i < n) {
-        const double mult = ldexp(1.0, bits) / sc[i];       // exact: powers of two
-        const double* src = A + (long long)i * lda + k0 + kg;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const long long x = (kg + j < kc) ? __double2ll_rn(src[j] * mult) : 0ll;
-            int8_t r[isdf_crt::NM_MAX];
-            isdf_crt::residues(x, r, isdf_crt::NM_MAX);
-#pragma unroll
-            for (int m = 0; m < isdf_crt::NM_MAX; ++m) w[m][j >> 2] |= ((uint32_t)r[m] & 0xffu) << (8 * (j & 3));
-        }
-    }
-    const int r = i & 127, c = (kg & 127) >> 4;
-    int8_t* dst = planes + (long long)(i >> 7) * rb_stride + (long long)(kg >> 7) * A_BYTES + r * 128 + ((c ^ (r & 7)) << 4);
-#pragma unroll
-    for (int m = 0; m < isdf_crt::NM_MAX; ++m)
-        if (m < nm) *reinterpret_cast<uint4*>(dst + m * plane_stride) = make_uint4(w[m][0], w[m][1], w[m][2], w[m][3]);
+    isdf_crt::split_item(idx, A, lda, n, nrows_pad, k0, kc, kcpad, sc, planes, rb_stride, plane_stride, nm, bits);
 }
 
 // C[row, col] += alpha sc[row] sc[col] 2^(-2 bits) x(row, col) for col >= row, x rebuilt from its nm residues
 __global__ void crt_reconstruct_kernel(const int8_t* __restrict__ R, long long ldr, long long res_stride, int nm,
                                        int n, const double* __restrict__ sc, double f, double* __restrict__ C, long long ldc)
 {
-    const int row = blockIdx.y;
-    const int col = blockIdx.x * blockDim.x + threadIdx.x;
-    if (col >= n || col < row) return;
-    int r[isdf_crt::NM_MAX];
-    const int8_t* src = R + (long long)row * ldr + col;
-#pragma unroll
-    for (int m = 0; m < isdf_crt::NM_MAX; ++m) r[m] = m < nm ? (int)src[m * res_stride] : 0;
-    const double x = isdf_crt::reconstruct(r, nm);
-    C[(long long)row * ldc + col] += x * (f * sc[row] * sc[col]);
+    isdf_crt::reconstruct_item((int)blockIdx.y, (int)(blockIdx.x * blockDim.x + threadIdx.x), R, ldr, res_stride, nm, n, sc, f, C, ldc);
 }
 
 struct Chunks { int nchunks, kc_full; };

@@ -123,3 +123,73 @@ def test_whole_scheme_matches_exact_product(crt):
     ref = (A.astype(np.longdouble)).dot(A.astype(np.longdouble).T).astype(np.float64)
     norms = np.sqrt((A * A).sum(axis=1))
     assert (abs(C - ref) / np.outer(norms, norms)).max() < 1e-15
+
+
+def _read_plane(planes, m, plane_stride, rb_stride, nrows_pad, kcpad):
+    """Undo the pre-tiled SWIZZLE_128B layout documented in crt_core.cuh / syrk_i8.cu: block (i/128, k/128)
+    is 16 KiB contiguous, row r at r*128 bytes, 16-byte chunk c at position c ^ (r & 7)."""
+    out = np.zeros((nrows_pad, kcpad), dtype=np.int64)
+    base = m * plane_stride
+    for i in range(nrows_pad):
+        r = i & 127
+        for kg in range(0, kcpad, 16):
+            c = (kg & 127) >> 4
+            off = base + (i >> 7) * rb_stride + (kg >> 7) * 16384 + r * 128 + ((c ^ (r & 7)) << 4)
+            out[i, kg:kg + 16] = planes[off:off + 16]
+    return out
+
+
+@pytest.mark.parametrize('nm', [16, 12])
+def test_kernel_item_routines_end_to_end(crt, nm):
+    """i8_split_crt_kernel -> (numpy in place of the tensor cores: exact integer products of the residue
+    planes read back through the documented layout, reduced like the epilogue) -> crt_reconstruct_kernel,
+    on a ragged case (n, kc not multiples of the block sizes, k0 > 0, padded leading dimensions)."""
+    lib = crt
+    p = _moduli(lib)
+    rng = np.random.default_rng(3 + nm)
+    n, K, k0, kc = 150, 700, 64, 333
+    lda = K + 5
+    A = np.zeros((n, lda))
+    A[:, :K] = rng.standard_normal((n, K)) * np.exp(2 * rng.standard_normal((n, 1)))
+    A[7] = 0.0                                                     # an all-zero row
+    chunk = A[:, k0:k0 + kc]
+    mx = abs(chunk).max(axis=1)
+    sc = np.where(mx > 0, 2.0 ** (np.floor(np.log2(np.where(mx > 0, mx, 1.0))) + 1), 1.0)   # max = m 2^e, m in [0.5, 1)
+    bits = lib.crt_input_bits(nm)
+    nrows_pad, kcpad = 512, 384                                    # multiples of 512 rows / 128 bytes
+    rb_stride = (kcpad // 128 | 1) * 16384
+    plane_stride = rb_stride * (nrows_pad // 128)
+    planes = np.full(nm * plane_stride, 77, dtype=np.int8)
+    lib.crt_split_all.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_int, ctypes.c_longlong,
+                                  ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_longlong,
+                                  ctypes.c_longlong, ctypes.c_int, ctypes.c_int]
+    lib.crt_split_all(A.ctypes.data, lda, n, nrows_pad, k0, kc, kcpad, sc.ctypes.data, planes.ctypes.data,
+                      rb_stride, plane_stride, nm, bits)
+    ldr = (n + 15) // 16 * 16
+    res_stride = n * ldr
+    R = np.zeros(nm * res_stride, dtype=np.int8)
+    X = np.rint(chunk / sc[:, None] * 2.0 ** bits).astype(np.int64)
+    for m in range(nm):
+        Pm = _read_plane(planes, m, plane_stride, rb_stride, nrows_pad, kcpad)
+        assert not Pm[n:].any() and not Pm[:, kc:].any()           # padding rows / columns are zero
+        assert ((Pm[:n, :kc] - X) % p[m] == 0).all() and abs(Pm).max() <= 128
+        acc = Pm[:n].dot(Pm[:n].T)                                   # what the int8 MMAs accumulate (exact in int32)
+        assert abs(acc).max() < 2**31
+        red = np.array([[lib.crt_centred_mod_rt(int(v), p[m]) for v in row] for row in acc], dtype=np.int8)
+        R[m * res_stride:(m + 1) * res_stride].reshape(n, ldr)[:, :n] = red
+    ldc = n + 3
+    C = np.zeros((n, ldc))
+    C[:, n:] = 7.0                                                 # padding columns must stay untouched
+    alpha = 0.37
+    lib.crt_reconstruct_all.argtypes = [ctypes.c_void_p, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_int, ctypes.c_int,
+                                        ctypes.c_void_p, ctypes.c_double, ctypes.c_void_p, ctypes.c_longlong]
+    lib.crt_reconstruct_all(R.ctypes.data, ldr, res_stride, nm, n, sc.ctypes.data,
+                            alpha * 2.0 ** (-2 * bits), C.ctypes.data, ldc)
+    ref = alpha * chunk.astype(np.longdouble).dot(chunk.astype(np.longdouble).T).astype(np.float64)
+    got = C[:, :n]
+    iu = np.triu_indices(n)
+    norms = np.sqrt((chunk * chunk).sum(axis=1))
+    scale = np.outer(norms, norms)[iu] + 1e-300
+    tol = 1e-15 if nm == 16 else 2.0 ** (-bits + 2)
+    assert (abs(got[iu] - ref[iu]) / scale).max() < tol
+    assert (C[:, n:] == 7.0).all() and (np.tril(got, -1) == 0).all()      # only the upper triangle is touched
