@@ -100,3 +100,22 @@ def test_cell_model_matches_reference_conventions():
     assert sup.natm == 64 and sup.nao == 832 and list(sup.mesh) == [71, 71, 71]
     coords = cell.get_uniform_grids([4, 4, 4])
     assert coords.shape == (64, 3) and abs(coords[1] - [0, 0, L / 4]).max() < 1e-12
+
+
+def test_reference_arm_prints_the_contract_line():
+    """bench.py --impl reference (the CPU oracle arm) on the smoke workload: one JSON line with the keys
+    the driver reads, a bounded sample described in cpu_baseline, no GPU involved."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, 'bench.py'), '--impl', 'reference', '--workload', 'c8-small',
+                          '--steps', '1', '--warmup', '0', '--c', '6'], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    for key in ('impl', 'metric', 'value', 'unit', 'n_gpus', 'steps', 'warmup', 'ms_per_step', 'higher_is_better',
+                'scaling', 'vs_baseline', 'dtype', 'data', 'config', 'cpu_baseline', 'e2e'):
+        assert key in line, key
+    assert line['impl'] == 'reference' and line['higher_is_better'] is False and line['value'] > 0
+    assert line['cpu_baseline']['kind'] == 'port' and line['cpu_baseline']['cores'] >= 1
+    assert line['e2e']['h2d_bytes_per_step'] == 0 and 'workload' in line['config']
