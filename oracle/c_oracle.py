@@ -14,6 +14,8 @@ def lib():
             raise RuntimeError('C oracle not built: run `make -C oracle/c` (or __graft_entry__.build())')
         _lib = ctypes.CDLL(_PATH)
         _lib.oracle_select_ip.restype = ctypes.c_long
+        _lib.oracle_select_ip_exact.restype = ctypes.c_long
+        _lib.oracle_recon_parts.restype = ctypes.c_double
     return _lib
 
 
@@ -34,6 +36,28 @@ def select_ip_chain(aoR, npts, tol=-1.0, return_factor=False):
     if return_factor:
         return ip[:rank].copy(), resid[:rank].copy(), Lt[:rank]
     return ip[:rank].copy(), resid[:rank].copy()
+
+
+def select_ip_exact(aoR, npts, tol=-1.0, return_factor=False):
+    """PROTOTYPE: the selection with exact fixed-point long sums
+    (oracle/c/isdf_oracle_exact.c); same interface as select_ip_chain."""
+    aoR = np.ascontiguousarray(aoR, dtype=np.float64)
+    nao, ng = aoR.shape
+    Lt = np.zeros((npts, ng))
+    ip = np.zeros(npts, dtype=np.int64)
+    resid = np.zeros(npts)
+    rank = lib().oracle_select_ip_exact(_p(aoR), ctypes.c_int(nao), ctypes.c_long(ng), ctypes.c_long(ng),
+                                        ctypes.c_int(npts), ctypes.c_double(tol), _p(Lt), ctypes.c_long(ng),
+                                        _p(ip), _p(resid))
+    if return_factor:
+        return ip[:rank].copy(), resid[:rank].copy(), Lt[:rank]
+    return ip[:rank].copy(), resid[:rank].copy()
+
+
+def recon_int(value):
+    """R(S) of the exact-arithmetic prototype for a Python integer |S| < 2^124."""
+    hi, lo = divmod(int(value), 1 << 64)
+    return lib().oracle_recon_parts(ctypes.c_longlong(hi), ctypes.c_ulonglong(lo))
 
 
 def gemm_chain(A, a_kmajor, B, b_kmajor, Cin=None, E=None, alpha=1.0, neg=0, epi=0):

@@ -118,7 +118,7 @@ __host__ __device__ inline double reconstruct(const int* r, int nm)
     double s = 0.0;
 #pragma unroll
     for (int k = NM_MAX - 1; k >= 0; --k)
-        if (k < nm) s = s * (double)modulus(k) + (double)d[k];
+        if (k < nm) s = fma(s, (double)modulus(k), (double)d[k]);      // explicit: the same bits on host and device
     return s;
 }
 

@@ -7,6 +7,7 @@
 using std::ldexp;
 using std::llrint;
 using std::rint;
+using std::fma;
 #include "../../pyscf_isdf_b200/csrc/crt_core.cuh"
 
 extern "C" int crt_modulus(int k) { return isdf_crt::modulus(k); }
