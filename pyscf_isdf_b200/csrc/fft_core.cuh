@@ -275,9 +275,9 @@ __device__ double2* fft_radix_smem(double2* a, double2* b, const Radix& pl, int 
     return a;
 }
 
-// The same driver with the wider radix set (6, 8, 9, 10, 12 on top of 2, 3, 4, 5, 7): composite lengths
-// under the FUSED kernels (plans with rader == 3, built by factorize_wide): 96 = 12 x 8 and 108 = 12 x 9
-// are two passes over shared memory instead of four.
+// The same driver with the wider radix set (6, 8, 10 on top of 2, 3, 4, 5, 7): composite lengths under the
+// FUSED kernels (plans with rader == 3, built by factorize_wide): 96 = 8 x 6 x 2 and 108 = 6 x 6 x 3 are three
+// passes over shared memory instead of four, 64 = 8 x 8 two instead of three.
 template <int SIGN>
 __device__ double2* fft_radix_wide_smem(double2* a, double2* b, const Radix& pl, int nlines,
                                         int line_stride, int elem_stride, bool line_fast)
@@ -293,9 +293,7 @@ __device__ double2* fft_radix_wide_smem(double2* a, double2* b, const Radix& pl,
         case 6: stage_small<6, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
         case 7: stage_small<7, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
         case 8: stage_small<8, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
-        case 9: stage_small<9, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
         case 10: stage_small<10, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
-        case 12: stage_small<12, SIGN>(a, b, pl, p, nlines, line_stride, elem_stride, line_fast); break;
         default: stage_big<SIGN, 1>(a, b, pl, r, p, nlines, line_stride, elem_stride, line_fast); break;
         }
         __syncthreads();
@@ -428,8 +426,6 @@ __device__ double2* subfft_fused(double2* a, double2* b, double2* a0, const FftP
         case 6: ISDF_FUSED_STAGE(6); break;
         case 7: ISDF_FUSED_STAGE(7); break;
         case 8: ISDF_FUSED_STAGE(8); break;
-        case 9: ISDF_FUSED_STAGE(9); break;
-        case 12: ISDF_FUSED_STAGE(12); break;
         default: ISDF_FUSED_STAGE(10); break;
         }
 #undef ISDF_FUSED_STAGE
@@ -475,7 +471,9 @@ inline int factorize(int n, int* rad)
     return k;
 }
 
-// Factorisation for the FUSED kernels: fewest stages with radices from {12, 10, 9, 8, 7, 6, 5, 4, 3, 2}
+// Factorisation for the FUSED kernels: fewest stages with radices from {10, 8, 7, 6, 5, 4, 3, 2} (the
+// two-level butterflies 9 and 12 exist in dft_small but cost 100-128 registers per thread; without them the
+// FUSED kernels fit 3 CTAs per SM like the default ones)
 // (ties: the smaller largest radix, i.e. fewer registers), larger primes <= BIG_RADIX_MAX appended for the
 // direct-DFT stage.  Returns the number of stages, or -1.  `small_only`: fail instead of appending primes.
 inline int factorize_wide(int n, int* rad, bool small_only)
@@ -489,7 +487,7 @@ inline int factorize_wide(int n, int* rad, bool small_only)
         while (m % p == 0) { if (small_only || p > BIG_RADIX_MAX || nbig >= MAX_RAD) return -1; big[nbig++] = p; m /= p; }
     }
     // m is now 2^a 3^b 5^c 7^d: depth-first search over the radix set (m <= 1024: tiny)
-    const int cand[10] = {12, 10, 9, 8, 7, 6, 5, 4, 3, 2};
+    const int cand[8] = {10, 8, 7, 6, 5, 4, 3, 2};
     int best[MAX_RAD], nbest = MAX_RAD + 1, bestmax = 1 << 30;
     int cur[MAX_RAD];
     struct Rec {
@@ -503,7 +501,7 @@ inline int factorize_wide(int n, int* rad, bool small_only)
                 return;
             }
             if (depth + 1 > nbest || depth >= MAX_RAD) return;
-            for (int c = from; c < 10; ++c)
+            for (int c = from; c < 8; ++c)
                 if (m % cand[c] == 0) {
                     cur[depth] = cand[c];
                     go(m / cand[c], depth + 1, c, curmax > cand[c] ? curmax : cand[c], cur, cand, best, nbest, bestmax);

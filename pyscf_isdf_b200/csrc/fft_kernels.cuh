@@ -62,7 +62,7 @@ __device__ __forceinline__ double coulG_at(const CoulGeom& g, int ix, int iy, in
 // X_even[k] = (Z[k] + conj Z[n-k]) / 2 and X_odd[k] = -i (Z[k] - conj Z[n-k]) / 2.
 // LB = complex (paired) lines per CTA, i.e. 2 LB real lines.
 template <bool FUSED>
-__global__ void __launch_bounds__(FFT_THREADS)
+__global__ void __launch_bounds__(FFT_THREADS, FUSED ? 3 : 0)
 fft_z_r2c_kernel(const double* __restrict__ in, long long ldin, double2* __restrict__ out, long long ldout,
                  FftPlan pl, int nlines, int LB)
 {
@@ -96,7 +96,7 @@ fft_z_r2c_kernel(const double* __restrict__ in, long long ldin, double2* __restr
 
 // ---- z pass: half spectrum -> real lines (unnormalised inverse) ----------------
 template <bool FUSED>
-__global__ void __launch_bounds__(FFT_THREADS)
+__global__ void __launch_bounds__(FFT_THREADS, FUSED ? 3 : 0)
 fft_z_c2r_kernel(const double2* __restrict__ in, long long ldin, double* __restrict__ out, long long ldout,
                  FftPlan pl, int nlines, int LB)
 {
@@ -127,7 +127,7 @@ fft_z_c2r_kernel(const double2* __restrict__ in, long long ldin, double* __restr
 // MODE 1: forward, then multiply by sqrt(w * coulG)   (x pass of the W build)
 // MODE 2: forward, multiply by coulG*scale, inverse   (x pass of the V build)
 template <int MODE, bool FUSED>
-__global__ void __launch_bounds__(FFT_THREADS)
+__global__ void __launch_bounds__(FFT_THREADS, FUSED ? 3 : 0)
 fft_cols_kernel(double2* __restrict__ data, long long vec_stride, long long outer_stride,
                 FftPlan pl, int ncols, int CH, CoulGeom geo)
 {

@@ -66,9 +66,9 @@ def test_line_ffts_match_numpy(emul, fused, line_fast):
                 took_fused[n] = used
     if fused:
         # 2: fused Rader (prime n > 7 with n-1 = 2^a 3^b 5^c 7^d); 3: composite n with fewer passes
-        # through the wide radix set (96 = 12 x 8, 108 = 12 x 9, ...); 23 - 1 = 2 x 11 stays on plain Rader
+        # through the wide radix set (96 = 6 x 4 x 4, 108 = 6 x 6 x 3, 64 = 8 x 8, ...); 23 - 1 = 2 x 11 stays on plain Rader
         assert {n for n, u in took_fused.items() if u == 2} == {11, 13, 31, 41, 71, 97, 101}
-        assert {n for n, u in took_fused.items() if u == 3} == {8, 9, 10, 12, 36, 48, 64, 96, 100, 108, 128}
+        assert {n for n, u in took_fused.items() if u == 3} == {8, 10, 36, 48, 64, 96, 100, 108, 128}
     else:
         assert not took_fused
 
