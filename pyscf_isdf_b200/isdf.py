@@ -384,16 +384,37 @@ class ISDF:
         self._check_gamma(kpts)
         return self.potential_matrix_device(pseudo.pp_loc_on_grid(self.cell, self.mesh)).cpu().numpy()
 
-    def get_pp(self, kpts=None):
-        """FFTDF.get_pp (pyscf/pbc/df/fft.py:64-152).  The local part runs here; the non-local
-        projector part (:86-141, analytic Fourier transforms of the AOs from libcint's ft_ao) is not
-        part of this path: cells whose species carry projectors must add it from the reference's CPU
-        code (pyscf.pbc.gto.pseudo.pp_int.get_pp_nl) -- raise rather than return a partial matrix."""
+    def get_pp_nl(self, kpts=None):
+        """Non-local projector part of FFTDF.get_pp (pyscf/pbc/df/fft.py:86-141).  The reference
+        evaluates it on the CPU in reciprocal space from analytic Fourier transforms of the AOs
+        (SURVEY 8f row 2 keeps it there); so does this: pyscf_isdf_b200/pseudo.py on the host,
+        once per geometry.  With several ranks each takes a contiguous range of reciprocal vectors
+        and the projector-AO overlaps are summed over ranks before h_ij is applied."""
         from . import pseudo
+        self._check_gamma(kpts)
+        cell = self.cell
+        nao = cell.nao_nr()
+        if not pseudo.has_nonlocal(cell):
+            return np.zeros((nao, nao))
+        ng = int(np.prod(self.mesh))
+        comm = self.comm
+        rank, size = (comm.rank, comm.size) if comm is not None else (0, 1)
+        Z = pseudo.pp_nl_overlaps(cell, ng * rank // size, ng * (rank + 1) // size, self.mesh)
+        if size > 1:
+            buf = self.handle.from_host(np.stack([Z.real, Z.imag]))
+            comm.all_reduce_sum(buf)
+            zz = buf.cpu().numpy()
+            Z = zz[0] + 1j * zz[1]
+        return pseudo.pp_nl_from_overlaps(cell, Z)
+
+    def get_pp(self, kpts=None):
+        """FFTDF.get_pp (pyscf/pbc/df/fft.py:64-152): local part on the device-resident AO values,
+        non-local projector part on the host as the reference has it."""
+        from . import pseudo
+        vpp = self.get_pp_loc(kpts)
         if pseudo.has_nonlocal(self.cell):
-            raise NotImplementedError('get_pp: non-local GTH projectors are outside the ISDF path; '
-                                      'use get_pp_loc() + pyscf.pbc.gto.pseudo.pp_int.get_pp_nl(cell)')
-        return self.get_pp_loc(kpts)
+            vpp = vpp + self.get_pp_nl(kpts)
+        return vpp
 
     def get_j(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None):
         return self.get_jk(dm, hermi, kpts, kpts_band, True, False, omega)[0]

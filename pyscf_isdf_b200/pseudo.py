@@ -107,6 +107,145 @@ def nuc_on_grid(cell, mesh=None):
     return _ifft_real(rhoG * _coulG(G2), mesh)
 
 
+# ---------------------------------------------------------------------------
+# non-local projectors (pyscf/pbc/df/fft.py:86-141), host side, Gamma point
+# ---------------------------------------------------------------------------
+def solid_harmonics(l, q, qq=None):
+    """Real solid harmonics r^l Y_lm at the points q[n, 3] -> [2l+1, n], in the normalisation and
+    order of the AO evaluator (l = 1 as x, y, z; l = 2 as xy, yz, 2zz-xx-yy, xz, xx-yy)."""
+    x, y, z = q[:, 0], q[:, 1], q[:, 2]
+    if l == 0:
+        return np.full((1, len(q)), 0.282094791773878143)
+    if l == 1:
+        return 0.488602511902919921 * np.stack([x, y, z])
+    if l == 2:
+        c1, c0, c2 = 1.092548430592079070, 0.315391565252520002, 0.546274215296039535
+        return np.stack([c1 * x * y, c1 * y * z, c0 * (2 * z * z - x * x - y * y), c1 * x * z, c2 * (x * x - y * y)])
+    raise NotImplementedError('solid harmonics for l = %d' % l)
+
+
+def _qli(x2, l, i):
+    """Polynomial factor of projector i (from 0) of channel l as a function of x^2 = (|G| r_l)^2
+    (pyscf/pbc/gto/pseudo/pp.py:150-194)."""
+    rt = np.sqrt
+    if (l, i) == (0, 0):
+        return 4 * rt(2.) + 0 * x2
+    if (l, i) == (0, 1):
+        return 8 * rt(2 / 15.) * (3 - x2)
+    if (l, i) == (0, 2):
+        return 16 / 3. * rt(2 / 105.) * (15 - 10 * x2 + x2 * x2)
+    if (l, i) == (1, 0):
+        return 8 * rt(1 / 3.) + 0 * x2
+    if (l, i) == (1, 1):
+        return 16 * rt(1 / 105.) * (5 - x2)
+    if (l, i) == (1, 2):
+        return 32 / 3. * rt(1 / 1155.) * (35 - 14 * x2 + x2 * x2)
+    if (l, i) == (2, 0):
+        return 8 * rt(2 / 15.) + 0 * x2
+    if (l, i) == (2, 1):
+        return 16 / 3. * rt(2 / 105.) * (7 - x2)
+    if (l, i) == (2, 2):
+        return 32 / 3. * rt(2 / 15015.) * (63 - 18 * x2 + x2 * x2)
+    raise NotImplementedError('projector l = %d, i = %d' % (l, i))
+
+
+def species_projectors(pp, q, qq):
+    """Rows of the projector table of one species at the points q: for every channel l with
+    projectors, i = 0..nl-1, m = -l..l (the reference's pYlm order, fft.py:118-124) -> real
+    [nproj, n]: r_l^(l+3/2) pi^(5/4) S_lm(q) exp(-r_l^2 q^2 / 2) q_li(|q| r_l)."""
+    rows = []
+    for l, (rl, nl, _) in enumerate(pp['nonlocal_']):
+        if nl == 0:
+            continue
+        base = solid_harmonics(l, q, qq) * (rl**(l + 1.5) * np.pi**1.25 * np.exp(-0.5 * rl * rl * qq))
+        for i in range(nl):
+            rows.append(base * _qli(qq * rl * rl, l, i))
+    return np.concatenate(rows) if rows else np.zeros((0, len(q)))
+
+
+def species_h_blocks(pp):
+    """[(l, nl, h[nl, nl])] of the channels that carry projectors; h symmetric from the table's
+    upper-triangular rows (pyscf/gto/basis/parse_cp2k_pp.py:86-89)."""
+    out = []
+    for l, (rl, nl, rows) in enumerate(pp['nonlocal_']):
+        if nl == 0:
+            continue
+        h = np.zeros((nl, nl))
+        for i, row in enumerate(rows):
+            h[i, i:] = row
+        out.append((l, nl, h + h.T - np.diag(h.diagonal())))
+    return out
+
+
+def species_ft_shells(cell, ia, q, qq):
+    """Centred analytic Fourier transforms of the AOs of atom ``ia`` at the points q, without the
+    atom's phase: complex [nao_atom, n].  FT[S_lm(r) exp(-a r^2)](q) = (-i)^l (pi/a)^(3/2) (2a)^(-l)
+    S_lm(q) exp(-q^2/4a)  (the closed form libcint's ft_ao evaluates; pyscf/pbc/df/ft_ao.py)."""
+    bas, env = cell._bas, cell._env
+    rows = []
+    for ib in np.where(bas[:, 0] == ia)[0]:
+        l, npr, nc = int(bas[ib, 1]), int(bas[ib, 2]), int(bas[ib, 3])
+        alpha = env[bas[ib, 5]:bas[ib, 5] + npr]
+        coeff = env[bas[ib, 6]:bas[ib, 6] + npr * nc].reshape(nc, npr)
+        prim = np.exp(-np.outer(0.25 / alpha, qq)) * ((np.pi / alpha)**1.5 * (2 * alpha)**(-float(l)))[:, None]
+        rad = coeff.dot(prim)                                          # [nc, n]
+        ang = solid_harmonics(l, q, qq)                                # [2l+1, n]
+        rows.append(((-1j)**l * rad[:, None, :] * ang[None, :, :]).reshape(nc * (2 * l + 1), -1))
+    return np.concatenate(rows)
+
+
+def pp_nl_overlaps(cell, g0=0, g1=None, mesh=None, max_bytes=1 << 29):
+    """Sum over the reciprocal vectors [g0, g1) of  conj(SI_a) P_a(G) x ft_ao(G)  for every projector
+    of every atom: complex [nproj_total, nao] (the reference's SPG_lm_aoGs, fft.py:129-130, for all
+    atoms at once and without the 1/sqrt(vol)).  The sum over G is a plain sum, so ranks can take
+    disjoint ranges and add their results."""
+    mesh = cell.mesh if mesh is None else mesh
+    Gv = cell.get_Gv(mesh)
+    g1 = len(Gv) if g1 is None else g1
+    coords = cell.atom_coords()
+    nao = cell.nao_nr()
+    pps = [cell._pseudo_for(cell.atom_symbol(ia)) for ia in range(cell.natm)]
+    first = {}
+    for ia in range(cell.natm):
+        first.setdefault(cell.atom_symbol(ia), ia)
+    nproj = [sum(nl * (2 * l + 1) for l, (_, nl, _) in enumerate(pp['nonlocal_'])) if pp is not None else 0 for pp in pps]
+    Z = np.zeros((sum(nproj), nao), dtype=np.complex128)
+    step = max(256, int(max_bytes // (16 * (nao + sum(nproj) + 1))))
+    for b0 in range(g0, g1, step):
+        q = Gv[b0:min(b0 + step, g1)]
+        qq = np.einsum('gx,gx->g', q, q)
+        SI = np.exp(-1j * np.dot(coords, q.T))                         # [natm, n]
+        ft = {s: species_ft_shells(cell, ia, q, qq) for s, ia in first.items()}
+        pr = {s: species_projectors(pps[ia], q, qq) for s, ia in first.items() if nproj[ia]}
+        aoG = np.concatenate([ft[cell.atom_symbol(ia)] * SI[ia] for ia in range(cell.natm)])       # [nao, n]
+        spg = [pr[cell.atom_symbol(ia)] * SI[ia].conj() for ia in range(cell.natm) if nproj[ia]]
+        if spg:
+            Z += np.concatenate(spg).dot(aoG.T)
+    return Z
+
+
+def pp_nl_from_overlaps(cell, Z):
+    """vppnl[nao, nao] = sum_atoms sum_l sum_m  Z^H h_l Z / vol^2  (fft.py:131-139; each ft_ao carries
+    1/sqrt(vol) there and the result another 1/vol); real part at the Gamma point (fft.py:144-145)."""
+    nao = cell.nao_nr()
+    out = np.zeros((nao, nao), dtype=np.complex128)
+    p = 0
+    for ia in range(cell.natm):
+        pp = cell._pseudo_for(cell.atom_symbol(ia))
+        if pp is None:
+            continue
+        for l, nl, h in species_h_blocks(pp):
+            n = nl * (2 * l + 1)
+            z = Z[p:p + n].reshape(nl, 2 * l + 1, nao)
+            out += np.einsum('imp,imq->pq', z.conj(), np.einsum('ij,jmp->imp', h, z))
+            p += n
+    return out.real / cell.vol**2
+
+
+def pp_nl_matrix(cell, mesh=None):
+    return pp_nl_from_overlaps(cell, pp_nl_overlaps(cell, mesh=mesh))
+
+
 def has_nonlocal(cell):
     """True if any atom carries non-local GTH projectors (pyscf/pbc/df/fft.py:86-141 needs them)."""
     for ia in range(cell.natm):

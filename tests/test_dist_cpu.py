@@ -43,7 +43,8 @@ def _run_rank(comm, out=None, fit='implicit'):
     vj, vk = dist.get_jk_device(mydf, comm, torch.from_numpy(dm[None].copy()))
     vpp = mydf.get_pp_loc()                    # hcore local part on the rank's grid slab, summed over ranks
     vne = mydf.get_nuc()
-    res = dict(ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(), vpp=vpp, vne=vne,
+    vnl = mydf.get_pp_nl()                     # projector part: every rank sums its own range of G vectors
+    res = dict(ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(), vpp=vpp, vne=vne, vnl=vnl,
                p0=int(mydf._part.ip_off[comm.rank]),
                vj=vj.numpy()[0].copy(), vk=vk.numpy()[0].copy(), slab=mydf._slab,
                panels=mydf.timings['select_panels'])
@@ -74,6 +75,8 @@ def _check(res, tol=1e-9):
     vne0 = opp.potential_matrix(ao, opp.nuc_on_grid(a, mesh, coords, charges))
     assert abs(res['vpp'] - vpp0).max() < 1e-10
     assert abs(res['vne'] - vne0).max() < 1e-10
+    vnl0 = opp.pp_nl_matrix(a, mesh, cell._atm, cell._bas, cell._env, coords, pps).real      # fft.py:86-145
+    assert abs(vnl0).max() > 1e-3 and abs(res['vnl'] - vnl0).max() < 1e-12
 
 
 def test_partition():

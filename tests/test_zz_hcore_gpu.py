@@ -1,6 +1,7 @@
 """GPU: hcore pieces on the device-resident AO values ("next" row 2 of SURVEY 8f):
-ISDF.get_nuc / get_pp_loc against the oracle's restatement of FFTDF.get_nuc / get_pp local part
-(pyscf/pbc/df/fft.py:39-84).  Tolerance 1e-10 abs (one FP64 contraction over the grid).
+ISDF.get_nuc / get_pp_loc / get_pp against the oracle's restatement of FFTDF.get_nuc / get_pp
+(pyscf/pbc/df/fft.py:39-152; the oracle itself is pinned to the reference's fingerprints of both
+matrices, tests/test_pseudo_cpu.py).  Tolerance 1e-10 abs (one FP64 contraction over the grid).
 
 (File name sorts last: this row was added after the last GPU session of round 1.)"""
 import numpy as np
@@ -24,6 +25,12 @@ def _ref(cell):
     return vpp, vne
 
 
+def _ref_nl(cell):
+    coords = cell.atom_coords()
+    pps = [cell._pseudo_for(cell.atom_symbol(i)) for i in range(cell.natm)]
+    return opp.pp_nl_matrix(cell.lattice_vectors(), cell.mesh, cell._atm, cell._bas, cell._env, coords, pps).real
+
+
 @pytest.mark.parametrize('which', ['c8', 'he_c'])
 def test_local_potentials_match_oracle(which):
     cell = diamond_c8([15, 14, 12], basis='gth-dzvp', jitter=0.15) if which == 'c8' else he_c_cell()
@@ -36,8 +43,9 @@ def test_local_potentials_match_oracle(which):
     vpp = mydf.get_pp_loc(np.zeros(3))
     assert abs(vpp - vpp0).max() < 1e-10
     assert abs(vpp - vpp.T).max() < 1e-12
-    with pytest.raises(NotImplementedError):
-        mydf.get_pp()                         # C carries non-local projectors
+    vnl0 = _ref_nl(cell)                      # C carries non-local projectors
+    assert abs(vnl0).max() > 1e-3
+    assert abs(mydf.get_pp() - (vpp0 + vnl0)).max() < 1e-10
     with pytest.raises(NotImplementedError):
         mydf.get_nuc(np.array([0.1, 0, 0]))
 
@@ -57,13 +65,14 @@ def test_sharded_local_potential():
     vpp0, _ = _ref(cell)
     n = 3
     shared = ThreadComm.Shared(n)
-    out, err = [None] * n, []
+    out, full, err = [None] * n, [None] * n, []
 
     def work(r):
         try:
             mydf = ISDF(cell, c=6, comm=ThreadComm(shared, r))
             mydf.build()
             out[r] = mydf.get_pp_loc()
+            full[r] = mydf.get_pp()
         except Exception as e:        # noqa: BLE001
             err.append(e)
             shared.barrier.abort()
@@ -75,5 +84,7 @@ def test_sharded_local_potential():
         t.join(timeout=600)
     if err:
         raise err[0]
+    vnl0 = _ref_nl(cell)
     for r in range(n):
         assert abs(out[r] - vpp0).max() < 1e-10
+        assert abs(full[r] - (vpp0 + vnl0)).max() < 1e-10
