@@ -70,12 +70,52 @@ def shell_values(l, dr, rr, alpha, coeff):
     return (ectr[:, None, :] * ang[None, :, :]).reshape(nc * ang.shape[0], -1)
 
 
-def eval_ao(atm, bas, env, coords, Ls, rcut, kpts=None, blksize=BLKSIZE):
+def shell_values_deriv1(l, dr, rr, alpha, coeff):
+    """Values and Cartesian gradient of one contracted shell at displaced points
+    (GTOshell_eval_grid_cart_deriv1, pyscf/lib/gto/deriv1.c:167-204, followed by the same
+    cartesian -> spherical step): [4, nc*(2l+1), n], components (value, d/dx, d/dy, d/dz).
+    d/dx [x^a y^b z^c e(r^2)] = a x^(a-1) y^b z^c e + x^(a+1) y^b z^c e',  e' = sum c (-2 alpha) exp(-alpha r^2)."""
+    fac = FAC_SP.get(l, 1.0)
+    eprim = np.exp(-np.outer(alpha, rr)) * fac
+    e0 = coeff.dot(eprim)                                            # [nc, n]
+    e1 = coeff.dot(eprim * (-2 * alpha)[:, None])
+    xyz = [dr[:, 0], dr[:, 1], dr[:, 2]]
+    pw = cart_powers(l)
+    cart = np.stack([xyz[0]**a * xyz[1]**b * xyz[2]**c for a, b, c in pw])
+    dcart = []
+    for ax in range(3):
+        rows = []
+        for a, b, c in pw:
+            e = [a, b, c]
+            if e[ax] == 0:
+                rows.append(np.zeros_like(rr))
+                continue
+            k = e[ax]
+            e[ax] -= 1
+            rows.append(k * xyz[0]**e[0] * xyz[1]**e[1] * xyz[2]**e[2])
+        dcart.append(np.stack(rows))
+    if l >= 2:
+        if l not in C2S:
+            raise NotImplementedError('l=%d' % l)
+        cart = C2S[l].dot(cart)
+        dcart = [C2S[l].dot(d) for d in dcart]
+    nc = e0.shape[0]
+    out = [e0[:, None, :] * cart[None]]
+    for ax in range(3):
+        out.append(e0[:, None, :] * dcart[ax][None] + e1[:, None, :] * (xyz[ax] * cart)[None])
+    return np.stack(out).reshape(4, nc * cart.shape[0], -1)
+
+
+def eval_ao(atm, bas, env, coords, Ls, rcut, kpts=None, blksize=BLKSIZE, deriv=0):
     """AO values, real spherical GTOs, lattice summed.
 
     Returns ``ao[ngrids, nao]`` float64 for the Gamma point (``kpts`` None),
-    else a complex array ``[nkpts, ngrids, nao]``.
+    else a complex array ``[nkpts, ngrids, nao]``.  With ``deriv=1``
+    (PBCGTOval_sph_deriv1, pyscf/lib/pbc/grid_ao.c:548-558) the result gains an
+    axis of 4 components (value, d/dx, d/dy, d/dz) in front of ``ngrids``.
     """
+    if deriv == 1:
+        return _eval_ao_deriv1(atm, bas, env, coords, Ls, rcut, kpts, blksize)
     atm = np.asarray(atm); bas = np.asarray(bas); env = np.asarray(env)
     coords = np.asarray(coords, dtype=float)
     Ls = np.asarray(Ls, dtype=float).reshape(-1, 3)
@@ -120,4 +160,53 @@ def eval_ao(atm, bas, env, coords, Ls, rcut, kpts=None, blksize=BLKSIZE):
                 for k in range(ao.shape[0]):
                     ao[k, pts, i0:i0 + val.shape[0]] += val.T * phase[m, k]
     ao = ao[:, :ngrids]
+    return ao[0] if gamma else ao
+
+
+def _eval_ao_deriv1(atm, bas, env, coords, Ls, rcut, kpts, blksize):
+    """Same driver as eval_ao (same image screening), four components per AO."""
+    atm = np.asarray(atm); bas = np.asarray(bas); env = np.asarray(env)
+    coords = np.asarray(coords, dtype=float)
+    Ls = np.asarray(Ls, dtype=float).reshape(-1, 3)
+    ngrids = len(coords)
+    nblk = (ngrids + blksize - 1) // blksize
+    npad = nblk * blksize
+    cpad = np.full((npad, 3), 1e9)
+    cpad[:ngrids] = coords
+    dims = (bas[:, 1] * 2 + 1) * bas[:, 3]
+    ao_loc = np.concatenate([[0], np.cumsum(dims)])
+    nao = int(ao_loc[-1])
+    gamma = kpts is None
+    if gamma:
+        ao = np.zeros((1, 4, npad, nao))
+        phase = np.ones((len(Ls), 1))
+    else:
+        kpts = np.reshape(kpts, (-1, 3))
+        ao = np.zeros((len(kpts), 4, npad, nao), dtype=np.complex128)
+        phase = np.exp(1j * Ls.dot(kpts.T))
+    for ia in range(len(atm)):
+        shls = np.where(bas[:, 0] == ia)[0]
+        if len(shls) == 0:
+            continue
+        ratm = env[atm[ia, 1]:atm[ia, 1] + 3]
+        rcmax = rcut[shls].max()
+        for m, L in enumerate(Ls):
+            dr = cpad - (ratm + L)
+            rr = np.einsum('gx,gx->g', dr, dr)
+            mind = np.sqrt(rr.reshape(nblk, blksize).min(axis=1))
+            if not (mind < rcmax).any():
+                continue
+            for ib in shls:
+                keep = mind < rcut[ib]
+                if not keep.any():
+                    continue
+                pts = np.repeat(keep, blksize).nonzero()[0]
+                l, npr, nc = bas[ib, 1], bas[ib, 2], bas[ib, 3]
+                alpha = env[bas[ib, 5]:bas[ib, 5] + npr]
+                coeff = env[bas[ib, 6]:bas[ib, 6] + npr * nc].reshape(nc, npr)
+                val = shell_values_deriv1(l, dr[pts], rr[pts], alpha, coeff)   # [4, dim, n]
+                i0 = ao_loc[ib]
+                for k in range(ao.shape[0]):
+                    ao[k][:, pts, i0:i0 + val.shape[1]] += val.transpose(0, 2, 1) * phase[m, k]
+    ao = ao[:, :, :ngrids]
     return ao[0] if gamma else ao
