@@ -21,7 +21,7 @@ tests/test_xc_cpu.py.
 """
 import numpy as np
 
-H = 1e-30          # complex step
+H = 1e-30          # complex step, relative to the argument
 
 
 def f_slater(rho, sigma):
@@ -106,8 +106,8 @@ def eval_xc(code, rho, sigma):
     vs = np.zeros_like(r)
     for fn in FUNCTIONALS[code.lower()]:
         f += fn(r, s)
-        vr += fn(r + 1j * H, s + 0j).imag / H
-        vs += fn(r + 0j, s + 1j * H).imag / H
+        vr += fn(r * (1 + 1j * H), s + 0j).imag / (r * H)
+        vs += fn(r + 0j, s * (1 + 1j * H)).imag / (s * H)
     return np.where(ok, f / r, 0.0), np.where(ok, vr, 0.0), np.where(ok, vs, 0.0)
 
 

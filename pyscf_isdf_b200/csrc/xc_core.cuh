@@ -1,0 +1,137 @@
+// Closed-shell exchange-correlation functionals at one grid point, f(rho, sigma) per unit volume with
+// its two first derivatives carried along by forward-mode dual numbers (value, d/d rho, d/d sigma), so
+// that each functional is written once, as its published energy expression, and no derivative is
+// derived by hand.  What the reference gets from libxc through pyscf/dft/libxc.py:eval_xc (spin = 0,
+// deriv = 1): exc per particle, vrho, vsigma.
+//   Slater exchange; Becke 88 exchange (Phys. Rev. A 38, 3098); LYP correlation in the closed-shell
+//   form of Miehlich et al. (Chem. Phys. Lett. 157, 200); PBE exchange and correlation (Phys. Rev.
+//   Lett. 77, 3865) over PW92 with libxc's pw_mod constants.
+// Like fft_core.cuh and crt_core.cuh this header also compiles with g++ (tests/emul/xc_emul.cpp), where
+// it is checked point by point against oracle/xc.py (complex-step derivatives of the same formulas,
+// pinned to the reference's BLYP numbers).
+#pragma once
+#include <cmath>
+
+namespace isdf_xc {
+
+constexpr int XC_LDA_X = 1;      // 'lda,'
+constexpr int XC_BLYP = 2;       // 'blyp' = b88 + lyp
+constexpr int XC_PBE = 3;        // 'pbe'  = pbe exchange + pbe correlation
+constexpr double RHO_CUT = 1e-15;
+constexpr double SIGMA_FLOOR = 1e-40;
+constexpr double PI = 3.14159265358979323846;
+
+struct Dual { double v, r, s; };
+
+__host__ __device__ __forceinline__ Dual cst(double a) { return Dual{a, 0.0, 0.0}; }
+__host__ __device__ __forceinline__ Dual operator+(Dual a, Dual b) { return Dual{a.v + b.v, a.r + b.r, a.s + b.s}; }
+__host__ __device__ __forceinline__ Dual operator-(Dual a, Dual b) { return Dual{a.v - b.v, a.r - b.r, a.s - b.s}; }
+__host__ __device__ __forceinline__ Dual operator-(Dual a) { return Dual{-a.v, -a.r, -a.s}; }
+__host__ __device__ __forceinline__ Dual operator*(Dual a, Dual b)
+{
+    return Dual{a.v * b.v, a.r * b.v + a.v * b.r, a.s * b.v + a.v * b.s};
+}
+__host__ __device__ __forceinline__ Dual operator/(Dual a, Dual b)
+{
+    const double q = a.v / b.v, ib = 1.0 / b.v;
+    return Dual{q, (a.r - q * b.r) * ib, (a.s - q * b.s) * ib};
+}
+__host__ __device__ __forceinline__ Dual operator+(Dual a, double b) { return Dual{a.v + b, a.r, a.s}; }
+__host__ __device__ __forceinline__ Dual operator+(double b, Dual a) { return Dual{a.v + b, a.r, a.s}; }
+__host__ __device__ __forceinline__ Dual operator-(Dual a, double b) { return Dual{a.v - b, a.r, a.s}; }
+__host__ __device__ __forceinline__ Dual operator-(double b, Dual a) { return Dual{b - a.v, -a.r, -a.s}; }
+__host__ __device__ __forceinline__ Dual operator*(Dual a, double b) { return Dual{a.v * b, a.r * b, a.s * b}; }
+__host__ __device__ __forceinline__ Dual operator*(double b, Dual a) { return Dual{a.v * b, a.r * b, a.s * b}; }
+__host__ __device__ __forceinline__ Dual operator/(Dual a, double b) { return a * (1.0 / b); }
+__host__ __device__ __forceinline__ Dual operator/(double b, Dual a) { return cst(b) / a; }
+__host__ __device__ __forceinline__ Dual chain(Dual a, double fv, double dfv) { return Dual{fv, dfv * a.r, dfv * a.s}; }
+__host__ __device__ __forceinline__ Dual dpow(Dual a, double p) { const double v = pow(a.v, p); return chain(a, v, p * v / a.v); }
+__host__ __device__ __forceinline__ Dual dsqrt(Dual a) { const double v = sqrt(a.v); return chain(a, v, 0.5 / v); }
+__host__ __device__ __forceinline__ Dual dexp(Dual a) { const double v = exp(a.v); return chain(a, v, v); }
+__host__ __device__ __forceinline__ Dual dlog(Dual a) { return chain(a, log(a.v), 1.0 / a.v); }
+__host__ __device__ __forceinline__ Dual dasinh(Dual a) { return chain(a, asinh(a.v), 1.0 / sqrt(1.0 + a.v * a.v)); }
+
+__host__ __device__ inline Dual f_slater(Dual rho)
+{
+    return -0.75 * pow(3.0 / PI, 1.0 / 3.0) * dpow(rho, 4.0 / 3.0);
+}
+
+__host__ __device__ inline Dual f_b88(Dual rho, Dual sigma)
+{
+    const double beta = 0.0042;
+    const Dual ra = 0.5 * rho;                         // one spin channel
+    const Dual ga = 0.5 * dsqrt(sigma);
+    const Dual r43 = dpow(ra, 4.0 / 3.0);
+    const Dual x = ga / r43;
+    const double cx = 1.5 * pow(3.0 / (4.0 * PI), 1.0 / 3.0);
+    return 2.0 * (-cx * r43 - beta * r43 * x * x / (1.0 + 6.0 * beta * x * dasinh(x)));
+}
+
+__host__ __device__ inline Dual f_lyp(Dual rho, Dual sigma)
+{
+    const double a = 0.04918, b = 0.132, c = 0.2533, d = 0.349;
+    const double cf = 0.3 * pow(3.0 * PI * PI, 2.0 / 3.0);
+    const Dual r13 = dpow(rho, -1.0 / 3.0);
+    const Dual den = 1.0 + d * r13;
+    const Dual omega = dexp(-c * r13) / den * dpow(rho, -11.0 / 3.0);
+    const Dual delta = c * r13 + d * r13 / den;
+    const Dual ra = 0.5 * rho;
+    const Dual saa = 0.25 * sigma;                     // |grad rho_a|^2 = |grad rho_b|^2
+    const Dual t1 = -a * 4.0 / den * ra * ra / rho;
+    const Dual brace = ra * ra * (pow(2.0, 11.0 / 3.0) * cf * 2.0 * dpow(ra, 8.0 / 3.0)
+                                  + (47.0 / 18.0 - 7.0 / 18.0 * delta) * sigma
+                                  - (2.5 - delta / 18.0) * 2.0 * saa
+                                  - (delta - 11.0) / 9.0 * 2.0 * (ra / rho) * saa)
+                       - 2.0 / 3.0 * rho * rho * sigma + 2.0 * (2.0 / 3.0 * rho * rho - ra * ra) * saa;
+    return t1 - a * b * omega * brace;
+}
+
+__host__ __device__ inline Dual f_pbe_x(Dual rho, Dual sigma)
+{
+    const double kappa = 0.804, mu = 0.2195149727645171;
+    const Dual kf = dpow(3.0 * PI * PI * rho, 1.0 / 3.0);
+    const Dual d = 2.0 * kf * rho;
+    const Dual s2 = sigma / (d * d);
+    return f_slater(rho) * (1.0 + kappa - kappa / (1.0 + mu / kappa * s2));
+}
+
+__host__ __device__ inline Dual eps_pw92(Dual rs)
+{
+    const double A = 0.0310906908696549, a1 = 0.21370, b1 = 7.5957, b2 = 3.5876, b3 = 1.6382, b4 = 0.49294;
+    const Dual sq = dsqrt(rs);
+    const Dual q = 2.0 * A * (b1 * sq + b2 * rs + b3 * rs * sq + b4 * rs * rs);
+    return -2.0 * A * (1.0 + a1 * rs) * dlog(1.0 + 1.0 / q);
+}
+
+__host__ __device__ inline Dual f_pbe_c(Dual rho, Dual sigma)
+{
+    const double beta = 0.06672455060314922;
+    const double gamma = (1.0 - 0.69314718055994530942) / (PI * PI);
+    const Dual rs = dpow(3.0 / (4.0 * PI) / rho, 1.0 / 3.0);
+    const Dual ec = eps_pw92(rs);
+    const Dual kf = dpow(3.0 * PI * PI * rho, 1.0 / 3.0);
+    const Dual ks2 = 4.0 / PI * kf;
+    const Dual t2 = sigma / (4.0 * ks2 * rho * rho);
+    const Dual A = beta / gamma / (dexp(-ec / gamma) - 1.0);
+    const Dual At2 = A * t2;
+    return rho * (ec + gamma * dlog(1.0 + beta / gamma * t2 * (1.0 + At2) / (1.0 + At2 + At2 * At2)));
+}
+
+// exc per particle, vrho = df/drho, vsigma = df/dsigma; zeros below the density threshold.
+// Returns false for an unknown functional code.
+__host__ __device__ inline bool eval_point(int code, double rho, double sigma, double* exc, double* vrho, double* vsigma)
+{
+    *exc = 0.0; *vrho = 0.0; *vsigma = 0.0;
+    if (code != XC_LDA_X && code != XC_BLYP && code != XC_PBE) return false;
+    if (!(rho > RHO_CUT)) return true;
+    const Dual r{rho, 1.0, 0.0};
+    const Dual s{sigma > SIGMA_FLOOR ? sigma : SIGMA_FLOOR, 0.0, 1.0};
+    Dual f;
+    if (code == XC_LDA_X) f = f_slater(r);
+    else if (code == XC_BLYP) f = f_b88(r, s) + f_lyp(r, s);
+    else f = f_pbe_x(r, s) + f_pbe_c(r, s);
+    *exc = f.v / rho; *vrho = f.r; *vsigma = f.s;
+    return true;
+}
+
+}  // namespace isdf_xc
