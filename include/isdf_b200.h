@@ -186,6 +186,39 @@ int isdf_j_from_potential(isdf_handle* h, const double* phi, long long ldphi, in
                           const double* vR, long long ldv, int nset, double weight,
                           double* vj, void* ws, size_t ws_bytes);
 
+/* GGA exchange-correlation on the device-resident AO values ("next" row 1 of SURVEY 8f): the pieces
+ * of NumInt.nr_rks [pyscf/pbc/dft/numint.py:283-381] for one slab of ngl grid points at the Gamma
+ * point, closed shell.
+ *   isdf_eval_ao_deriv1  AO values and Cartesian gradients [PBCGTOval_sph_deriv1,
+ *                        pyscf/lib/pbc/grid_ao.c:548-558]: four planes (value, d/dx, d/dy, d/dz), each
+ *                        [nao, ldphi], comp_stride doubles apart; other arguments as isdf_eval_ao.
+ *   isdf_xc_density      rho4[4, ldr] = (rho, grad rho) for a symmetric dm[nao, nao]
+ *                        [eval_rho, numint.py:138-145, hermi = 1].
+ *   isdf_xc_potential    functional at every grid point [libxc through pyscf/dft/libxc.py:eval_xc in the
+ *                        reference; published closed forms here, csrc/xc_core.cuh]; writes
+ *                        wv4[4, ldr] = weight (vrho/2, 2 vsigma grad rho) [numint.py:366, :987-994] and
+ *                        d_sums[2] (device) = (sum rho weight, sum rho weight exc) [numint.py:361-365].
+ *                        code from isdf_xc_code("lda," | "blyp" | "pbe"), -1 if unknown.
+ *   isdf_xc_matrix       vmat[nao, nao] = M + M^T, M = Phi (sum_c wv_c Phi_c)^T [_vxc_mat, numint.py:812-815, :374].
+ * A sharded grid sums vmat and d_sums over ranks.  Workspace of the three xc calls: isdf_xc_ws_bytes. */
+int isdf_eval_ao_deriv1(isdf_handle* h,
+                        const int* h_atm, int natm, const int* h_bas, int nbas,
+                        const double* h_env, int nenv,
+                        const double* h_a, const int* h_mesh,
+                        const double* h_Ls, int nimg, const double* h_rcut,
+                        long long g0, long long g1,
+                        double* phi4, long long ldphi, long long comp_stride);
+int isdf_xc_code(const char* name);
+size_t isdf_xc_ws_bytes(int nao, long long ldphi);
+int isdf_xc_density(isdf_handle* h, const double* phi4, long long ldphi, long long comp_stride,
+                    int nao, long long ngl, const double* dm, double* rho4, long long ldr,
+                    void* ws, size_t ws_bytes);
+int isdf_xc_potential(isdf_handle* h, int code, const double* rho4, long long ldr, long long ngl,
+                      double weight, double* wv4, double* d_sums, void* ws, size_t ws_bytes);
+int isdf_xc_matrix(isdf_handle* h, const double* phi4, long long ldphi, long long comp_stride,
+                   int nao, long long ngl, const double* wv4, long long ldr, double* vmat,
+                   void* ws, size_t ws_bytes);
+
 /* Stage 5 [spec; exact limit pyscf/pbc/df/fft_jk.py:33-109,177-302].
  * X[nao, np] = phi[:, ip];  J = X diag(W rho) X^T, rho_P = (X^T D X)_PP;
  * K = X ((X^T D X) o W) X^T.  dm/vj/vk: [nset, nao, nao]. */

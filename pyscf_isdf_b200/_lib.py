@@ -58,6 +58,13 @@ SIGNATURES = {
     'isdf_grid_j_ws_bytes': (c_sz, [c_int, c_ll]),
     'isdf_density_on_grid': (c_int, [c_vp, c_vp, c_ll, c_int, c_ll, c_vp, c_int, c_vp, c_ll, c_vp, c_sz]),
     'isdf_j_from_potential': (c_int, [c_vp, c_vp, c_ll, c_int, c_ll, c_vp, c_ll, c_int, c_dbl, c_vp, c_vp, c_sz]),
+    'isdf_eval_ao_deriv1': (c_int, [c_vp, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp,
+                                    c_vp, c_int, c_vp, c_ll, c_ll, c_vp, c_ll, c_ll]),
+    'isdf_xc_code': (c_int, [ctypes.c_char_p]),
+    'isdf_xc_ws_bytes': (c_sz, [c_int, c_ll]),
+    'isdf_xc_density': (c_int, [c_vp, c_vp, c_ll, c_ll, c_int, c_ll, c_vp, c_vp, c_ll, c_vp, c_sz]),
+    'isdf_xc_potential': (c_int, [c_vp, c_int, c_vp, c_ll, c_ll, c_dbl, c_vp, c_vp, c_vp, c_sz]),
+    'isdf_xc_matrix': (c_int, [c_vp, c_vp, c_ll, c_ll, c_int, c_ll, c_vp, c_ll, c_vp, c_vp, c_sz]),
     'isdf_get_jk_block_ws_bytes': (c_sz, [c_int, c_int, c_int]),
     'isdf_get_jk_block': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_int, c_int, c_int,
                                   c_int, c_int, c_vp, c_vp, c_vp, c_sz]),
@@ -232,6 +239,43 @@ class Handle:
         check(self.lib.isdf_eval_ao(self.h, hptr(atm), len(atm), hptr(bas), len(bas), hptr(env), len(env),
                                     hptr(a), hptr(mesh), hptr(Ls), len(Ls), hptr(rcut),
                                     g0, g1, c_vp(phi.data_ptr()), ldphi))
+
+    def eval_ao_deriv1(self, atm, bas, env, a, mesh, Ls, rcut, g0, g1, phi4, ldphi, comp_stride):
+        """phi4: device tensor [4, nao, ldphi] (value, d/dx, d/dy, d/dz planes)."""
+        atm = np.ascontiguousarray(atm, dtype=np.int32)
+        bas = np.ascontiguousarray(bas, dtype=np.int32)
+        env = np.ascontiguousarray(env, dtype=np.float64)
+        a = np.ascontiguousarray(a, dtype=np.float64)
+        mesh = np.ascontiguousarray(mesh, dtype=np.int32)
+        Ls = np.ascontiguousarray(Ls, dtype=np.float64)
+        rcut = np.ascontiguousarray(rcut, dtype=np.float64)
+        check(self.lib.isdf_eval_ao_deriv1(self.h, hptr(atm), len(atm), hptr(bas), len(bas), hptr(env), len(env),
+                                           hptr(a), hptr(mesh), hptr(Ls), len(Ls), hptr(rcut),
+                                           g0, g1, c_vp(phi4.data_ptr()), ldphi, comp_stride))
+
+    def xc_code(self, name):
+        code = self.lib.isdf_xc_code(str(name).encode())
+        if code < 0:
+            raise NotImplementedError('xc functional %r (have: lda, / blyp / pbe)' % (name,))
+        return code
+
+    def xc_density(self, phi4, ldphi, comp_stride, nao, ngl, dm, rho4, ldr, ws=None):
+        nbytes = self.lib.isdf_xc_ws_bytes(nao, ldphi)
+        if ws is None:
+            ws = self.workspace(nbytes)
+        check(self.lib.isdf_xc_density(self.h, c_vp(phi4.data_ptr()), ldphi, comp_stride, nao, ngl, c_vp(dm.data_ptr()),
+                                       c_vp(rho4.data_ptr()), ldr, c_vp(ws.data_ptr()), nbytes))
+        return ws
+
+    def xc_potential(self, code, rho4, ldr, ngl, weight, wv4, sums, ws):
+        check(self.lib.isdf_xc_potential(self.h, int(code), c_vp(rho4.data_ptr()), ldr, ngl, float(weight),
+                                         c_vp(wv4.data_ptr()), c_vp(sums.data_ptr()), c_vp(ws.data_ptr()),
+                                         ws.numel() * ws.element_size()))
+
+    def xc_matrix(self, phi4, ldphi, comp_stride, nao, ngl, wv4, ldr, vmat, ws):
+        check(self.lib.isdf_xc_matrix(self.h, c_vp(phi4.data_ptr()), ldphi, comp_stride, nao, ngl,
+                                      c_vp(wv4.data_ptr()), ldr, c_vp(vmat.data_ptr()), c_vp(ws.data_ptr()),
+                                      ws.numel() * ws.element_size()))
 
     def select_ip(self, phi, nao, ng, ldphi, npts, tol, Lt, ldl):
         nbytes = self.lib.isdf_select_ip_ws_bytes(nao, ng, npts)

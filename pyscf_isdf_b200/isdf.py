@@ -416,6 +416,57 @@ class ISDF:
             vpp = vpp + self.get_pp_nl(kpts)
         return vpp
 
+    # -- exchange-correlation on the same grid ("next" row 1 of SURVEY 8f) -----------------------
+    def _ao_deriv1_on_grid(self):
+        """AO values and gradients of this rank's grid slab, [4, nao, ld] on the device, evaluated on
+        first use and kept (4 x the AO matrix; drop with ``self._aoR4 = None``)."""
+        if getattr(self, '_aoR4', None) is not None:
+            return self._aoR4
+        h = self.handle
+        cell = self.cell
+        ng = int(np.prod(self.mesh))
+        g0, g1 = self._slab if self._slab is not None else (0, ng)
+        ld = _lib.pad8(g1 - g0)
+        nao = cell.nao_nr()
+        rcut, Ls = cell.ao_eval_params()
+        phi4 = h.zeros((4, nao, ld))
+        h.eval_ao_deriv1(cell._atm, cell._bas, cell._env,
+                         np.ascontiguousarray(cell.lattice_vectors(), dtype=np.float64),
+                         np.asarray(cell.mesh, dtype=np.int32), Ls, rcut, g0, g1, phi4, ld, nao * ld)
+        self._aoR4 = phi4
+        return phi4
+
+    def nr_rks(self, xc_code, dm, kpts=None):
+        """(nelec, exc, vmat) of a closed-shell density matrix at the Gamma point: NumInt.nr_rks of the
+        reference (pyscf/pbc/dft/numint.py:283-381) for the functionals 'lda,', 'blyp' and 'pbe', on the
+        device: density and gradient from the AO values, the functional, and the potential matrix.  With a
+        sharded grid every rank works on its slab and the three results are summed over ranks."""
+        self._check_gamma(kpts)
+        h = self.handle
+        dm = np.asarray(dm, dtype=np.float64)
+        if dm.ndim != 2 or abs(dm - dm.T).max() > 1e-10 * max(1.0, abs(dm).max()):
+            raise ValueError('nr_rks: one symmetric density matrix expected')
+        if self.comm is not None and self.comm.size > 1 and self._slab is None:
+            raise RuntimeError('nr_rks on a sharded grid needs build() first (it assigns the grid slabs)')
+        code = h.xc_code(xc_code)
+        phi4 = self._ao_deriv1_on_grid()
+        nao, ld = phi4.shape[1], phi4.shape[2]
+        ng = int(np.prod(self.mesh))
+        g0, g1 = self._slab if self._slab is not None else (0, ng)
+        ngl = g1 - g0
+        weight = self.cell.vol / ng
+        d_dm = h.from_host(np.ascontiguousarray(dm))
+        rho4 = h.zeros((4, ld))
+        wv4 = h.zeros((4, ld))
+        out = h.zeros((nao * nao + 2,))              # vmat and the two sums in one buffer: one all-reduce
+        ws = h.xc_density(phi4, ld, nao * ld, nao, ngl, d_dm, rho4, ld)
+        h.xc_potential(code, rho4, ld, ngl, weight, wv4, out[nao * nao:], ws)
+        h.xc_matrix(phi4, ld, nao * ld, nao, ngl, wv4, ld, out[:nao * nao], ws)
+        if self.comm is not None and self.comm.size > 1:
+            self.comm.all_reduce_sum(out)
+        res = out.cpu().numpy()
+        return float(res[-2]), float(res[-1]), res[:nao * nao].reshape(nao, nao).copy()
+
     def get_j(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None):
         return self.get_jk(dm, hermi, kpts, kpts_band, True, False, omega)[0]
 

@@ -188,6 +188,44 @@ class FakeOps:
         ao = oracle.eval_ao(atm, bas, env, coords[b0:b1], Ls, rcut)
         _np(phi)[:, :g1 - g0] = ao[g0 - b0:g1 - b0].T
 
+    def eval_ao_deriv1(self, atm, bas, env, a, mesh, Ls, rcut, g0, g1, phi4, ldphi, comp_stride):
+        from pyscf_isdf_b200.cell import cartesian_prod
+        mesh = [int(m) for m in mesh]
+        coords = cartesian_prod([np.fft.fftfreq(n) for n in mesh]).dot(np.asarray(a))
+        b0 = g0 - g0 % 56
+        b1 = min(len(coords), (g1 + 55) // 56 * 56)
+        ao = oracle.eval_ao(atm, bas, env, coords[b0:b1], Ls, rcut, deriv=1)         # [4, n, nao]
+        _np(phi4)[:, :, :g1 - g0] = ao[:, g0 - b0:g1 - b0].transpose(0, 2, 1)
+
+    # -- exchange-correlation (NumPy restatement of what csrc/xc.cu computes) ---------
+    def xc_code(self, name):
+        if str(name).lower() not in ('lda,', 'blyp', 'pbe'):
+            raise NotImplementedError('xc functional %r' % (name,))
+        return str(name).lower()
+
+    def xc_density(self, phi4, ldphi, comp_stride, nao, ngl, dm, rho4, ldr, ws=None):
+        P = _np(phi4)[:, :nao, :ngl]
+        T = _np(dm).dot(P[0])
+        r = _np(rho4)
+        for c in range(4):
+            r[c, :ngl] = (1.0 if c == 0 else 2.0) * np.einsum('ig,ig->g', P[c], T)
+        return ws
+
+    def xc_potential(self, code, rho4, ldr, ngl, weight, wv4, sums, ws):
+        from oracle import xc
+        r = _np(rho4)[:, :ngl]
+        exc, vrho, vsigma = xc.eval_xc(code, r[0], np.einsum('xg,xg->g', r[1:], r[1:]))
+        w = _np(wv4)
+        w[0, :ngl] = 0.5 * weight * vrho
+        w[1:, :ngl] = 2 * weight * vsigma * r[1:]
+        _np(sums)[:] = [(r[0] * weight).sum(), (r[0] * weight).dot(exc)]
+
+    def xc_matrix(self, phi4, ldphi, comp_stride, nao, ngl, wv4, ldr, vmat, ws):
+        P = _np(phi4)[:, :nao, :ngl]
+        aow = np.einsum('cig,cg->ig', P, _np(wv4)[:, :ngl])
+        m = P[0].dot(aow.T)
+        _np(vmat)[:] = (m + m.T).reshape(-1)
+
     # -- stage 2 / 3 ----------------------------------------------------------------
     def select_create(self, nao, ngl, g_offset, ng_total, npts):
         return FakePlan(nao, ngl, g_offset, ng_total, npts)

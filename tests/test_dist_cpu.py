@@ -44,7 +44,8 @@ def _run_rank(comm, out=None, fit='implicit'):
     vpp = mydf.get_pp_loc()                    # hcore local part on the rank's grid slab, summed over ranks
     vne = mydf.get_nuc()
     vnl = mydf.get_pp_nl()                     # projector part: every rank sums its own range of G vectors
-    res = dict(ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(), vpp=vpp, vne=vne, vnl=vnl,
+    xc_out = {name: mydf.nr_rks(name, dm) for name in ('pbe', 'blyp')}      # GGA exchange-correlation on the rank's slab
+    res = dict(xc=xc_out, ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(), vpp=vpp, vne=vne, vnl=vnl,
                p0=int(mydf._part.ip_off[comm.rank]),
                vj=vj.numpy()[0].copy(), vk=vk.numpy()[0].copy(), slab=mydf._slab,
                panels=mydf.timings['select_panels'])
@@ -75,6 +76,15 @@ def _check(res, tol=1e-9):
     vne0 = opp.potential_matrix(ao, opp.nuc_on_grid(a, mesh, coords, charges))
     assert abs(res['vpp'] - vpp0).max() < 1e-10
     assert abs(res['vne'] - vne0).max() < 1e-10
+    # exchange-correlation (pyscf/pbc/dft/numint.py:283-381) against the oracle pinned to the reference's BLYP numbers
+    import oracle
+    from oracle import xc
+    rcut, Ls = cell.ao_eval_params()
+    ao4 = oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, deriv=1)
+    for name, (ne, exc, vmat) in res['xc'].items():
+        ne0, exc0, vmat0 = xc.nr_rks(ao4, cell.vol / ao4.shape[1], name, rand_dm(cell.nao))
+        assert abs(ne - ne0) < 1e-10 * abs(ne0) and abs(exc - exc0) < 1e-10 * abs(exc0)
+        assert abs(vmat - vmat0).max() < 1e-10 * abs(vmat0).max()
     vnl0 = opp.pp_nl_matrix(a, mesh, cell._atm, cell._bas, cell._env, coords, pps).real      # fft.py:86-145
     assert abs(vnl0).max() > 1e-3 and abs(res['vnl'] - vnl0).max() < 1e-12
 
