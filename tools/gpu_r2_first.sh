@@ -2,15 +2,16 @@
 # First GPU call of round 2: (1) the regular GPU suite incl. the hcore tests written at the end of
 # round 1, (2) the opt-in pivot-kernel forms (ISDF_PANEL_CLUSTER=1/2) for bit-exactness, (3) C64 bench
 # lines for form 0 / 1 / 2 with the selection breakdown, (4) the fused Rader FFT (ISDF_FFT_FUSED=1) and (5) the CRT form of the int8
-# metric product (ISDF_SYRK_CRT=16): tests and a C64 bench line each -- so the defaults can be switched on evidence.
+# metric product (ISDF_SYRK_CRT=16): tests and a C64 bench line each, (6) the GGA exchange-correlation row (tests/test_zz_xc_gpu.py) -- so the defaults can be switched on evidence.
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_panel_forms_gpu.py -m gpu -q > gpurun_out/pytest_forms.log 2>&1; echo "forms rc=$?"; tail -15 gpurun_out/pytest_forms.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_syrk_crt_gpu.py -m gpu -q > gpurun_out/pytest_crt.log 2>&1; echo "crt rc=$?"; tail -15 gpurun_out/pytest_crt.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_fft_fused_gpu.py -m gpu -q > gpurun_out/pytest_fftfused.log 2>&1; echo "fft fused rc=$?"; tail -15 gpurun_out/pytest_fftfused.log
+ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_xc_gpu.py -m gpu -q > gpurun_out/pytest_xc.log 2>&1; echo "xc rc=$?"; tail -15 gpurun_out/pytest_xc.log
 # memory checker on the small experimental tests (slow: only these files)
 ISDF_TEST_EXPERIMENTAL=1 timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest \
-    tests/test_zz_panel_forms_gpu.py tests/test_zz_syrk_crt_gpu.py -m gpu -q -x -k "bit_exact or 200-300 or 128-128" \
+    tests/test_zz_panel_forms_gpu.py tests/test_zz_syrk_crt_gpu.py tests/test_zz_xc_gpu.py -m gpu -q -x -k "bit_exact or 200-300 or 128-128 or he_c or lda" \
     > gpurun_out/sanitizer.log 2>&1; echo "sanitizer rc=$?"; grep -E "ERROR SUMMARY|passed|failed" gpurun_out/sanitizer.log | tail -5
 for mode in 0 1 2; do
   ISDF_PANEL_CLUSTER=$mode ISDF_PROFILE_SELECT=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
