@@ -1,0 +1,49 @@
+"""TEST INFRASTRUCTURE: a plain Gamma-point restricted Hartree-Fock loop around a ``get_jk`` callable,
+so that SCF energies -- the last item of the parity bar -- can be compared with the reference's own
+fixed numbers.  The SCF driver is the CALLER of the ISDF plugin (pyscf/pbc/scf/hf.py in the reference)
+and is not part of the product; this stands in for it in tests only: Roothaan iterations with DIIS on
+the commutator, energy  E = 1/2 Tr[D (h + F)] + E_nuc  (pyscf/scf/hf.py:energy_elec)."""
+import numpy as np
+import scipy.linalg
+
+
+def rhf_gamma(hcore, ovlp, nelec, enuc, get_jk, conv_tol=1e-11, max_cycle=60):
+    """get_jk(dm) -> (vj, vk); returns (e_tot, dm, ncycle)."""
+    nocc = nelec // 2
+
+    def density(f):
+        e, c = scipy.linalg.eigh(f, ovlp)
+        co = c[:, :nocc]
+        return 2 * co.dot(co.T)
+
+    dm = density(hcore)
+    e_last = None
+    errs, focks = [], []
+    for it in range(max_cycle):
+        vj, vk = get_jk(dm)
+        f = hcore + vj - 0.5 * vk
+        e_tot = 0.5 * np.einsum('ij,ji->', dm, hcore + f) + enuc
+        err = f.dot(dm).dot(ovlp)
+        err = err - err.T
+        focks.append(f)
+        errs.append(err)
+        focks, errs = focks[-8:], errs[-8:]
+        if e_last is not None and abs(e_tot - e_last) < conv_tol and abs(err).max() < 1e-7:
+            return e_tot, dm, it + 1
+        e_last = e_tot
+        n = len(errs)
+        if n > 1:
+            B = -np.ones((n + 1, n + 1))
+            B[n, n] = 0
+            for i in range(n):
+                for j in range(n):
+                    B[i, j] = np.vdot(errs[i], errs[j])
+            rhs = np.zeros(n + 1)
+            rhs[n] = -1
+            try:
+                c = np.linalg.solve(B, rhs)[:n]
+                f = sum(ci * fi for ci, fi in zip(c, focks))
+            except np.linalg.LinAlgError:
+                pass
+        dm = density(f)
+    raise RuntimeError('SCF not converged')

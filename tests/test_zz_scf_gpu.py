@@ -1,0 +1,26 @@
+"""GPU: SCF energies through the product path.  The reference's Gamma-point RHF fixture
+(pyscf/pbc/scf/test/test_hf.py:30-43) run with ISDF.get_jk and ISDF.get_nuc inside the test harness's
+Roothaan loop: with n_ip >= the rank of the pair space (21) ISDF is exact, so the energies must equal the
+reference's fixed numbers (test_hf.py:94-95, :129-132).  Tolerance 1e-7 Ha (the reference asserts 7 places;
+the oracle chain itself sits 1.1e-8 from them, tests/test_scf_cpu.py); overlap and kinetic matrices come
+from the oracle (in the reference they come from libcint, outside the ISDF path)."""
+import numpy as np
+import pytest
+from oracle import int1e
+from pyscf_isdf_b200.isdf import ISDF
+from scf_harness import rhf_gamma
+from test_scf_cpu import E_EXX_EWALD, E_EXX_NONE, he2_cell
+
+pytestmark = pytest.mark.gpu
+
+
+def test_rhf_energies_with_isdf_in_the_exact_limit():
+    cell = he2_cell()
+    S, T = int1e.overlap_kinetic(cell.lattice_vectors(), cell._atm, cell._bas, cell._env)
+    mydf = ISDF(cell, n_ip=60).build()
+    assert mydf.n_ip <= 22
+    hcore = T + mydf.get_nuc()
+    enuc = cell.ewald()
+    for exx, gold in ((None, E_EXX_NONE), ('ewald', E_EXX_EWALD)):
+        e, dm, ncyc = rhf_gamma(hcore, S, cell.nelectron, enuc, lambda dm: mydf.get_jk(dm, exxdiv=exx))
+        assert abs(e - gold) < 1e-7, (exx, e - gold)
