@@ -90,6 +90,7 @@ class ISDF:
         self._jk_ws = None
         self._part = None
         self._slab = None
+        self._aoR4 = None          # AO values + gradients of nr_rks
         return self
 
     def release_buffers(self):
@@ -420,7 +421,7 @@ class ISDF:
     def _ao_deriv1_on_grid(self):
         """AO values and gradients of this rank's grid slab, [4, nao, ld] on the device, evaluated on
         first use and kept (4 x the AO matrix; drop with ``self._aoR4 = None``)."""
-        if getattr(self, '_aoR4', None) is not None:
+        if self._aoR4 is not None:
             return self._aoR4
         h = self.handle
         cell = self.cell
