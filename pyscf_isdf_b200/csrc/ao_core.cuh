@@ -64,4 +64,40 @@ __host__ __device__ inline void radial01(const double* ex, const double* cf, int
     *e0 = s0; *e1 = s1;
 }
 
+// Running sums of one contraction of one shell at one grid point over the screened image list of the
+// point's block: acc[k][d], k = value, d/dx, d/dy, d/dz.  img/mind: images kept for the atom and their
+// block-minimum distances; an image contributes to this shell iff mind < rcut (the reference's rule,
+// pyscf/lib/pbc/grid_ao.c:344-365).  ex/cf: exponents and the coefficients of THIS contraction.
+__host__ __device__ inline void shell_point_deriv1(int l, int nprim, const double* ex, const double* cf, double fac,
+                                                   double rcut, const int* img, const double* mind, int cnt,
+                                                   const double* Ls, double ax, double ay, double az,
+                                                   double px, double py, double pz, double (*acc)[7])
+{
+    const int deg = 2 * l + 1;
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int d = 0; d < 7; ++d) acc[k][d] = 0.0;
+    for (int q = 0; q < cnt; ++q) {
+        if (!(mind[q] < rcut)) continue;
+        const int m = img[q];
+        const double dx = px - (ax + Ls[3 * m]);
+        const double dy = py - (ay + Ls[3 * m + 1]);
+        const double dz = pz - (az + Ls[3 * m + 2]);
+        double e0, e1, ang[7], dang[3][7];
+        radial01(ex, cf, nprim, dx * dx + dy * dy + dz * dz, fac, &e0, &e1);
+        ang_grad(l, dx, dy, dz, ang, dang);
+#pragma unroll
+        for (int d = 0; d < 7; ++d) {
+            if (d < deg) {
+                const double r1 = e1 * ang[d];
+                acc[0][d] += e0 * ang[d];
+                acc[1][d] += e0 * dang[0][d] + r1 * dx;
+                acc[2][d] += e0 * dang[1][d] + r1 * dy;
+                acc[3][d] += e0 * dang[2][d] + r1 * dz;
+            }
+        }
+    }
+}
+
 }  // namespace isdf_ao

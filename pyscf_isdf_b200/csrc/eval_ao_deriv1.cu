@@ -161,30 +161,8 @@ __global__ void __launch_bounds__(AO_THREADS) eval_ao_deriv1_kernel(AoParams p)
             for (int c = 0; c < sh.nctr; ++c) {
                 const double* cf = p.env + sh.coef_off + c * sh.nprim;
                 double acc[4][7];
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-#pragma unroll
-                    for (int d = 0; d < 7; ++d) acc[k][d] = 0.0;
-                for (int q = 0; q < cnt; ++q) {
-                    if (!(s_mind[q] < sh.rcut)) continue;
-                    const int m = s_img[q];
-                    const double dx = px - (at.x + p.Ls[3 * m]);
-                    const double dy = py - (at.y + p.Ls[3 * m + 1]);
-                    const double dz = pz - (at.z + p.Ls[3 * m + 2]);
-                    double e0, e1, ang[7], dang[3][7];
-                    isdf_ao::radial01(ex, cf, sh.nprim, dx * dx + dy * dy + dz * dz, fac, &e0, &e1);
-                    isdf_ao::ang_grad(sh.l, dx, dy, dz, ang, dang);
-#pragma unroll
-                    for (int d = 0; d < 7; ++d) {
-                        if (d < deg) {
-                            const double r1 = e1 * ang[d];
-                            acc[0][d] += e0 * ang[d];
-                            acc[1][d] += e0 * dang[0][d] + r1 * dx;
-                            acc[2][d] += e0 * dang[1][d] + r1 * dy;
-                            acc[3][d] += e0 * dang[2][d] + r1 * dz;
-                        }
-                    }
-                }
+                isdf_ao::shell_point_deriv1(sh.l, sh.nprim, ex, cf, fac, sh.rcut, s_img, s_mind, cnt, p.Ls,
+                                            at.x, at.y, at.z, px, py, pz, acc);
                 if (valid && g >= p.g0 && g < p.g1) {
 #pragma unroll
                     for (int k = 0; k < 4; ++k)

@@ -37,3 +37,26 @@ def test_shell_values_and_gradients(lib, l):
                         ctypes.c_double(FAC_SP.get(l, 1.0)), ctypes.c_longlong(n), p(np.ascontiguousarray(dr)), p(out))
     assert abs(ref).max() > 0.1
     assert abs(out - ref).max() < 1e-13 * max(1.0, abs(ref).max())
+
+
+@pytest.mark.parametrize('which', ['he_c', 'c8'])
+def test_whole_grid_with_image_screening(lib, which):
+    """The kernel's per-point accumulation (shared routine) with the kernel's block / image-list structure
+    on real cells -- lattice sums, two contractions per shell, s/p/d shells -- against the oracle."""
+    import oracle
+    from util import diamond_c8, he_c_cell
+    cell = he_c_cell() if which == 'he_c' else diamond_c8([9, 10, 8], basis='gth-dzvp', jitter=0.15)
+    rcut, Ls = cell.ao_eval_params()
+    coords = np.ascontiguousarray(cell.get_uniform_grids())
+    ref = oracle.eval_ao(cell._atm, cell._bas, cell._env, coords, Ls, rcut, deriv=1).transpose(0, 2, 1)   # [4, nao, ng]
+    out = np.zeros(ref.shape)
+    atm = np.ascontiguousarray(cell._atm, dtype=np.int32)
+    bas = np.ascontiguousarray(cell._bas, dtype=np.int32)
+    env = np.ascontiguousarray(cell._env, dtype=np.float64)
+    rc = np.ascontiguousarray(rcut, dtype=np.float64)
+    Lc = np.ascontiguousarray(Ls, dtype=np.float64)
+    p = lambda a: a.ctypes.data_as(ctypes.c_void_p)          # noqa: E731
+    lib.ao_grid_deriv1(p(atm), ctypes.c_int(len(atm)), p(bas), ctypes.c_int(len(bas)), p(env), p(rc), p(Lc),
+                       ctypes.c_int(len(Lc)), ctypes.c_longlong(len(coords)), p(coords), p(out))
+    assert abs(ref[1:]).max() > 0.1
+    assert abs(out - ref).max() < 1e-12
