@@ -26,19 +26,7 @@ xc_rho_kernel(const double* __restrict__ phi4, long long ldphi, long long cstrid
 {
     const int g = blockIdx.x * XC_THREADS + threadIdx.x;
     if (g >= ngl) return;
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    for (int mu = 0; mu < nao; ++mu) {
-        const long long o = (long long)mu * ldphi + g;
-        const double t = T[o];
-        s0 = fma(phi4[o], t, s0);
-        s1 = fma(phi4[o + cstride], t, s1);
-        s2 = fma(phi4[o + 2 * cstride], t, s2);
-        s3 = fma(phi4[o + 3 * cstride], t, s3);
-    }
-    rho4[g] = s0;
-    rho4[ldr + g] = 2.0 * s1;
-    rho4[2 * ldr + g] = 2.0 * s2;
-    rho4[3 * ldr + g] = 2.0 * s3;
+    isdf_xc::rho_item(g, phi4, ldphi, cstride, T, nao, rho4, ldr);
 }
 
 // functional at every grid point; wv4 = weight (vrho/2, 2 vsigma grad rho); per-block partial sums of
@@ -50,18 +38,7 @@ xc_point_kernel(int code, const double* __restrict__ rho4, long long ldr, int ng
     __shared__ double s_n[XC_THREADS], s_e[XC_THREADS];
     const int g = blockIdx.x * XC_THREADS + threadIdx.x;
     double den = 0.0, ex = 0.0;
-    if (g < ngl) {
-        const double rho = rho4[g], gx = rho4[ldr + g], gy = rho4[2 * ldr + g], gz = rho4[3 * ldr + g];
-        double exc, vrho, vsigma;
-        isdf_xc::eval_point(code, rho, gx * gx + gy * gy + gz * gz, &exc, &vrho, &vsigma);
-        den = rho * weight;
-        ex = den * exc;
-        const double f = 2.0 * weight * vsigma;
-        wv4[g] = 0.5 * weight * vrho;
-        wv4[ldr + g] = f * gx;
-        wv4[2 * ldr + g] = f * gy;
-        wv4[3 * ldr + g] = f * gz;
-    }
+    if (g < ngl) isdf_xc::point_item(code, g, rho4, ldr, weight, wv4, &den, &ex);
     s_n[threadIdx.x] = den; s_e[threadIdx.x] = ex;
     __syncthreads();
     for (int o = XC_THREADS / 2; o > 0; o >>= 1) {
@@ -94,11 +71,7 @@ xc_aow_kernel(const double* __restrict__ phi4, long long ldphi, long long cstrid
 {
     const int g = blockIdx.x * XC_THREADS + threadIdx.x;
     if (g >= ngl) return;
-    const double w0 = wv4[g], w1 = wv4[ldr + g], w2 = wv4[2 * ldr + g], w3 = wv4[3 * ldr + g];
-    for (int mu = blockIdx.y; mu < nao; mu += gridDim.y) {
-        const long long o = (long long)mu * ldphi + g;
-        aow[o] = fma(w3, phi4[o + 3 * cstride], fma(w2, phi4[o + 2 * cstride], fma(w1, phi4[o + cstride], w0 * phi4[o])));
-    }
+    isdf_xc::aow_item(g, blockIdx.y, gridDim.y, phi4, ldphi, cstride, wv4, ldr, nao, aow);
 }
 
 // vmat = mat + mat^T

@@ -134,4 +134,53 @@ __host__ __device__ inline bool eval_point(int code, double rho, double sigma, d
     return true;
 }
 
+// ---- per-grid-point bodies of the streaming kernels of xc.cu (shared with tests/emul/xc_emul.cpp) ----
+
+// rho4[c][g] = f_c sum_mu phi_c[mu,g] T[mu,g],  f = 1, 2, 2, 2   (eval_rho, pyscf/pbc/dft/numint.py:138-145)
+__host__ __device__ inline void rho_item(long long g, const double* phi4, long long ldphi, long long cstride,
+                                         const double* T, int nao, double* rho4, long long ldr)
+{
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    for (int mu = 0; mu < nao; ++mu) {
+        const long long o = (long long)mu * ldphi + g;
+        const double t = T[o];
+        s0 = fma(phi4[o], t, s0);
+        s1 = fma(phi4[o + cstride], t, s1);
+        s2 = fma(phi4[o + 2 * cstride], t, s2);
+        s3 = fma(phi4[o + 3 * cstride], t, s3);
+    }
+    rho4[g] = s0;
+    rho4[ldr + g] = 2.0 * s1;
+    rho4[2 * ldr + g] = 2.0 * s2;
+    rho4[3 * ldr + g] = 2.0 * s3;
+}
+
+// functional at one point: wv4 = weight (vrho/2, 2 vsigma grad rho) (numint.py:366, :987-994);
+// den = rho weight, ex = den exc (numint.py:361-365)
+__host__ __device__ inline void point_item(int code, long long g, const double* rho4, long long ldr, double weight,
+                                           double* wv4, double* den, double* ex)
+{
+    const double rho = rho4[g], gx = rho4[ldr + g], gy = rho4[2 * ldr + g], gz = rho4[3 * ldr + g];
+    double exc, vrho, vsigma;
+    eval_point(code, rho, gx * gx + gy * gy + gz * gz, &exc, &vrho, &vsigma);
+    *den = rho * weight;
+    *ex = *den * exc;
+    const double f = 2.0 * weight * vsigma;
+    wv4[g] = 0.5 * weight * vrho;
+    wv4[ldr + g] = f * gx;
+    wv4[2 * ldr + g] = f * gy;
+    wv4[3 * ldr + g] = f * gz;
+}
+
+// aow[mu,g] = sum_c wv4[c][g] phi_c[mu,g] for mu = mu0, mu0 + step, ...   (_scale_ao, numint.py:812-814)
+__host__ __device__ inline void aow_item(long long g, int mu0, int step, const double* phi4, long long ldphi,
+                                         long long cstride, const double* wv4, long long ldr, int nao, double* aow)
+{
+    const double w0 = wv4[g], w1 = wv4[ldr + g], w2 = wv4[2 * ldr + g], w3 = wv4[3 * ldr + g];
+    for (int mu = mu0; mu < nao; mu += step) {
+        const long long o = (long long)mu * ldphi + g;
+        aow[o] = fma(w3, phi4[o + 3 * cstride], fma(w2, phi4[o + 2 * cstride], fma(w1, phi4[o + cstride], w0 * phi4[o])));
+    }
+}
+
 }  // namespace isdf_xc

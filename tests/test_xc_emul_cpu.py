@@ -55,3 +55,35 @@ def test_dual_number_functionals_match_the_oracle(lib, name):
 def test_unknown_code_is_an_error(lib):
     rc, _ = _eval(lib, 9, np.ones(2), np.ones(2))
     assert rc == 1
+
+
+@pytest.mark.parametrize('name', ['pbe', 'blyp'])
+def test_streaming_kernel_bodies_give_nr_rks(lib, name):
+    """rho / functional / aow item routines of xc.cu on a real cell, NumPy products in place of the two
+    GEMMs: (nelec, exc, vmat) equal the oracle's nr_rks; padding columns stay untouched."""
+    import oracle
+    import sys
+    sys.path.insert(0, HERE)
+    from util import diamond_c8, rand_dm
+    cell = diamond_c8([9, 10, 8], basis='gth-dzvp', jitter=0.15)
+    rcut, Ls = cell.ao_eval_params()
+    ao4 = oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, deriv=1)   # [4, ng, nao]
+    ng, nao = ao4.shape[1:]
+    ld = (ng + 7) // 8 * 8 + 8
+    phi4 = np.zeros((4, nao, ld))
+    phi4[:, :, :ng] = ao4.transpose(0, 2, 1)
+    dm = rand_dm(nao) * 0.05
+    weight = cell.vol / ng
+    T = np.ascontiguousarray(dm.dot(phi4[0]))
+    rho4 = np.full((4, ld), 7.0)
+    wv4 = np.full((4, ld), 7.0)
+    aow = np.full((nao, ld), 7.0)
+    sums = np.zeros(2)
+    p = lambda a: a.ctypes.data_as(ctypes.c_void_p)          # noqa: E731
+    lib.xc_stream_items(ctypes.c_int(CODES[name]), ctypes.c_int(nao), ctypes.c_longlong(ng), ctypes.c_longlong(ld),
+                        p(phi4), p(T), ctypes.c_double(weight), p(rho4), p(wv4), p(aow), p(sums), ctypes.c_int(5))
+    m = phi4[0, :, :ng].dot(aow[:, :ng].T)
+    ne0, exc0, vmat0 = xc.nr_rks(ao4, weight, name, dm)
+    assert abs(sums[0] - ne0) < 1e-12 * abs(ne0) and abs(sums[1] - exc0) < 1e-12 * abs(exc0)
+    assert abs(m + m.T - vmat0).max() < 1e-12 * abs(vmat0).max()
+    assert (rho4[:, ng:] == 7.0).all() and (wv4[:, ng:] == 7.0).all() and (aow[:, ng:] == 7.0).all()
