@@ -198,7 +198,7 @@ int isdf_j_from_potential(isdf_handle* h, const double* phi, long long ldphi, in
  *                        reference; published closed forms here, csrc/xc_core.cuh]; writes
  *                        wv4[4, ldr] = weight (vrho/2, 2 vsigma grad rho) [numint.py:366, :987-994] and
  *                        d_sums[2] (device) = (sum rho weight, sum rho weight exc) [numint.py:361-365].
- *                        code from isdf_xc_code("lda," | "blyp" | "pbe"), -1 if unknown.
+ *                        code from isdf_xc_code("lda," | "lda,vwn" | "blyp" | "pbe"), -1 if unknown.
  *   isdf_xc_matrix       vmat[nao, nao] = M + M^T, M = Phi (sum_c wv_c Phi_c)^T [_vxc_mat, numint.py:812-815, :374].
  * A sharded grid sums vmat and d_sums over ranks.  Workspace of the three xc calls: isdf_xc_ws_bytes. */
 int isdf_eval_ao_deriv1(isdf_handle* h,

@@ -8,7 +8,8 @@ not in its tree; the reference calls it through ``pyscf/dft/libxc.py:eval_xc``),
 their published closed forms are restated here as energy densities ``f(rho, sigma)``
 per unit volume and differentiated by the complex-step rule (exact to rounding for
 these analytic expressions):
-  Slater exchange; Becke 88 exchange (Phys. Rev. A 38, 3098); LYP correlation in the
+  Slater exchange; VWN correlation (form V, Can. J. Phys. 58, 1200; libxc's lda_c_vwn, the
+  'vwn' of the reference's default 'LDA,VWN'); Becke 88 exchange (Phys. Rev. A 38, 3098); LYP correlation in the
   form of Miehlich et al. (Chem. Phys. Lett. 157, 200); PBE exchange and correlation
   (Phys. Rev. Lett. 77, 3865) on the PW92 correlation with libxc's ``pw_mod`` constants.
 
@@ -81,7 +82,21 @@ def f_pbe_c(rho, sigma):
     return rho * (ec + gamma * np.log(1 + beta / gamma * t2 * (1 + At2) / (1 + At2 + At2 * At2)))
 
 
+def f_vwn5(rho, sigma):
+    A, b, c, x0 = 0.0310907, 3.72744, 12.9352, -0.10498
+    x = np.sqrt((3 / (4 * np.pi * rho))**(1 / 3.))
+    X = x * x + b * x + c
+    X0 = x0 * x0 + b * x0 + c
+    Q = np.sqrt(4 * c - b * b)
+    at = np.arctan(Q / (2 * x + b))
+    ec = A * (np.log(x * x / X) + 2 * b / Q * at
+              - b * x0 / X0 * (np.log((x - x0)**2 / X) + 2 * (b + 2 * x0) / Q * at))
+    return rho * ec
+
+
 FUNCTIONALS = {
+    'lda,vwn': (f_slater, f_vwn5),
+    ',vwn': (f_vwn5,),
     'lda,': (f_slater,),
     'b88,': (f_b88,),
     ',lyp': (f_lyp,),

@@ -256,7 +256,7 @@ class Handle:
     def xc_code(self, name):
         code = self.lib.isdf_xc_code(str(name).encode())
         if code < 0:
-            raise NotImplementedError('xc functional %r (have: lda, / blyp / pbe)' % (name,))
+            raise NotImplementedError('xc functional %r (have: lda, / lda,vwn / blyp / pbe)' % (name,))
         return code
 
     def xc_density(self, phi4, ldphi, comp_stride, nao, ngl, dm, rho4, ldr, ws=None):

@@ -3,7 +3,7 @@
 // that each functional is written once, as its published energy expression, and no derivative is
 // derived by hand.  What the reference gets from libxc through pyscf/dft/libxc.py:eval_xc (spin = 0,
 // deriv = 1): exc per particle, vrho, vsigma.
-//   Slater exchange; Becke 88 exchange (Phys. Rev. A 38, 3098); LYP correlation in the closed-shell
+//   Slater exchange; VWN correlation, form V (Can. J. Phys. 58, 1200); Becke 88 exchange (Phys. Rev. A 38, 3098); LYP correlation in the closed-shell
 //   form of Miehlich et al. (Chem. Phys. Lett. 157, 200); PBE exchange and correlation (Phys. Rev.
 //   Lett. 77, 3865) over PW92 with libxc's pw_mod constants.
 // Like fft_core.cuh and crt_core.cuh this header also compiles with g++ (tests/emul/xc_emul.cpp), where
@@ -17,6 +17,7 @@ namespace isdf_xc {
 constexpr int XC_LDA_X = 1;      // 'lda,'
 constexpr int XC_BLYP = 2;       // 'blyp' = b88 + lyp
 constexpr int XC_PBE = 3;        // 'pbe'  = pbe exchange + pbe correlation
+constexpr int XC_LDA_VWN = 4;    // 'lda,vwn' = slater + vwn (form V): the default xc of the reference's pbc RKS
 constexpr double RHO_CUT = 1e-15;
 constexpr double SIGMA_FLOOR = 1e-40;
 constexpr double PI = 3.14159265358979323846;
@@ -50,6 +51,22 @@ __host__ __device__ __forceinline__ Dual dsqrt(Dual a) { const double v = sqrt(a
 __host__ __device__ __forceinline__ Dual dexp(Dual a) { const double v = exp(a.v); return chain(a, v, v); }
 __host__ __device__ __forceinline__ Dual dlog(Dual a) { return chain(a, log(a.v), 1.0 / a.v); }
 __host__ __device__ __forceinline__ Dual dasinh(Dual a) { return chain(a, asinh(a.v), 1.0 / sqrt(1.0 + a.v * a.v)); }
+
+__host__ __device__ __forceinline__ Dual datan(Dual a) { return chain(a, atan(a.v), 1.0 / (1.0 + a.v * a.v)); }
+
+__host__ __device__ inline Dual f_vwn5(Dual rho)
+{
+    const double A = 0.0310907, b = 3.72744, c = 12.9352, x0 = -0.10498;
+    const Dual x = dsqrt(dpow(3.0 / (4.0 * PI) / rho, 1.0 / 3.0));
+    const Dual X = x * x + b * x + c;
+    const double X0 = x0 * x0 + b * x0 + c;
+    const double Q = sqrt(4.0 * c - b * b);
+    const Dual at = datan(Q / (2.0 * x + b));
+    const Dual xm = x - x0;
+    const Dual ec = A * (dlog(x * x / X) + 2.0 * b / Q * at
+                         - b * x0 / X0 * (dlog(xm * xm / X) + 2.0 * (b + 2.0 * x0) / Q * at));
+    return rho * ec;
+}
 
 __host__ __device__ inline Dual f_slater(Dual rho)
 {
@@ -122,12 +139,13 @@ __host__ __device__ inline Dual f_pbe_c(Dual rho, Dual sigma)
 __host__ __device__ inline bool eval_point(int code, double rho, double sigma, double* exc, double* vrho, double* vsigma)
 {
     *exc = 0.0; *vrho = 0.0; *vsigma = 0.0;
-    if (code != XC_LDA_X && code != XC_BLYP && code != XC_PBE) return false;
+    if (code != XC_LDA_X && code != XC_BLYP && code != XC_PBE && code != XC_LDA_VWN) return false;
     if (!(rho > RHO_CUT)) return true;
     const Dual r{rho, 1.0, 0.0};
     const Dual s{sigma > SIGMA_FLOOR ? sigma : SIGMA_FLOOR, 0.0, 1.0};
     Dual f;
     if (code == XC_LDA_X) f = f_slater(r);
+    else if (code == XC_LDA_VWN) f = f_slater(r) + f_vwn5(r);
     else if (code == XC_BLYP) f = f_b88(r, s) + f_lyp(r, s);
     else f = f_pbe_x(r, s) + f_pbe_c(r, s);
     *exc = f.v / rho; *vrho = f.r; *vsigma = f.s;

@@ -439,7 +439,7 @@ class ISDF:
 
     def nr_rks(self, xc_code, dm, kpts=None):
         """(nelec, exc, vmat) of a closed-shell density matrix at the Gamma point: NumInt.nr_rks of the
-        reference (pyscf/pbc/dft/numint.py:283-381) for the functionals 'lda,', 'blyp' and 'pbe', on the
+        reference (pyscf/pbc/dft/numint.py:283-381) for the functionals 'lda,', 'lda,vwn', 'blyp' and 'pbe', on the
         device: density and gradient from the AO values, the functional, and the potential matrix.  With a
         sharded grid every rank works on its slab and the three results are summed over ranks."""
         self._check_gamma(kpts)

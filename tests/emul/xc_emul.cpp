@@ -4,7 +4,7 @@
 #define __device__
 #define __forceinline__ inline
 #include <cmath>
-using std::pow; using std::sqrt; using std::exp; using std::log; using std::asinh; using std::fma;
+using std::pow; using std::sqrt; using std::exp; using std::log; using std::asinh; using std::fma; using std::atan;
 #include "../../pyscf_isdf_b200/csrc/xc_core.cuh"
 
 extern "C" int xc_eval(int code, long long n, const double* rho, const double* sigma,

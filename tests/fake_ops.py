@@ -199,7 +199,7 @@ class FakeOps:
 
     # -- exchange-correlation (NumPy restatement of what csrc/xc.cu computes) ---------
     def xc_code(self, name):
-        if str(name).lower() not in ('lda,', 'blyp', 'pbe'):
+        if str(name).lower() not in ('lda,', 'blyp', 'pbe', 'lda,vwn'):
             raise NotImplementedError('xc functional %r' % (name,))
         return str(name).lower()
 

@@ -61,7 +61,7 @@ def test_functional_derivatives_and_published_limits():
     rng = np.random.default_rng(3)
     rho = 10.0**rng.uniform(-4, 1, 200)
     sigma = rho**(8 / 3.) * 10.0**rng.uniform(-3, 2, 200)
-    for code in ('blyp', 'pbe', 'lda,'):
+    for code in ('blyp', 'pbe', 'lda,', 'lda,vwn'):
         exc, vr, vs = xc.eval_xc(code, rho, sigma)
         f = lambda r, s: xc.eval_xc(code, r, s)[0] * r            # noqa: E731
         hr, hs = 1e-5 * rho, 1e-5 * sigma
@@ -80,6 +80,13 @@ def test_functional_derivatives_and_published_limits():
     assert abs(xc.f_pbe_c(r, 1e14 * r)) < 1e-6
     # PW92 at rs = 1 and 2 (Perdew & Wang 1992, table: -0.0598, -0.0448 Ha to the digits given)
     assert abs(xc.eps_pw92(np.array([1.0, 2.0])) - np.array([-0.0598, -0.0448])).max() < 1.5e-4
+    # VWN (form V) against PW92: two fits of the same Monte-Carlo data, within 6e-4 Ha over rs = 0.5 .. 20;
+    # and its own published high-density coefficient A ln rs: d eps / d ln rs -> A = 0.0310907 as rs -> 0
+    rs_ = np.array([0.5, 1.0, 2.0, 5.0, 10.0, 20.0])
+    rr = 3 / (4 * np.pi * rs_**3)
+    assert abs(xc.f_vwn5(rr, 0 * rr) / rr - xc.eps_pw92(rs_)).max() < 6e-4
+    e = lambda x: xc.f_vwn5(np.array([3 / (4 * np.pi * x**3)]), 0.0)[0] / (3 / (4 * np.pi * x**3))      # noqa: E731
+    assert abs((e(2e-6) - e(1e-6)) / np.log(2.0) - 0.0310907) < 2e-4
     # densities below the threshold give zeros, not NaNs
     e0, v0, s0 = xc.eval_xc('pbe', np.array([0.0, 1e-20]), np.array([0.0, 1e-30]))
     assert (e0 == 0).all() and (v0 == 0).all() and (s0 == 0).all()
