@@ -16,8 +16,9 @@ these analytic expressions):
 Pinning: ``nr_rks(..., 'blyp', ...)`` reproduces the reference's fixed numbers of
 pyscf/pbc/dft/test/test_numint.py:183-206 (electron count, exc, fingerprint of vmat at a
 k-point), which pins the density, gradient and matrix assembly and the B88 and LYP
-restatements; the AO gradients reproduce test_numint.py:77-100.  The reference holds no
-fixed number for PBE: its formulas are **unpinned** beyond the published limits checked in
+restatements; the AO gradients reproduce test_numint.py:77-100.  Slater + VWN is pinned through the reference's
+Gamma-point RKS energies of diamond (pyscf/pbc/dft/test/test_krks.py:90-118, tests/test_scf_cpu.py).  The
+reference holds no fixed number for PBE: its formulas are **unpinned** beyond the published limits checked in
 tests/test_xc_cpu.py.
 """
 import numpy as np

@@ -47,3 +47,47 @@ def rhf_gamma(hcore, ovlp, nelec, enuc, get_jk, conv_tol=1e-11, max_cycle=60):
                 pass
         dm = density(f)
     raise RuntimeError('SCF not converged')
+
+
+def rks_gamma(hcore, ovlp, nelec, enuc, get_j, nr_rks, conv_tol=1e-10, max_cycle=80):
+    """Restricted Kohn-Sham with a pure functional: get_j(dm) -> vj, nr_rks(dm) -> (nelec, exc, vxc);
+    E = Tr[D h] + 1/2 Tr[D J] + Exc + E_nuc (pyscf/pbc/dft/rks.py:44-125).  Returns (e_tot, dm, ncycle)."""
+    nocc = nelec // 2
+
+    def density(f):
+        e, c = scipy.linalg.eigh(f, ovlp)
+        co = c[:, :nocc]
+        return 2 * co.dot(co.T)
+
+    dm = density(hcore)
+    e_last = None
+    errs, focks = [], []
+    for it in range(max_cycle):
+        vj = get_j(dm)
+        _, exc, vxc = nr_rks(dm)
+        f = hcore + vj + vxc
+        e_tot = np.einsum('ij,ji->', dm, hcore) + 0.5 * np.einsum('ij,ji->', dm, vj) + exc + enuc
+        err = f.dot(dm).dot(ovlp)
+        err = err - err.T
+        focks.append(f)
+        errs.append(err)
+        focks, errs = focks[-8:], errs[-8:]
+        if e_last is not None and abs(e_tot - e_last) < conv_tol and abs(err).max() < 1e-6:
+            return e_tot, dm, it + 1
+        e_last = e_tot
+        n = len(errs)
+        if n > 1:
+            B = -np.ones((n + 1, n + 1))
+            B[n, n] = 0
+            for i in range(n):
+                for j in range(n):
+                    B[i, j] = np.vdot(errs[i], errs[j])
+            rhs = np.zeros(n + 1)
+            rhs[n] = -1
+            try:
+                c = np.linalg.solve(B, rhs)[:n]
+                f = sum(ci * fi for ci, fi in zip(c, focks))
+            except np.linalg.LinAlgError:
+                pass
+        dm = density(f)
+    raise RuntimeError('SCF not converged')

@@ -57,3 +57,53 @@ def test_rhf_energies_reproduce_the_reference():
         # lattice sums truncated at precision 1e-8)
         assert abs(e - gold) < 5e-8, (exx, e - gold)
         assert abs(np.einsum('ij,ji->', dm, S) - 4) < 1e-10
+
+
+# ---------------------------------------------------------------------------
+# Kohn-Sham LDA on diamond with GTH pseudopotentials: every piece of the one-electron and
+# exchange-correlation rows in one number
+# ---------------------------------------------------------------------------
+E_LDA_C8_CUBIC = -44.892502703975893       # pyscf/pbc/dft/test/test_krks.py:90-97  (RKS, 'lda,vwn', Gamma, mesh 17^3)
+E_LDA_C2_PRIMITIVE = -10.221426445656439   # pyscf/pbc/dft/test/test_krks.py:111-118
+
+
+def diamond_cubic(mesh):
+    """Fixture of pyscf/pbc/dft/test/test_krks.py:27-49 (8 C, gth-szv / gth-pade)."""
+    return Cell(unit='A', a=np.eye(3) * 3.5668, mesh=mesh, basis='gth-szv', pseudo='gth-pade',
+                atom='''C 0. 0. 0.; C 0.8917 0.8917 0.8917; C 1.7834 1.7834 0.; C 2.6751 2.6751 0.8917;
+                        C 1.7834 0. 1.7834; C 2.6751 0.8917 2.6751; C 0. 1.7834 1.7834; C 0.8917 2.6751 2.6751''').build()
+
+
+def diamond_primitive(mesh):
+    """Fixture of pyscf/pbc/dft/test/test_krks.py:51-65 (2 C, fcc lattice vectors)."""
+    return Cell(unit='A', atom='C 0. 0. 0.; C 0.8917 0.8917 0.8917', basis='gth-szv', pseudo='gth-pade', mesh=mesh,
+                a=[[0, 1.7834, 1.7834], [1.7834, 0, 1.7834], [1.7834, 1.7834, 0]]).build()
+
+
+def oracle_rks_pieces(cell):
+    """(S, hcore = T + local + non-local pseudopotential, ao4[4, ng, nao]) from the oracle."""
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    S, T = int1e.overlap_kinetic(a, cell._atm, cell._bas, cell._env)
+    rcut, Ls = cell.ao_eval_params()
+    ao4 = oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, deriv=1)
+    coords = cell.atom_coords()
+    charges = [float(z) for z in cell.atom_charges()]
+    pps = [cell._pseudo_for(cell.atom_symbol(i)) for i in range(cell.natm)]
+    vpp = opp.potential_matrix(ao4[0], opp.pp_loc_on_grid(a, mesh, coords, charges, pps)) \
+        + opp.pp_nl_matrix(a, mesh, cell._atm, cell._bas, cell._env, coords, pps).real
+    return S, T + vpp, ao4
+
+
+def test_rks_lda_energies_of_diamond_reproduce_the_reference():
+    """Local and non-local GTH pseudopotential, Coulomb, Slater + VWN, kinetic/overlap, Ewald: the
+    reference's two Gamma-point numbers to 1e-8 Ha (observed 6e-10 and 4e-10; it asserts 7 places)."""
+    from oracle import xc
+    from scf_harness import rks_gamma
+    for cell, gold in ((diamond_primitive([17] * 3), E_LDA_C2_PRIMITIVE), (diamond_cubic([17] * 3), E_LDA_C8_CUBIC)):
+        S, hcore, ao4 = oracle_rks_pieces(cell)
+        a, mesh = cell.lattice_vectors(), cell.mesh
+        w = cell.vol / ao4.shape[1]
+        e, dm, ncyc = rks_gamma(hcore, S, cell.nelectron, cell.ewald(),
+                                lambda dm: oracle.fftdf_get_j(ao4[0], dm, a, mesh),
+                                lambda dm: xc.nr_rks(ao4, w, 'lda,vwn', dm))
+        assert abs(e - gold) < 1e-8, (cell.natm, e - gold)

@@ -24,3 +24,31 @@ def test_rhf_energies_with_isdf_in_the_exact_limit():
     for exx, gold in ((None, E_EXX_NONE), ('ewald', E_EXX_EWALD)):
         e, dm, ncyc = rhf_gamma(hcore, S, cell.nelectron, enuc, lambda dm: mydf.get_jk(dm, exxdiv=exx))
         assert abs(e - gold) < 1e-7, (exx, e - gold)
+
+
+def _rks_diamond(xc_on_device):
+    """RKS 'lda,vwn' on the reference's cubic diamond fixture (pyscf/pbc/dft/test/test_krks.py:90-97) with the
+    product's get_pp (local part on the device, projectors on the host) and exact-density J on the device;
+    exchange-correlation from ISDF.nr_rks on the device, or from the oracle."""
+    from oracle import xc
+    from scf_harness import rks_gamma
+    from test_scf_cpu import E_LDA_C8_CUBIC, diamond_cubic, oracle_rks_pieces
+    cell = diamond_cubic([17] * 3)
+    S, _, ao4 = oracle_rks_pieces(cell)
+    T = int1e.overlap_kinetic(cell.lattice_vectors(), cell._atm, cell._bas, cell._env)[1]
+    mydf = ISDF(cell, c=10, exact_j=True).build()
+    hcore = T + mydf.get_pp()
+    w = cell.vol / ao4.shape[1]
+    nr_rks = (lambda dm: mydf.nr_rks('lda,vwn', dm)) if xc_on_device else (lambda dm: xc.nr_rks(ao4, w, 'lda,vwn', dm))
+    e, dm, ncyc = rks_gamma(hcore, S, cell.nelectron, cell.ewald(), lambda dm: mydf.get_j(dm), nr_rks)
+    assert abs(e - E_LDA_C8_CUBIC) < 1e-7, e - E_LDA_C8_CUBIC
+
+
+def test_rks_lda_energy_of_diamond_with_device_hcore_and_j():
+    _rks_diamond(False)
+
+
+@pytest.mark.skipif(__import__('os').environ.get('ISDF_TEST_EXPERIMENTAL') != '1',
+                    reason='exchange-correlation kernels not yet validated on a B200 (set ISDF_TEST_EXPERIMENTAL=1)')
+def test_rks_lda_energy_of_diamond_all_on_device():
+    _rks_diamond(True)
