@@ -8,7 +8,7 @@ timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_panel_forms_gpu.py -m gpu -q > gpurun_out/pytest_forms.log 2>&1; echo "forms rc=$?"; tail -15 gpurun_out/pytest_forms.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_syrk_crt_gpu.py -m gpu -q > gpurun_out/pytest_crt.log 2>&1; echo "crt rc=$?"; tail -15 gpurun_out/pytest_crt.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_fft_fused_gpu.py -m gpu -q > gpurun_out/pytest_fftfused.log 2>&1; echo "fft fused rc=$?"; tail -15 gpurun_out/pytest_fftfused.log
-ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_xc_gpu.py -m gpu -q > gpurun_out/pytest_xc.log 2>&1; echo "xc rc=$?"; tail -15 gpurun_out/pytest_xc.log
+ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_xc_gpu.py tests/test_zz_scf_gpu.py -m gpu -q > gpurun_out/pytest_xc.log 2>&1; echo "xc rc=$?"; tail -15 gpurun_out/pytest_xc.log
 # memory checker on the small experimental tests (slow: only these files)
 ISDF_TEST_EXPERIMENTAL=1 timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest \
     tests/test_zz_panel_forms_gpu.py tests/test_zz_syrk_crt_gpu.py tests/test_zz_xc_gpu.py -m gpu -q -x -k "bit_exact or 200-300 or 128-128 or he_c or lda" \
