@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--jk-reps', type=int, default=5)
     ap.add_argument('--no-e2e', action='store_true', help='exploratory runs only: skip the host-API leg')
+    ap.add_argument('--xc', default=None,
+                    help="also time ISDF.nr_rks(XC, dm) per SCF iteration ('pbe' for BASELINE configs[1]); reported "
+                         "beside the headline under 'xc', never part of 'value'")
     return ap.parse_args()
 
 
@@ -215,6 +218,36 @@ def cpu_sample_target(cell, npts, seed=5):
     return t, desc
 
 
+def cpu_full_run(cell, npts):
+    """Small workloads (C8 and below): every stage of the NumPy/SciPy oracle in full, timed as it runs."""
+    import oracle
+    from oracle import isdf_ref
+    from pyscf_isdf_b200.workloads import synthetic_dm
+    t = {}
+    rcut, Ls = cell.ao_eval_params()
+    a = cell.lattice_vectors()
+    t0 = time.perf_counter()
+    phi = np.ascontiguousarray(oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut).T)
+    t['ao'] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    ip, resid = isdf_ref.select_ip(phi, npts)
+    t['select'] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    zeta = isdf_ref.fit_aux(phi, ip)
+    t['fit'] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    V = isdf_ref.build_V(zeta, a, cell.mesh)
+    t['fft'] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    W = isdf_ref.build_W(zeta, a, cell.mesh, V=V)
+    t['wgemm'] = time.perf_counter() - t0
+    X = np.ascontiguousarray(phi[:, ip])
+    t0 = time.perf_counter()
+    oracle.isdf_get_jk(X, W, synthetic_dm(cell.nao))
+    t['jk'] = time.perf_counter() - t0
+    return t, 'the whole workload, every stage of the oracle in full (no sampling, no extrapolation)'
+
+
 def cpu_baseline_run(cell, npts):
     """(total s, build s, J/K s, per-stage s, description, cores) of one bounded CPU sample."""
     from oracle import pbc_tools
@@ -224,7 +257,11 @@ def cpu_baseline_run(cell, npts):
     # and the Np-dependence of each stage's work model is applied on top (said in the description)
     nps = npts if npts <= 16384 else 12480
     try:
-        t, desc = cpu_sample_target(cell, nps)
+        ng = int(np.prod(cell.mesh))
+        if float(ng) * npts * npts <= 2e11:
+            t, desc = cpu_full_run(cell, npts)       # small workloads: the whole oracle, no sampling
+        else:
+            t, desc = cpu_sample_target(cell, nps)
     finally:
         pbc_tools.FFT_WORKERS = 1
     if nps != npts:
@@ -377,6 +414,22 @@ def run_b200(args):
         jk_ms.append(a0.elapsed_time(a1))
     jk_ms = float(np.median(jk_ms[2:]))
 
+    # exchange-correlation per SCF iteration (optional): first call evaluates the AO gradients
+    xc_info = None
+    if args.xc:
+        t0 = time.perf_counter()
+        mydf.nr_rks(args.xc, dm_host[0])
+        torch.cuda.synchronize(dev)
+        first_s = time.perf_counter() - t0
+        xs = []
+        for _ in range(args.jk_reps):
+            t0 = time.perf_counter()
+            ne, exc, vxc = mydf.nr_rks(args.xc, dm_host[0])
+            xs.append(time.perf_counter() - t0)
+        xc_info = {'functional': args.xc, 'ms': float(np.median(xs)) * 1e3, 'first_call_ms': first_s * 1e3,
+                   'nelec': ne, 'exc': exc, 'timed': 'host API, wall clock, includes H2D of dm and D2H of vmat'}
+        mydf._aoR4 = None
+
     # end to end through the plugin's host API
     if args.no_e2e:
         vj, vk = mydf.get_jk(dm_host[0], exxdiv=None)
@@ -444,6 +497,8 @@ def run_b200(args):
                             'max_planes': planes, 'int8_ops_per_rank': ops, 'ms': stages_ms['wgemm_ms'],
                             'achieved_pops': ops / (stages_ms['wgemm_ms'] * 1e-3) / 1e15,
                             'fp64_equivalent_tflops': fm['coulomb_gemm'] / world / (stages_ms['wgemm_ms'] * 1e-3) / 1e12}
+    if xc_info is not None:
+        line['xc'] = xc_info
     if world == 1 and not args.no_cpu_baseline:
         v, b, j, per, desc, ncores = cpu_baseline_run(cell, int(mydf.n_ip))
         line['cpu_baseline'] = {'value': v, 'unit': 's', 'cores': ncores, 'kind': 'port', 'sample': desc,
