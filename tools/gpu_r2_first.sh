@@ -45,3 +45,14 @@ try:
 except Exception as e:
     print('crt: no line', e)
 PY
+# J/K + exchange-correlation per SCF iteration for the RKS-PBE configuration (BASELINE configs[1])
+timeout 600 python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e --xc pbe \
+    > gpurun_out/bench_xc.json 2> gpurun_out/bench_xc.err; echo "bench xc rc=$?"
+python - <<PY
+import json
+try:
+    d = json.loads(open('gpurun_out/bench_xc.json').read().strip().splitlines()[-1])
+    print('xc', d.get('xc'), 'jk_ms', d.get('jk_ms'))
+except Exception as e:
+    print('xc: no line', e)
+PY
