@@ -468,6 +468,11 @@ class ISDF:
         res = out.cpu().numpy()
         return float(res[-2]), float(res[-1]), res[:nao * nao].reshape(nao, nao).copy()
 
+    def numint(self):
+        """Object with the ``nr_rks`` call signature the reference's RKS uses on ``mf._numint``
+        (pyscf/pbc/dft/rks.py:88-89), backed by :meth:`nr_rks`."""
+        return ISDFNumInt(self)
+
     def get_j(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None):
         return self.get_jk(dm, hermi, kpts, kpts_band, True, False, omega)[0]
 
@@ -493,3 +498,28 @@ class ISDF:
         self.aoR_ip = torch.from_numpy(z['aoR_ip']).to(h.torch_device)
         self._jk_ws = None
         return self
+
+
+class ISDFNumInt:
+    """Stand-in for ``pyscf.pbc.dft.numint.NumInt`` on the exchange-correlation call of the SCF loop:
+    ``ni.nr_rks(cell, grids, xc_code, dms, relativity, hermi, kpt, kpts_band, max_memory=...)``
+    (pyscf/pbc/dft/rks.py:88-89; signature pyscf/pbc/dft/numint.py:283-285) -> ``(nelec, excsum, vmat)``,
+    scalars and one matrix for a single density matrix, arrays over the set otherwise (numint.py:370-378).
+    With PySCF present, subclass its NumInt and override ``nr_rks`` with this method so that the
+    functional parsing helpers (``libxc.is_hybrid_xc`` ...) stay the reference's own."""
+
+    def __init__(self, mydf):
+        self.mydf = mydf
+
+    def nr_rks(self, cell, grids, xc_code, dms, relativity=0, hermi=1, kpt=None, kpts_band=None,
+               max_memory=2000, verbose=None):
+        if kpts_band is not None:
+            raise NotImplementedError('kpts_band')
+        if hermi != 1:
+            raise NotImplementedError('nr_rks: hermitian density matrices only (hermi=1)')
+        dms = np.asarray(dms, dtype=np.float64)
+        single = dms.ndim == 2
+        out = [self.mydf.nr_rks(xc_code, dm, kpts=kpt) for dm in (dms[None] if single else dms)]
+        if single:
+            return out[0]
+        return (np.array([o[0] for o in out]), np.array([o[1] for o in out]), np.stack([o[2] for o in out]))

@@ -45,6 +45,12 @@ def _run_rank(comm, out=None, fit='implicit'):
     vne = mydf.get_nuc()
     vnl = mydf.get_pp_nl()                     # projector part: every rank sums its own range of G vectors
     xc_out = {name: mydf.nr_rks(name, dm) for name in ('pbe', 'blyp')}      # GGA exchange-correlation on the rank's slab
+    # the NumInt-shaped adapter: positional call of pyscf/pbc/dft/rks.py:88-89, one matrix and a set of two
+    ni = mydf.numint()
+    one = ni.nr_rks(cell, None, 'pbe', dm, 0, 1, np.zeros(3), None, max_memory=100)
+    two = ni.nr_rks(cell, None, 'pbe', np.stack([dm, dm]), 0, 1, None, None)
+    assert one[0] == xc_out['pbe'][0] and np.array_equal(one[2], xc_out['pbe'][2])
+    assert two[0].shape == (2,) and two[2].shape == (2,) + dm.shape and np.array_equal(two[2][1], one[2])
     res = dict(xc=xc_out, ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(), vpp=vpp, vne=vne, vnl=vnl,
                p0=int(mydf._part.ip_off[comm.rank]),
                vj=vj.numpy()[0].copy(), vk=vk.numpy()[0].copy(), slab=mydf._slab,
