@@ -107,3 +107,15 @@ def test_rks_lda_energies_of_diamond_reproduce_the_reference():
                                 lambda dm: oracle.fftdf_get_j(ao4[0], dm, a, mesh),
                                 lambda dm: xc.nr_rks(ao4, w, 'lda,vwn', dm))
         assert abs(e - gold) < 1e-8, (cell.natm, e - gold)
+
+
+def test_product_overlap_kinetic_match_the_oracle():
+    """pyscf_isdf_b200/int1e.py (species-grouped, sphere of G vectors) against oracle/int1e.py (per shell,
+    cube of G vectors): orthogonal and fcc cells, s/p/d shells, atoms with and without pseudopotential."""
+    from pyscf_isdf_b200 import int1e as pint
+    from util import diamond_c8, he_c_cell
+    for cell in (he_c_cell(), diamond_c8([12] * 3, basis='gth-dzvp', jitter=0.1), diamond_primitive([9] * 3)):
+        S0, T0 = int1e.overlap_kinetic(cell.lattice_vectors(), cell._atm, cell._bas, cell._env)
+        S, T = pint.overlap_kinetic(cell)
+        assert abs(S - S0).max() < 1e-13 and abs(T - T0).max() < 1e-13
+        assert np.linalg.eigvalsh(S).min() > 0
