@@ -3,10 +3,10 @@
 Roothaan loop: with n_ip >= the rank of the pair space (21) ISDF is exact, so the energies must equal the
 reference's fixed numbers (test_hf.py:94-95, :129-132).  Tolerance 1e-7 Ha (the reference asserts 7 places;
 the oracle chain itself sits 1.1e-8 from them, tests/test_scf_cpu.py); overlap and kinetic matrices come
-from the oracle (in the reference they come from libcint, outside the ISDF path)."""
+from pyscf_isdf_b200/int1e.py (in the reference they come from libcint, outside the ISDF path)."""
 import numpy as np
 import pytest
-from oracle import int1e
+from pyscf_isdf_b200 import int1e
 from pyscf_isdf_b200.isdf import ISDF
 from scf_harness import rhf_gamma
 from test_scf_cpu import E_EXX_EWALD, E_EXX_NONE, he2_cell
@@ -16,7 +16,7 @@ pytestmark = pytest.mark.gpu
 
 def test_rhf_energies_with_isdf_in_the_exact_limit():
     cell = he2_cell()
-    S, T = int1e.overlap_kinetic(cell.lattice_vectors(), cell._atm, cell._bas, cell._env)
+    S, T = int1e.overlap_kinetic(cell)
     mydf = ISDF(cell, n_ip=60).build()
     assert mydf.n_ip <= 22
     hcore = T + mydf.get_nuc()
@@ -34,8 +34,8 @@ def _rks_diamond(xc_on_device):
     from scf_harness import rks_gamma
     from test_scf_cpu import E_LDA_C8_CUBIC, diamond_cubic, oracle_rks_pieces
     cell = diamond_cubic([17] * 3)
-    S, _, ao4 = oracle_rks_pieces(cell)
-    T = int1e.overlap_kinetic(cell.lattice_vectors(), cell._atm, cell._bas, cell._env)[1]
+    ao4 = oracle_rks_pieces(cell)[2]
+    S, T = int1e.overlap_kinetic(cell)
     mydf = ISDF(cell, c=10, exact_j=True).build()
     hcore = T + mydf.get_pp()
     w = cell.vol / ao4.shape[1]
