@@ -194,11 +194,34 @@ def species_ft_shells(cell, ia, q, qq):
     return np.concatenate(rows)
 
 
+def _pair_classes(mesh, g0, g1):
+    """For the flat reciprocal-grid indices [g0, g1): which are representatives of a +-G pair (the lower flat
+    index of the two) and which stand alone (G = 0, or a Nyquist component -n/2 on an even axis, whose
+    negative is not on the grid).  The partner of a representative may lie outside [g0, g1)."""
+    nx, ny, nz = (int(m) for m in mesh)
+    flat = np.arange(g0, g1)
+    ix, rem = np.divmod(flat, ny * nz)
+    iy, iz = np.divmod(rem, nz)
+    neg = (((-ix) % nx) * ny + ((-iy) % ny)) * nz + ((-iz) % nz)
+    single = neg == flat                                         # G = 0 and pure-Nyquist corners
+    for i, n in ((ix, nx), (iy, ny), (iz, nz)):
+        if n % 2 == 0:
+            single |= i == n // 2
+    # a pair in which exactly one member has a Nyquist component cannot occur: negation keeps index n/2
+    rep = (~single) & (flat < neg)
+    return rep, single
+
+
 def pp_nl_overlaps(cell, g0=0, g1=None, mesh=None, max_bytes=1 << 29):
     """Sum over the reciprocal vectors [g0, g1) of  conj(SI_a) P_a(G) x ft_ao(G)  for every projector
     of every atom: complex [nproj_total, nao] (the reference's SPG_lm_aoGs, fft.py:129-130, for all
     atoms at once and without the 1/sqrt(vol)).  The sum over G is a plain sum, so ranks can take
-    disjoint ranges and add their results."""
+    disjoint ranges and add their results.
+
+    At the Gamma point the term of -G is (-1)^l times the conjugate of the term of G (real AOs, real
+    projectors of parity l), so a +-G pair contributes 2 Re (even l) or 2i Im (odd l) of one term: only one
+    member of each pair is evaluated, with real matrix products (a quarter of the arithmetic of the
+    complex product over all G).  Vectors without a partner on the grid are summed as they are."""
     mesh = cell.mesh if mesh is None else mesh
     Gv = cell.get_Gv(mesh)
     g1 = len(Gv) if g1 is None else g1
@@ -210,17 +233,34 @@ def pp_nl_overlaps(cell, g0=0, g1=None, mesh=None, max_bytes=1 << 29):
         first.setdefault(cell.atom_symbol(ia), ia)
     nproj = [sum(nl * (2 * l + 1) for l, (_, nl, _) in enumerate(pp['nonlocal_'])) if pp is not None else 0 for pp in pps]
     Z = np.zeros((sum(nproj), nao), dtype=np.complex128)
-    step = max(256, int(max_bytes // (16 * (nao + sum(nproj) + 1))))
-    for b0 in range(g0, g1, step):
-        q = Gv[b0:min(b0 + step, g1)]
+    if Z.shape[0] == 0 or g1 <= g0:
+        return Z
+    odd = np.concatenate([np.concatenate([np.full(nl * (2 * l + 1), l % 2 == 1) for l, (_, nl, _) in enumerate(pp['nonlocal_'])] or [np.zeros(0, bool)])
+                          for pp in pps if pp is not None and any(nl for _, nl, _ in pp['nonlocal_'])])
+    rep, single = _pair_classes(mesh, g0, g1)
+
+    def tables(q):
         qq = np.einsum('gx,gx->g', q, q)
         SI = np.exp(-1j * np.dot(coords, q.T))                         # [natm, n]
         ft = {s: species_ft_shells(cell, ia, q, qq) for s, ia in first.items()}
         pr = {s: species_projectors(pps[ia], q, qq) for s, ia in first.items() if nproj[ia]}
         aoG = np.concatenate([ft[cell.atom_symbol(ia)] * SI[ia] for ia in range(cell.natm)])       # [nao, n]
-        spg = [pr[cell.atom_symbol(ia)] * SI[ia].conj() for ia in range(cell.natm) if nproj[ia]]
-        if spg:
-            Z += np.concatenate(spg).dot(aoG.T)
+        spg = np.concatenate([pr[cell.atom_symbol(ia)] * SI[ia].conj() for ia in range(cell.natm) if nproj[ia]])
+        return spg, aoG
+
+    step = max(256, int(max_bytes // (16 * (nao + sum(nproj) + 1))))
+    idx = g0 + np.nonzero(single)[0]
+    for b0 in range(0, len(idx), step):                                # unpaired vectors: complex product
+        spg, aoG = tables(Gv[idx[b0:b0 + step]])
+        Z += spg.dot(aoG.T)
+    idx = g0 + np.nonzero(rep)[0]
+    Zr = np.zeros(Z.shape)
+    for b0 in range(0, len(idx), step):                                # one of each pair: real products
+        spg, aoG = tables(Gv[idx[b0:b0 + step]])
+        A = np.where(odd[:, None], np.concatenate([spg.imag, spg.real], axis=1),
+                     np.concatenate([spg.real, -spg.imag], axis=1))   # Im t (odd l) / Re t (even l)
+        Zr += A.dot(np.concatenate([aoG.real, aoG.imag], axis=1).T)
+    Z += 2 * np.where(odd[:, None], 1j * Zr, Zr)
     return Z
 
 
