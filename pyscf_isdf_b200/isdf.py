@@ -418,30 +418,39 @@ class ISDF:
         return vpp
 
     # -- exchange-correlation on the same grid ("next" row 1 of SURVEY 8f) -----------------------
-    def _ao_deriv1_on_grid(self):
-        """AO values and gradients of this rank's grid slab, [4, nao, ld] on the device, evaluated on
-        first use and kept (4 x the AO matrix; drop with ``self._aoR4 = None``)."""
-        if self._aoR4 is not None:
-            return self._aoR4
+    XC_CACHE_BYTES = 48 << 30       # AO values + gradients are kept between SCF iterations up to this size
+
+    def _ao_deriv1(self, c0, c1):
+        """AO values and gradients of the grid points [c0, c1): a new device tensor [4, nao, ld]."""
         h = self.handle
         cell = self.cell
-        ng = int(np.prod(self.mesh))
-        g0, g1 = self._slab if self._slab is not None else (0, ng)
-        ld = _lib.pad8(g1 - g0)
+        ld = _lib.pad8(c1 - c0)
         nao = cell.nao_nr()
         rcut, Ls = cell.ao_eval_params()
         phi4 = h.zeros((4, nao, ld))
         h.eval_ao_deriv1(cell._atm, cell._bas, cell._env,
                          np.ascontiguousarray(cell.lattice_vectors(), dtype=np.float64),
-                         np.asarray(cell.mesh, dtype=np.int32), Ls, rcut, g0, g1, phi4, ld, nao * ld)
-        self._aoR4 = phi4
+                         np.asarray(cell.mesh, dtype=np.int32), Ls, rcut, c0, c1, phi4, ld, nao * ld)
         return phi4
 
-    def nr_rks(self, xc_code, dm, kpts=None):
+    def _ao_deriv1_on_grid(self):
+        """AO values and gradients of this rank's whole grid slab, evaluated on first use and kept
+        (4 x the AO matrix; drop with ``self._aoR4 = None``)."""
+        if self._aoR4 is None:
+            ng = int(np.prod(self.mesh))
+            g0, g1 = self._slab if self._slab is not None else (0, ng)
+            self._aoR4 = self._ao_deriv1(g0, g1)
+        return self._aoR4
+
+    def nr_rks(self, xc_code, dm, kpts=None, max_bytes=None):
         """(nelec, exc, vmat) of a closed-shell density matrix at the Gamma point: NumInt.nr_rks of the
         reference (pyscf/pbc/dft/numint.py:283-381) for the functionals 'lda,', 'lda,vwn', 'blyp' and 'pbe', on the
         device: density and gradient from the AO values, the functional, and the potential matrix.  With a
-        sharded grid every rank works on its slab and the three results are summed over ranks."""
+        sharded grid every rank works on its slab and the three results are summed over ranks.
+
+        The AO values and gradients of the slab (32 nao ngl bytes) are kept between calls when they fit in
+        ``max_bytes`` (default ``XC_CACHE_BYTES``); a larger slab is walked in chunks of that size whose AO
+        gradients are re-evaluated on every call, the way the reference's ``block_loop`` does (numint.py:354-356)."""
         self._check_gamma(kpts)
         h = self.handle
         dm = np.asarray(dm, dtype=np.float64)
@@ -450,22 +459,29 @@ class ISDF:
         if self.comm is not None and self.comm.size > 1 and self._slab is None:
             raise RuntimeError('nr_rks on a sharded grid needs build() first (it assigns the grid slabs)')
         code = h.xc_code(xc_code)
-        phi4 = self._ao_deriv1_on_grid()
-        nao, ld = phi4.shape[1], phi4.shape[2]
+        nao = self.cell.nao_nr()
         ng = int(np.prod(self.mesh))
         g0, g1 = self._slab if self._slab is not None else (0, ng)
-        ngl = g1 - g0
         weight = self.cell.vol / ng
+        max_bytes = self.XC_CACHE_BYTES if max_bytes is None else max_bytes
+        chunk = max(56, int(max_bytes // (32 * nao)) // 56 * 56)      # whole 56-point blocks of the AO kernel
         d_dm = h.from_host(np.ascontiguousarray(dm))
-        rho4 = h.zeros((4, ld))
-        wv4 = h.zeros((4, ld))
-        out = h.zeros((nao * nao + 2,))              # vmat and the two sums in one buffer: one all-reduce
-        ws = h.xc_density(phi4, ld, nao * ld, nao, ngl, d_dm, rho4, ld)
-        h.xc_potential(code, rho4, ld, ngl, weight, wv4, out[nao * nao:], ws)
-        h.xc_matrix(phi4, ld, nao * ld, nao, ngl, wv4, ld, out[:nao * nao], ws)
+        total = h.zeros((nao * nao + 2,))            # vmat and the two sums in one buffer: one all-reduce
+        ws = None
+        for c0 in range(g0, g1, chunk):
+            c1 = min(c0 + chunk, g1)
+            phi4 = self._ao_deriv1_on_grid() if chunk >= g1 - g0 else self._ao_deriv1(c0, c1)
+            ld = phi4.shape[2]
+            rho4 = h.zeros((4, ld))
+            wv4 = h.zeros((4, ld))
+            out = h.zeros((nao * nao + 2,))
+            ws = h.xc_density(phi4, ld, nao * ld, nao, c1 - c0, d_dm, rho4, ld, ws if c1 - c0 == chunk else None)
+            h.xc_potential(code, rho4, ld, c1 - c0, weight, wv4, out[nao * nao:], ws)
+            h.xc_matrix(phi4, ld, nao * ld, nao, c1 - c0, wv4, ld, out[:nao * nao], ws)
+            total += out
         if self.comm is not None and self.comm.size > 1:
-            self.comm.all_reduce_sum(out)
-        res = out.cpu().numpy()
+            self.comm.all_reduce_sum(total)
+        res = total.cpu().numpy()
         return float(res[-2]), float(res[-1]), res[:nao * nao].reshape(nao, nao).copy()
 
     def numint(self):

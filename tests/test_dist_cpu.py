@@ -45,6 +45,10 @@ def _run_rank(comm, out=None, fit='implicit'):
     vne = mydf.get_nuc()
     vnl = mydf.get_pp_nl()                     # projector part: every rank sums its own range of G vectors
     xc_out = {name: mydf.nr_rks(name, dm) for name in ('pbe', 'blyp')}      # GGA exchange-correlation on the rank's slab
+    # a memory budget below the slab size walks the slab in chunks of whole 56-point blocks, same result
+    chunked = mydf.nr_rks('pbe', dm, max_bytes=32 * cell.nao * 200)
+    assert abs(chunked[0] - xc_out['pbe'][0]) < 1e-12 * abs(chunked[0]) and abs(chunked[1] - xc_out['pbe'][1]) < 1e-12 * abs(chunked[1])
+    assert abs(chunked[2] - xc_out['pbe'][2]).max() < 1e-12 * abs(chunked[2]).max()
     # the NumInt-shaped adapter: positional call of pyscf/pbc/dft/rks.py:88-89, one matrix and a set of two
     ni = mydf.numint()
     one = ni.nr_rks(cell, None, 'pbe', dm, 0, 1, np.zeros(3), None, max_memory=100)

@@ -64,6 +64,10 @@ def test_nr_rks_matches_oracle(name):
     assert abs(exc - exc0) < 1e-10 * abs(exc0)
     assert abs(vmat - vmat0).max() < 1e-10 * abs(vmat0).max()
     assert abs(vmat - vmat.T).max() == 0.0
+    if name == 'pbe':       # a small memory budget walks the grid in chunks and re-evaluates the AO gradients
+        ne2, exc2, vmat2 = ISDF(cell, c=4).nr_rks(name, dm, max_bytes=32 * cell.nao * 500)
+        assert abs(ne2 - ne0) < 1e-10 * abs(ne0) and abs(exc2 - exc0) < 1e-10 * abs(exc0)
+        assert abs(vmat2 - vmat0).max() < 1e-10 * abs(vmat0).max()
 
 
 def test_nr_rks_errors():
