@@ -60,3 +60,55 @@ def test_whole_grid_with_image_screening(lib, which):
                        ctypes.c_int(len(Lc)), ctypes.c_longlong(len(coords)), p(coords), p(out))
     assert abs(ref[1:]).max() > 0.1
     assert abs(out - ref).max() < 1e-12
+
+
+KSRC = os.path.join(HERE, 'emul', 'ao_kernel_emul.cpp')
+KOUT = os.path.join(HERE, 'emul', '_build', 'libao_kernel_emul.so')
+KDEPS = [KSRC] + [os.path.join(HERE, '..', 'pyscf_isdf_b200', 'csrc', f) for f in ('ao_core.cuh', 'eval_ao_deriv1_kernel.cuh')]
+
+
+@pytest.fixture(scope='module')
+def klib():
+    os.makedirs(os.path.dirname(KOUT), exist_ok=True)
+    if not os.path.exists(KOUT) or any(os.path.getmtime(d) > os.path.getmtime(KOUT) for d in KDEPS):
+        subprocess.check_call(['g++', '-std=c++20', '-O1', '-fPIC', '-shared', '-pthread', '-Wno-unknown-pragmas',
+                               '-o', KOUT, KSRC])
+    return ctypes.CDLL(KOUT)
+
+
+def _run_kernel(klib, cell, g0, g1, ny, fill=7.0):
+    rcut, Ls = cell.ao_eval_params()
+    nao = cell.nao
+    ld = (g1 - g0 + 7) // 8 * 8 + 8
+    out = np.full((4, nao, ld), fill)
+    arrs = [np.ascontiguousarray(cell._atm, dtype=np.int32), np.ascontiguousarray(cell._bas, dtype=np.int32),
+            np.ascontiguousarray(cell._env, dtype=np.float64), np.ascontiguousarray(cell.lattice_vectors(), dtype=np.float64),
+            np.ascontiguousarray(cell.mesh, dtype=np.int32), np.ascontiguousarray(Ls, dtype=np.float64),
+            np.ascontiguousarray(rcut, dtype=np.float64)]
+    p = lambda a: a.ctypes.data_as(ctypes.c_void_p)          # noqa: E731
+    atm, bas, env, a, mesh, Lc, rc = arrs
+    rcode = klib.emul_eval_ao_deriv1(p(atm), ctypes.c_int(len(atm)), p(bas), ctypes.c_int(len(bas)), p(env),
+                                     ctypes.c_int(len(env)), p(a), p(mesh), p(Lc), ctypes.c_int(len(Lc)), p(rc),
+                                     ctypes.c_longlong(g0), ctypes.c_longlong(g1), p(out), ctypes.c_longlong(ld),
+                                     ctypes.c_longlong(nao * ld), ctypes.c_int(ny))
+    assert rcode == 0
+    return out
+
+
+def test_the_kernel_itself_block_by_block(klib):
+    """eval_ao_deriv1_kernel compiled with g++ and run CTA by CTA (64 threads, barriers, emulated warp
+    shuffles / ballots): whole grid, a slab that starts and ends inside 56-point blocks, atoms split over
+    grid.y -- values and gradients equal the oracle, nothing outside [g0, g1) is written."""
+    import oracle
+    from util import diamond_c8, he_c_cell
+    for cell, ny in ((he_c_cell(), 1), (diamond_c8([7, 8, 9], basis='gth-dzvp', jitter=0.15), 4)):
+        rcut, Ls = cell.ao_eval_params()
+        ref = oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, deriv=1).transpose(0, 2, 1)
+        ng = ref.shape[2]
+        out = _run_kernel(klib, cell, 0, ng, ny)
+        assert abs(out[:, :, :ng] - ref).max() < 1e-12
+        assert (out[:, :, ng:] == 7.0).all()
+        g0, g1 = 100, 100 + 333
+        part = _run_kernel(klib, cell, g0, g1, 1)
+        assert abs(part[:, :, :g1 - g0] - ref[:, :, g0:g1]).max() < 1e-12
+        assert (part[:, :, g1 - g0:] == 7.0).all()
