@@ -681,12 +681,14 @@ int kernel_variant()
     return v;
 }
 
-// ISDF_SYRK_CRT=<moduli> (8..16, opt-in): the residue form of the product (crt_core.cuh); 0 / unset: digit planes.
+// The residue form of the product (crt_core.cuh) with 16 moduli is the default: on the C64 workload it gives the
+// same W as the digit-plane form to 2e-12 (J/K to 2e-13) in 462 ms instead of 737 ms (profiles/r01_optin_forms.md).
+// ISDF_SYRK_CRT=<moduli> (8..16) changes the ceiling, ISDF_SYRK_CRT=0 selects the digit planes.
 // Needs the 256x256 kernel (variant 2).
 int crt_moduli()
 {
     const char* e = getenv("ISDF_SYRK_CRT");
-    int nm = e ? atoi(e) : 0;
+    int nm = e ? atoi(e) : 16;
     if (nm <= 0 || kernel_variant() != 2) return 0;
     return std::max(8, std::min(nm, (int)isdf_crt::NM_MAX));
 }

@@ -2,16 +2,14 @@
 against numpy.fft + coulG on prime meshes, 1e-10 relative like the default path.
 
 The line-FFT routines are already checked on the CPU by tests/test_fft_emul_cpu.py; this file checks
-the kernels that call them.  Written after the last GPU session of round 1: skipped unless
-ISDF_TEST_EXPERIMENTAL=1 until it has been run on a B200 (tools/gpu_r2_first.sh does that)."""
+the kernels that call them.  First run on a B200 at the end of round 1: all passed
+(profiles/r01_optin_forms.md); the path stays opt-in (it gains 5 % of the FFT stage on C64)."""
 import os
 import numpy as np
 import pytest
 import test_stages_gpu as stages
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get('ISDF_TEST_EXPERIMENTAL') != '1',
-                                 reason='opt-in kernel forms not yet validated on a B200 (set ISDF_TEST_EXPERIMENTAL=1)')]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.fixture

@@ -2,9 +2,10 @@
 cluster with st.async pushes, ISDF_PANEL_CLUSTER = 0 / 1 / 2) give pivots, residuals and factor
 bit-identical to the unblocked FMA-chain oracle, on generic data and on a symmetric cell with exact ties.
 
-Forms 1 and 2 were written after the last GPU session of round 1: they are opt-in in the library
-(the default is form 0) and this file is skipped unless ISDF_TEST_EXPERIMENTAL=1, until they have
-been run and timed on a B200 (tools/gpu_r2_first.sh does that)."""
+Forms 1 and 2 are opt-in in the library (the default is form 0).  First run on a B200 at the end of
+round 1: both tests passed and form 2 saves 34 ms of the C64 selection (profiles/r01_optin_forms.md).  The
+file stays behind ISDF_TEST_EXPERIMENTAL=1 until the cluster protocols have more than one run behind them
+(multi-rank, compute-sanitizer): tools/gpu_r2_first.sh."""
 import os
 import numpy as np
 import pytest

@@ -48,7 +48,5 @@ def test_rks_lda_energy_of_diamond_with_device_hcore_and_j():
     _rks_diamond(False)
 
 
-@pytest.mark.skipif(__import__('os').environ.get('ISDF_TEST_EXPERIMENTAL') != '1',
-                    reason='exchange-correlation kernels not yet validated on a B200 (set ISDF_TEST_EXPERIMENTAL=1)')
 def test_rks_lda_energy_of_diamond_all_on_device():
     _rks_diamond(True)

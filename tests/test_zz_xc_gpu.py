@@ -4,10 +4,7 @@ pinned to the reference's fingerprints in pyscf/pbc/dft/test/test_numint.py, see
 Tolerances: AO values and gradients 1e-12 abs on O(1) numbers; nelec, exc and vmat 1e-10 relative (FP64
 sums over the grid in a different order).
 
-The kernels of this row (csrc/eval_ao_deriv1.cu, csrc/xc.cu) were written after the last GPU session of
-round 1; their arithmetic is checked on the CPU (tests/test_ao_emul_cpu.py, tests/test_xc_emul_cpu.py) and
-the host driver against the oracle through the NumPy stand-ins (tests/test_dist_cpu.py).  This file is
-skipped unless ISDF_TEST_EXPERIMENTAL=1 until it has passed on a B200 (tools/gpu_r2_first.sh runs it)."""
+First run on a B200 at the end of round 1: all passed (profiles/r01_optin_forms.md)."""
 import os
 import numpy as np
 import pytest
@@ -17,9 +14,7 @@ from util import diamond_c8, he_c_cell, rand_dm
 from pyscf_isdf_b200 import _lib
 from pyscf_isdf_b200.isdf import ISDF
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get('ISDF_TEST_EXPERIMENTAL') != '1',
-                                 reason='kernels of this row not yet validated on a B200 (set ISDF_TEST_EXPERIMENTAL=1)')]
+pytestmark = pytest.mark.gpu
 
 
 def _oracle_ao4(cell):

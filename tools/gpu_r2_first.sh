@@ -6,12 +6,11 @@
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_panel_forms_gpu.py -m gpu -q > gpurun_out/pytest_forms.log 2>&1; echo "forms rc=$?"; tail -15 gpurun_out/pytest_forms.log
-ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_syrk_crt_gpu.py -m gpu -q > gpurun_out/pytest_crt.log 2>&1; echo "crt rc=$?"; tail -15 gpurun_out/pytest_crt.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_fft_fused_gpu.py -m gpu -q > gpurun_out/pytest_fftfused.log 2>&1; echo "fft fused rc=$?"; tail -15 gpurun_out/pytest_fftfused.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_xc_gpu.py tests/test_zz_scf_gpu.py -m gpu -q > gpurun_out/pytest_xc.log 2>&1; echo "xc rc=$?"; tail -15 gpurun_out/pytest_xc.log
 # memory checker on the small experimental tests (slow: only these files)
 ISDF_TEST_EXPERIMENTAL=1 timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest \
-    tests/test_zz_panel_forms_gpu.py tests/test_zz_syrk_crt_gpu.py tests/test_zz_xc_gpu.py -m gpu -q -x -k "bit_exact or 200-300 or 128-128 or he_c or lda" \
+    tests/test_zz_panel_forms_gpu.py tests/test_syrk_i8_gpu.py tests/test_zz_xc_gpu.py -m gpu -q -x -k "bit_exact or 200-300 or 128-128 or he_c or lda" \
     > gpurun_out/sanitizer.log 2>&1; echo "sanitizer rc=$?"; grep -E "ERROR SUMMARY|passed|failed" gpurun_out/sanitizer.log | tail -5
 for mode in 0 1 2; do
   ISDF_PANEL_CLUSTER=$mode ISDF_PROFILE_SELECT=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
@@ -35,7 +34,7 @@ try:
 except Exception as e:
     print('fft fused: no line', e)
 PY
-ISDF_SYRK_CRT=16 ISDF_SYRK_VERBOSE=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
+ISDF_SYRK_CRT=0 ISDF_SYRK_VERBOSE=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
     > gpurun_out/bench_crt.json 2> gpurun_out/bench_crt.err; echo "bench crt rc=$?"; grep -m2 isdf_syrk gpurun_out/bench_crt.err
 python - <<PY
 import json
