@@ -493,8 +493,12 @@ def run_b200(args):
     if args.wgemm.startswith('i8') and stages_ms.get('wgemm_ms'):
         planes = int(args.wgemm.split(':')[1]) if ':' in args.wgemm else 8
         ops = float(getattr(h, 'syrk_i8_ops', 0.0))         # int8 ops issued by this rank's last W product
-        line['wgemm_i8'] = {'kernel': 'syrk_i8_kernel (tcgen05 kind::i8, TMEM accumulators, bulk-copy ring, cluster multicast)',
-                            'max_planes': planes, 'int8_ops_per_rank': ops, 'ms': stages_ms['wgemm_ms'],
+        crt = os.environ.get('ISDF_SYRK_CRT')
+        form = ('digit planes: S(S+1)/2 int8 products per K chunk' if crt is not None and int(crt) <= 0 else
+                'residues modulo %d coprime moduli <= 256 (one int8 product per modulus, Garner reconstruction)'
+                % (16 if crt is None else max(8, min(16, int(crt)))))
+        line['wgemm_i8'] = {'kernel': 'syrk_i8_kernel2 (tcgen05 kind::i8, TMEM accumulators, bulk-copy ring, cluster multicast)',
+                            'form': form, 'max_planes': planes, 'int8_ops_per_rank': ops, 'ms': stages_ms['wgemm_ms'],
                             'achieved_pops': ops / (stages_ms['wgemm_ms'] * 1e-3) / 1e15,
                             'fp64_equivalent_tflops': fm['coulomb_gemm'] / world / (stages_ms['wgemm_ms'] * 1e-3) / 1e12}
     if xc_info is not None:
