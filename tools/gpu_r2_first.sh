@@ -1,8 +1,10 @@
 #!/bin/bash
-# First GPU call of round 2: (1) the regular GPU suite incl. the hcore tests written at the end of
-# round 1, (2) the opt-in pivot-kernel forms (ISDF_PANEL_CLUSTER=1/2) for bit-exactness, (3) C64 bench
-# lines for form 0 / 1 / 2 with the selection breakdown, (4) the fused Rader FFT (ISDF_FFT_FUSED=1) and (5) the CRT form of the int8
-# metric product (ISDF_SYRK_CRT=16): tests and a C64 bench line each, (6) the GGA exchange-correlation row (tests/test_zz_xc_gpu.py) -- so the defaults can be switched on evidence.
+# First GPU call of round 2.  State at the end of round 1 (profiles/r01_optin_forms.md): the residue form of the
+# int8 metric product is the default (first runs passed, C64 wgemm 462 vs 737 ms); the cluster pivot kernels
+# (ISDF_PANEL_CLUSTER=1/2) and the fused FFT (ISDF_FFT_FUSED=1) passed their first tests and stay opt-in.
+# This call: (1) the whole GPU suite under the new default, (2) the cluster pivot forms again plus
+# compute-sanitizer over the late kernels, (3) C64 bench lines per pivot form with the selection breakdown,
+# (4) fused FFT line, (5) the digit-plane product for comparison (ISDF_SYRK_CRT=0), (6) nr_rks('pbe') timing.
 mkdir -p gpurun_out
 timeout 1200 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_panel_forms_gpu.py -m gpu -q > gpurun_out/pytest_forms.log 2>&1; echo "forms rc=$?"; tail -15 gpurun_out/pytest_forms.log
