@@ -693,6 +693,14 @@ int crt_moduli()
     return std::max(8, std::min(nm, (int)isdf_crt::NM_MAX));
 }
 
+// ISDF_SYRK_OVERLAP=1 (opt-in, residue form only): the element-wise kernels of chunk c+1 / c-1 run on a second
+// stream beside the tensor-core products of chunk c (double-buffered residue planes and residue output).
+bool overlap_requested()
+{
+    const char* e = getenv("ISDF_SYRK_OVERLAP");
+    return e && atoi(e) > 0 && crt_moduli() > 0;
+}
+
 int rows_padded(int n, int cl)
 {
     if (kernel_variant() == 2) return (int)align_up((size_t)n, (size_t)CT);
@@ -700,8 +708,9 @@ int rows_padded(int n, int cl)
 }
 
 template <bool CRT>
-int launch_syrk2(isdf_handle* h, const SyrkArgs& a, int& nclusters)
+int launch_syrk2(isdf_handle* h, const SyrkArgs& a, int& nclusters, cudaStream_t stream = nullptr)
 {
+    if (!stream) stream = h->stream;
     if (nclusters == 0) {
         CUDA_TRY(cudaFuncSetAttribute(syrk_i8_kernel2<CRT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
         int fit = h->num_sms / 4;
@@ -715,7 +724,7 @@ int launch_syrk2(isdf_handle* h, const SyrkArgs& a, int& nclusters)
         else (void)cudaGetLastError();
         nclusters = std::max(1, std::min(fit, a.ntiles));
     }
-    syrk_i8_kernel2<CRT><<<nclusters * 4, NTHREADS2, SMEM2, h->stream>>>(a);
+    syrk_i8_kernel2<CRT><<<nclusters * 4, NTHREADS2, SMEM2, stream>>>(a);
     return ISDF_OK;
 }
 
@@ -753,8 +762,9 @@ extern "C" size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices)
     const int cl = cluster_size();
     const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
     const int nm = crt_moduli();
-    const size_t crt_extra = nm ? align_up((size_t)nm * (size_t)n * align_up((size_t)n, 16), 1024) : 0;    // residues of the products
-    return crt_extra + align_up((size_t)std::max(nslices, nm) * (size_t)rows_padded(n, cl) * ((c.kc_full / BKB | 1) * BKB), 1024) +
+    const size_t nbuf = overlap_requested() ? 2 : 1;
+    const size_t crt_extra = nm ? nbuf * align_up((size_t)nm * (size_t)n * align_up((size_t)n, 16), 1024) : 0;    // residues of the products
+    return crt_extra + nbuf * align_up((size_t)std::max(nslices, nm) * (size_t)rows_padded(n, cl) * ((c.kc_full / BKB | 1) * BKB), 1024) +
            align_up((size_t)(c.nchunks + 1) * n * sizeof(double), 256) + align_up((size_t)c.nchunks * sizeof(double), 256) +
            align_up((size_t)tr * tc * sizeof(int2), 256) + 2048;
 }
@@ -779,12 +789,17 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     const long long plane_stride = rb_stride * (nrows_pad / TM);
     char* base = (char*)align_up((size_t)ws, 1024);
     const int nm_max = crt_moduli();
+    const bool overlap = overlap_requested();
     int8_t* planes = (int8_t*)base;
     base += align_up((size_t)std::max(nslices, nm_max) * plane_stride, 1024);
+    int8_t* planes2 = planes;                              // second set of residue planes (overlap form)
+    if (overlap) { planes2 = (int8_t*)base; base += align_up((size_t)std::max(nslices, nm_max) * plane_stride, 1024); }
     const long long ldr = (long long)align_up((size_t)n, 16);
     const long long res_stride = (long long)n * ldr;
     int8_t* resid = (int8_t*)base;                         // [nm][n][ldr] residues of one chunk's products (CRT form)
     if (nm_max) base += align_up((size_t)nm_max * res_stride, 1024);
+    int8_t* resid2 = resid;
+    if (overlap) { resid2 = (int8_t*)base; base += align_up((size_t)nm_max * res_stride, 1024); }
     double* sc_all = (double*)base;                        // [nchunks][n] row scales, then [n] row norms
     double* nrm = sc_all + (size_t)ch.nchunks * n;
     base += align_up((size_t)(ch.nchunks + 1) * n * sizeof(double), 256);
@@ -854,6 +869,74 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
             CUDA_TRY(cudaStreamSynchronize(h->stream));    // the host copies are locals
             tables = true;
         }
+    }
+    if (overlap) {
+        // Same kernels, same order per buffer and the same order of the updates of C as the loop below; only
+        // the streams differ.  s1 carries split(0), split(1), then recon(i), split(i+2) for i = 0, 1, ...;
+        // h->stream carries the products.  planes/resid buffer of chunk i: i & 1.
+        std::vector<int> act;
+        for (int c = 0; c < ch.nchunks; ++c)
+            if ((long long)c * ch.kc_full < K && planes_of[c] > 0) act.push_back(c);
+        const int m = (int)act.size();
+        cudaStream_t s1 = nullptr;
+        CUDA_TRY(cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking));
+        std::vector<cudaEvent_t> ev(3 * (size_t)m + 1);
+        for (auto& e : ev) CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        cudaEvent_t* ev_split = ev.data();
+        cudaEvent_t* ev_syrk = ev.data() + m;
+        cudaEvent_t* ev_recon = ev.data() + 2 * m;
+        CUDA_TRY(cudaEventRecord(ev[3 * m], h->stream));          // s1 starts after the row statistics
+        CUDA_TRY(cudaStreamWaitEvent(s1, ev[3 * m], 0));
+        struct Geo { long long k0; int kc, kcpad, nm, bits; const double* sc; };
+        auto geo = [&](int i) {
+            Geo g;
+            const int c = act[i];
+            g.k0 = (long long)c * ch.kc_full;
+            g.kc = (int)std::min<long long>(ch.kc_full, K - g.k0);
+            g.kcpad = (int)align_up((size_t)g.kc, BKB);
+            g.nm = 8;
+            while (g.nm < nm_max && isdf_crt::input_bits(g.nm) < 7 * planes_of[c] - 5) ++g.nm;
+            g.bits = isdf_crt::input_bits(g.nm);
+            g.sc = sc_all + (size_t)c * n;
+            return g;
+        };
+        auto split = [&](int i) -> int {
+            const Geo g = geo(i);
+            if (i >= 2) CUDA_TRY(cudaStreamWaitEvent(s1, ev_syrk[i - 2], 0));     // the products that read this buffer
+            const long long items = (long long)nrows_pad * (g.kcpad / 16);
+            i8_split_crt_kernel<<<(unsigned)((items + 255) / 256), 256, 0, s1>>>(
+                A, lda, n, nrows_pad, g.k0, g.kc, g.kcpad, g.sc, (i & 1) ? planes2 : planes, rb_stride, plane_stride, g.nm, g.bits);
+            CUDA_TRY(cudaEventRecord(ev_split[i], s1));
+            return ISDF_OK;
+        };
+        int rc;
+        if (m > 0 && (rc = split(0)) != ISDF_OK) return rc;
+        if (m > 1 && (rc = split(1)) != ISDF_OK) return rc;
+        for (int i = 0; i < m; ++i) {
+            const Geo g = geo(i);
+            CUDA_TRY(cudaStreamWaitEvent(h->stream, ev_split[i], 0));
+            if (i >= 2) CUDA_TRY(cudaStreamWaitEvent(h->stream, ev_recon[i - 2], 0));    // the reader of this residue buffer
+            SyrkArgs a;
+            a.planes = (i & 1) ? planes2 : planes; a.plane_stride = plane_stride; a.rb_stride = rb_stride;
+            a.tiles = d_tiles; a.ntiles = ntiles; a.n = n; a.nkb = g.kcpad / BKB; a.S = g.nm;
+            a.C = C; a.ldc = ldc; a.sc = g.sc; a.alpha = alpha;
+            a.R = (i & 1) ? resid2 : resid; a.ldr = ldr; a.res_stride = res_stride;
+            if ((rc = launch_syrk2<true>(h, a, nclusters)) != ISDF_OK) return rc;
+            CUDA_TRY(cudaEventRecord(ev_syrk[i], h->stream));
+            CUDA_TRY(cudaStreamWaitEvent(s1, ev_syrk[i], 0));
+            dim3 rg((unsigned)((n + 127) / 128), (unsigned)n);
+            crt_reconstruct_kernel<<<rg, 128, 0, s1>>>((i & 1) ? resid2 : resid, ldr, res_stride, g.nm, n, g.sc,
+                                                        alpha * ldexp(1.0, -2 * g.bits), C, ldc);
+            CUDA_TRY(cudaEventRecord(ev_recon[i], s1));
+            if (i + 2 < m && (rc = split(i + 2)) != ISDF_OK) return rc;
+            g_last_ops += 2.0 * g.nm * (double)ntiles * (double)CT * CT * (double)g.kcpad;
+            h->other_launches += 3;
+        }
+        if (m > 0) CUDA_TRY(cudaStreamWaitEvent(h->stream, ev_recon[m - 1], 0));     // C is complete for whatever follows
+        CUDA_TRY(cudaGetLastError());
+        for (auto& e : ev) CUDA_TRY(cudaEventDestroy(e));          // released when the recorded work has finished
+        CUDA_TRY(cudaStreamDestroy(s1));
+        return ISDF_OK;
     }
     for (int c = 0; c < ch.nchunks; ++c) {
         const long long k0 = (long long)c * ch.kc_full;

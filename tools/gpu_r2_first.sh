@@ -57,3 +57,15 @@ try:
 except Exception as e:
     print('xc: no line', e)
 PY
+# two-stream form of the residue product (ISDF_SYRK_OVERLAP=1): bit-identity test, then a C64 line
+ISDF_TEST_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_syrk_i8_gpu.py -m gpu -q -k overlapped > gpurun_out/pytest_overlap.log 2>&1; echo "overlap rc=$?"; tail -5 gpurun_out/pytest_overlap.log
+ISDF_SYRK_OVERLAP=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
+    > gpurun_out/bench_overlap.json 2> gpurun_out/bench_overlap.err; echo "bench overlap rc=$?"
+python - <<PY
+import json
+try:
+    d = json.loads(open('gpurun_out/bench_overlap.json').read().strip().splitlines()[-1])
+    print('overlap step %.3f s' % d['value'], {k: round(v, 1) for k, v in d['stages_ms'].items()})
+except Exception as e:
+    print('overlap: no line', e)
+PY
