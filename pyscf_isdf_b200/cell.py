@@ -422,13 +422,15 @@ class Cell:
         cut = float(_rcut_overlap(eta**2, 0, 1., self.precision))
         return eta, cut
 
-    def ewald(self):
+    def ewald(self, ew_eta=None, ew_cut=None):
         """Ewald energy of the point (valence) charges; 3-D branch of
-        pyscf/pbc/gto/cell.py:692-813."""
+        pyscf/pbc/gto/cell.py:692-813 (same optional splitting parameter and real-space cutoff)."""
         if self.natm == 0:
             return 0.
         q = self.atom_charges()
         eta, cut = self.get_ewald_params()
+        eta = eta if ew_eta is None else float(ew_eta)
+        cut = cut if ew_cut is None else float(ew_cut)
         logp = np.log(self.precision / (q.sum() * 16 * np.pi**2))
         mesh = cutoff_to_mesh(self._a, -2 * eta**2 * logp)
         xyz = self.atom_coords()

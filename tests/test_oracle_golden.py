@@ -54,6 +54,20 @@ def test_fftdf_jk_golden():
     assert abs(oracle.fp(vk) - 4.290076429522121) < 1e-8
 
 
+def test_ewald_goldens():
+    # pyscf/pbc/gto/test/test_cell.py:117-146: the result does not depend on the splitting parameter
+    c = Cell(unit='B', a=np.diag([5., 5., 5.]), mesh=[41] * 3, atom=[['He', (2, 2.5, 2.5)], ['He', (3, 2.5, 2.5)]],
+             basis={'He': [[0, (1.0, 1.0)]]}, pseudo=None).build()
+    for eta, cut in ((0.2, 30), (1, 30), (None, None)):
+        assert abs(c.ewald(eta, cut) - (-0.468640671931)) < 1e-9
+    rs = np.random.RandomState(10)
+    a = rs.random_sample((3, 3)) * 2 + np.eye(3) * 2
+    c = Cell(a=a, mesh=[41] * 3, atom=[['He', (1, 1, 2)], ['He', (3, 2, 1)]], basis={'He': [[0, (1.0, 1.0)]]},
+             pseudo=None).build()
+    for eta, cut in ((1, 20), (2, 10), (2, 5), (None, None)):
+        assert abs(c.ewald(eta, cut) - (-2.3711356723457615)) < 1e-9
+
+
 def test_c2s_orthonormal():
     """The restated libcint cart->sph matrices give orthonormal real harmonics."""
     from oracle.eval_ao import C2S, cart_powers
