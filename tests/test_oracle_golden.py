@@ -68,6 +68,28 @@ def test_ewald_goldens():
         assert abs(c.ewald(eta, cut) - (-2.3711356723457615)) < 1e-9
 
 
+def test_cell_goldens_gv_si_lattice_images_and_overlap():
+    """Host-side Cell pieces against the reference's own numbers (pyscf/pbc/gto/test/test_cell.py:
+    :40-51 fixture, :65-76 get_Gv / get_SI, :93-114 number of lattice images, :280-292 Gamma-point overlap)."""
+    from pyscf_isdf_b200 import int1e as pint
+    from test_xc_cpu import HE_CCPVDZ
+    rs = np.random.RandomState(1)
+    cl1 = Cell(a=rs.random_sample((3, 3)).T, precision=1e-9, mesh=[41] * 3, pseudo=None, basis={'He': HE_CCPVDZ},
+               atom='He .1 .0 .0; He .5 .1 .0; He .0 .5 .0; He .1 .3 .2').build()
+    Gv = cl1.get_Gv()
+    assert abs(oracle.fp(Gv) - (-99.791927068519939)) < 1e-9
+    assert abs(oracle.fp(cl1.get_SI(Gv)) - (16.506917823339265 + 1.6393578329869585j)) < 1e-9
+    G5 = np.random.RandomState(2).random_sample((5, 3))
+    assert abs(oracle.fp(cl1.get_SI(G5)) - (0.65237631847195221 - 1.5736011413431059j)) < 1e-12
+    # analytic lattice-summed overlap of the reference (it asserts 4 places) against the reciprocal-space sum
+    S, T = pint.overlap_kinetic(cl1)
+    assert abs(oracle.fp(S) - 492.30658304804126) < 1e-4
+    c2 = Cell(atom='C 0 0 0; C 1.685068664391 1.685068664391 1.685068664391', unit='B', basis='gth-dzvp',
+              pseudo='gth-pade', mesh=[15] * 3,
+              a=[[0, 3.370137329, 3.370137329], [3.370137329, 0, 3.370137329], [3.370137329, 3.370137329, 0]]).build()
+    assert c2.get_lattice_Ls(rcut=c2.rcut).shape == (1439, 3)
+
+
 def test_c2s_orthonormal():
     """The restated libcint cart->sph matrices give orthonormal real harmonics."""
     from oracle.eval_ao import C2S, cart_powers
