@@ -198,7 +198,8 @@ int isdf_j_from_potential(isdf_handle* h, const double* phi, long long ldphi, in
  *                        reference; published closed forms here, csrc/xc_core.cuh]; writes
  *                        wv4[4, ldr] = weight (vrho/2, 2 vsigma grad rho) [numint.py:366, :987-994] and
  *                        d_sums[2] (device) = (sum rho weight, sum rho weight exc) [numint.py:361-365].
- *                        code from isdf_xc_code("lda," | "lda,vwn" | "blyp" | "pbe"), -1 if unknown.
+ *                        code from isdf_xc_code("lda," | "lda,vwn" | "blyp" | "pbe" | "pbe0" | "b3lyp"), -1 if unknown;
+ *                        the two hybrids give their semilocal part, the caller adds -fraction/2 K [pbc/dft/rks.py:103-118].
  *   isdf_xc_matrix       vmat[nao, nao] = M + M^T, M = Phi (sum_c wv_c Phi_c)^T [_vxc_mat, numint.py:812-815, :374].
  * A sharded grid sums vmat and d_sums over ranks.  Workspace of the three xc calls: isdf_xc_ws_bytes. */
 int isdf_eval_ao_deriv1(isdf_handle* h,
@@ -209,6 +210,7 @@ int isdf_eval_ao_deriv1(isdf_handle* h,
                         long long g0, long long g1,
                         double* phi4, long long ldphi, long long comp_stride);
 int isdf_xc_code(const char* name);
+double isdf_xc_hybrid_fraction(int code);   /* exact-exchange fraction of "pbe0" (0.25) / "b3lyp" (0.20), else 0 */
 size_t isdf_xc_ws_bytes(int nao, long long ldphi);
 int isdf_xc_density(isdf_handle* h, const double* phi4, long long ldphi, long long comp_stride,
                     int nao, long long ngl, const double* dm, double* rho4, long long ldr,

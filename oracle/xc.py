@@ -8,7 +8,8 @@ not in its tree; the reference calls it through ``pyscf/dft/libxc.py:eval_xc``),
 their published closed forms are restated here as energy densities ``f(rho, sigma)``
 per unit volume and differentiated by the complex-step rule (exact to rounding for
 these analytic expressions):
-  Slater exchange; VWN correlation (form V, Can. J. Phys. 58, 1200; libxc's lda_c_vwn, the
+  Slater exchange; the semilocal parts of PBE0 (0.75 PBE exchange + PBE correlation) and of libxc's B3LYP
+  (0.08 Slater + 0.72 B88 + 0.81 LYP + 0.19 VWN-RPA); VWN correlation (form V, Can. J. Phys. 58, 1200; libxc's lda_c_vwn, the
   'vwn' of the reference's default 'LDA,VWN'); Becke 88 exchange (Phys. Rev. A 38, 3098); LYP correlation in the
   form of Miehlich et al. (Chem. Phys. Lett. 157, 200); PBE exchange and correlation
   (Phys. Rev. Lett. 77, 3865) on the PW92 correlation with libxc's ``pw_mod`` constants.
@@ -83,8 +84,8 @@ def f_pbe_c(rho, sigma):
     return rho * (ec + gamma * np.log(1 + beta / gamma * t2 * (1 + At2) / (1 + At2 + At2 * At2)))
 
 
-def f_vwn5(rho, sigma):
-    A, b, c, x0 = 0.0310907, 3.72744, 12.9352, -0.10498
+def f_vwn5(rho, sigma, params=(0.0310907, 3.72744, 12.9352, -0.10498)):
+    A, b, c, x0 = params
     x = np.sqrt((3 / (4 * np.pi * rho))**(1 / 3.))
     X = x * x + b * x + c
     X0 = x0 * x0 + b * x0 + c
@@ -95,7 +96,21 @@ def f_vwn5(rho, sigma):
     return rho * ec
 
 
+def f_vwn_rpa(rho, sigma):
+    """VWN fit to the RPA correlation energy (libxc lda_c_vwn_rpa): the local correlation of libxc's B3LYP."""
+    return f_vwn5(rho, sigma, (0.0310907, 13.0720, 42.7198, -0.409286))
+
+
+def _scaled(fn, w):
+    return lambda rho, sigma: w * fn(rho, sigma)
+
+
+# semilocal parts of the two hybrids (the exact-exchange fraction is the caller's: K from get_jk)
+HYBRID = {'pbe0': 0.25, 'b3lyp': 0.20}
+
 FUNCTIONALS = {
+    'pbe0': (_scaled(f_pbe_x, 0.75), f_pbe_c),
+    'b3lyp': (_scaled(f_slater, 0.08), _scaled(f_b88, 0.72), _scaled(f_lyp, 0.81), _scaled(f_vwn_rpa, 0.19)),
     'lda,vwn': (f_slater, f_vwn5),
     ',vwn': (f_vwn5,),
     'lda,': (f_slater,),

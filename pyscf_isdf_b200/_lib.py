@@ -61,6 +61,7 @@ SIGNATURES = {
     'isdf_eval_ao_deriv1': (c_int, [c_vp, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_vp,
                                     c_vp, c_int, c_vp, c_ll, c_ll, c_vp, c_ll, c_ll]),
     'isdf_xc_code': (c_int, [ctypes.c_char_p]),
+    'isdf_xc_hybrid_fraction': (c_dbl, [c_int]),
     'isdf_xc_ws_bytes': (c_sz, [c_int, c_ll]),
     'isdf_xc_density': (c_int, [c_vp, c_vp, c_ll, c_ll, c_int, c_ll, c_vp, c_vp, c_ll, c_vp, c_sz]),
     'isdf_xc_potential': (c_int, [c_vp, c_int, c_vp, c_ll, c_ll, c_dbl, c_vp, c_vp, c_vp, c_sz]),
@@ -256,8 +257,11 @@ class Handle:
     def xc_code(self, name):
         code = self.lib.isdf_xc_code(str(name).encode())
         if code < 0:
-            raise NotImplementedError('xc functional %r (have: lda, / lda,vwn / blyp / pbe)' % (name,))
+            raise NotImplementedError('xc functional %r (have: lda, / lda,vwn / blyp / pbe / pbe0 / b3lyp)' % (name,))
         return code
+
+    def xc_hybrid_fraction(self, name):
+        return float(self.lib.isdf_xc_hybrid_fraction(self.xc_code(name)))
 
     def xc_density(self, phi4, ldphi, comp_stride, nao, ngl, dm, rho4, ldr, ws=None):
         nbytes = self.lib.isdf_xc_ws_bytes(nao, ldphi)

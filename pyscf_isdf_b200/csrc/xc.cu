@@ -95,8 +95,12 @@ extern "C" int isdf_xc_code(const char* name)
     if (s == "lda,vwn" || s == "lda,vwn5" || s == "slater,vwn" || s == "svwn") return isdf_xc::XC_LDA_VWN;
     if (s == "blyp" || s == "b88,lyp") return isdf_xc::XC_BLYP;
     if (s == "pbe" || s == "pbe,pbe") return isdf_xc::XC_PBE;
+    if (s == "pbe0") return isdf_xc::XC_PBE0;
+    if (s == "b3lyp") return isdf_xc::XC_B3LYP;
     return -1;
 }
+
+extern "C" double isdf_xc_hybrid_fraction(int code) { return isdf_xc::hybrid_fraction(code); }
 
 extern "C" size_t isdf_xc_ws_bytes(int nao, long long ldphi)
 {
@@ -129,7 +133,7 @@ extern "C" int isdf_xc_potential(isdf_handle* h, int code, const double* rho4, l
                                  double weight, double* wv4, double* d_sums, void* ws, size_t ws_bytes)
 {
     ARG_CHECK(h && rho4 && wv4 && d_sums && ws && ngl > 0 && ldr >= ngl && ngl < 0x7fffffffLL);
-    ARG_CHECK(code == isdf_xc::XC_LDA_X || code == isdf_xc::XC_BLYP || code == isdf_xc::XC_PBE || code == isdf_xc::XC_LDA_VWN);
+    ARG_CHECK(code >= isdf_xc::XC_LDA_X && code <= isdf_xc::XC_B3LYP);
     if (ws_bytes < xc_partial_bytes(ngl) + 256) { isdf_set_error("isdf_xc_potential: workspace too small"); return ISDF_ERR_WS; }
     double* partial = (double*)align_up((size_t)ws, 256);
     const int nblk = (int)((ngl + XC_THREADS - 1) / XC_THREADS);

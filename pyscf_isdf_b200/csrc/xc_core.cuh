@@ -17,6 +17,8 @@ namespace isdf_xc {
 constexpr int XC_LDA_X = 1;      // 'lda,'
 constexpr int XC_BLYP = 2;       // 'blyp' = b88 + lyp
 constexpr int XC_PBE = 3;        // 'pbe'  = pbe exchange + pbe correlation
+constexpr int XC_PBE0 = 5;       // semilocal part of 'pbe0':  0.75 pbe exchange + pbe correlation (exact-exchange fraction 0.25)
+constexpr int XC_B3LYP = 6;      // semilocal part of libxc's 'b3lyp': 0.08 slater + 0.72 b88 + 0.81 lyp + 0.19 vwn-rpa (fraction 0.20)
 constexpr int XC_LDA_VWN = 4;    // 'lda,vwn' = slater + vwn (form V): the default xc of the reference's pbc RKS
 constexpr double RHO_CUT = 1e-15;
 constexpr double SIGMA_FLOOR = 1e-40;
@@ -54,9 +56,8 @@ __host__ __device__ __forceinline__ Dual dasinh(Dual a) { return chain(a, asinh(
 
 __host__ __device__ __forceinline__ Dual datan(Dual a) { return chain(a, atan(a.v), 1.0 / (1.0 + a.v * a.v)); }
 
-__host__ __device__ inline Dual f_vwn5(Dual rho)
+__host__ __device__ inline Dual f_vwn(Dual rho, double A, double b, double c, double x0)
 {
-    const double A = 0.0310907, b = 3.72744, c = 12.9352, x0 = -0.10498;
     const Dual x = dsqrt(dpow(3.0 / (4.0 * PI) / rho, 1.0 / 3.0));
     const Dual X = x * x + b * x + c;
     const double X0 = x0 * x0 + b * x0 + c;
@@ -67,6 +68,8 @@ __host__ __device__ inline Dual f_vwn5(Dual rho)
                          - b * x0 / X0 * (dlog(xm * xm / X) + 2.0 * (b + 2.0 * x0) / Q * at));
     return rho * ec;
 }
+__host__ __device__ inline Dual f_vwn5(Dual rho) { return f_vwn(rho, 0.0310907, 3.72744, 12.9352, -0.10498); }
+__host__ __device__ inline Dual f_vwn_rpa(Dual rho) { return f_vwn(rho, 0.0310907, 13.0720, 42.7198, -0.409286); }
 
 __host__ __device__ inline Dual f_slater(Dual rho)
 {
@@ -134,12 +137,15 @@ __host__ __device__ inline Dual f_pbe_c(Dual rho, Dual sigma)
     return rho * (ec + gamma * dlog(1.0 + beta / gamma * t2 * (1.0 + At2) / (1.0 + At2 + At2 * At2)));
 }
 
+// exact-exchange fraction that goes with a functional code (the caller adds -fraction/2 K)
+__host__ __device__ inline double hybrid_fraction(int code) { return code == XC_PBE0 ? 0.25 : (code == XC_B3LYP ? 0.20 : 0.0); }
+
 // exc per particle, vrho = df/drho, vsigma = df/dsigma; zeros below the density threshold.
 // Returns false for an unknown functional code.
 __host__ __device__ inline bool eval_point(int code, double rho, double sigma, double* exc, double* vrho, double* vsigma)
 {
     *exc = 0.0; *vrho = 0.0; *vsigma = 0.0;
-    if (code != XC_LDA_X && code != XC_BLYP && code != XC_PBE && code != XC_LDA_VWN) return false;
+    if (code < XC_LDA_X || code > XC_B3LYP) return false;
     if (!(rho > RHO_CUT)) return true;
     const Dual r{rho, 1.0, 0.0};
     const Dual s{sigma > SIGMA_FLOOR ? sigma : SIGMA_FLOOR, 0.0, 1.0};
@@ -147,6 +153,8 @@ __host__ __device__ inline bool eval_point(int code, double rho, double sigma, d
     if (code == XC_LDA_X) f = f_slater(r);
     else if (code == XC_LDA_VWN) f = f_slater(r) + f_vwn5(r);
     else if (code == XC_BLYP) f = f_b88(r, s) + f_lyp(r, s);
+    else if (code == XC_PBE0) f = 0.75 * f_pbe_x(r, s) + f_pbe_c(r, s);
+    else if (code == XC_B3LYP) f = 0.08 * f_slater(r) + 0.72 * f_b88(r, s) + 0.81 * f_lyp(r, s) + 0.19 * f_vwn_rpa(r);
     else f = f_pbe_x(r, s) + f_pbe_c(r, s);
     *exc = f.v / rho; *vrho = f.r; *vsigma = f.s;
     return true;

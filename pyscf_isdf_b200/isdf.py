@@ -444,7 +444,7 @@ class ISDF:
 
     def nr_rks(self, xc_code, dm, kpts=None, max_bytes=None):
         """(nelec, exc, vmat) of a closed-shell density matrix at the Gamma point: NumInt.nr_rks of the
-        reference (pyscf/pbc/dft/numint.py:283-381) for the functionals 'lda,', 'lda,vwn', 'blyp' and 'pbe', on the
+        reference (pyscf/pbc/dft/numint.py:283-381) for the functionals 'lda,', 'lda,vwn', 'blyp', 'pbe' and the semilocal parts of 'pbe0' / 'b3lyp', on the
         device: density and gradient from the AO values, the functional, and the potential matrix.  With a
         sharded grid every rank works on its slab and the three results are summed over ranks.
 
@@ -483,6 +483,12 @@ class ISDF:
             self.comm.all_reduce_sum(total)
         res = total.cpu().numpy()
         return float(res[-2]), float(res[-1]), res[:nao * nao].reshape(nao, nao).copy()
+
+    def xc_hybrid_fraction(self, xc_code):
+        """Exact-exchange fraction of a functional nr_rks knows ('pbe0' 0.25, 'b3lyp' 0.20, else 0): for the
+        hybrids nr_rks returns the semilocal part and the caller adds ``-fraction/2 K`` from get_jk, as
+        pyscf/pbc/dft/rks.py:103-118 does."""
+        return self.handle.xc_hybrid_fraction(xc_code)
 
     def numint(self):
         """Object with the ``nr_rks`` call signature the reference's RKS uses on ``mf._numint``
@@ -526,6 +532,11 @@ class ISDFNumInt:
 
     def __init__(self, mydf):
         self.mydf = mydf
+
+    def rsh_and_hybrid_coeff(self, xc_code, spin=0):
+        """(omega, alpha, hyb) in the reference's convention (pyscf/dft/numint.py:rsh_and_hybrid_coeff):
+        no range separation here, so (0, 0, exact-exchange fraction)."""
+        return 0.0, 0.0, self.mydf.xc_hybrid_fraction(xc_code)
 
     def nr_rks(self, cell, grids, xc_code, dms, relativity=0, hermi=1, kpt=None, kpts_band=None,
                max_memory=2000, verbose=None):

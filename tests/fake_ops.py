@@ -199,9 +199,13 @@ class FakeOps:
 
     # -- exchange-correlation (NumPy restatement of what csrc/xc.cu computes) ---------
     def xc_code(self, name):
-        if str(name).lower() not in ('lda,', 'blyp', 'pbe', 'lda,vwn'):
+        if str(name).lower() not in ('lda,', 'blyp', 'pbe', 'lda,vwn', 'pbe0', 'b3lyp'):
             raise NotImplementedError('xc functional %r' % (name,))
         return str(name).lower()
+
+    def xc_hybrid_fraction(self, name):
+        from oracle import xc
+        return xc.HYBRID.get(self.xc_code(name), 0.0)
 
     def xc_density(self, phi4, ldphi, comp_stride, nao, ngl, dm, rho4, ldr, ws=None):
         P = _np(phi4)[:, :nao, :ngl]

@@ -55,6 +55,8 @@ def _run_rank(comm, out=None, fit='implicit'):
     two = ni.nr_rks(cell, None, 'pbe', np.stack([dm, dm]), 0, 1, None, None)
     assert one[0] == xc_out['pbe'][0] and np.array_equal(one[2], xc_out['pbe'][2])
     assert two[0].shape == (2,) and two[2].shape == (2,) + dm.shape and np.array_equal(two[2][1], one[2])
+    assert ni.rsh_and_hybrid_coeff('pbe0') == (0.0, 0.0, 0.25) and mydf.xc_hybrid_fraction('pbe') == 0.0
+    xc_out['b3lyp'] = mydf.nr_rks('b3lyp', dm)          # semilocal part of a hybrid
     res = dict(xc=xc_out, ip=mydf.ip_index, W=mydf.W.numpy().copy(), X=mydf.aoR_ip.numpy().copy(), vpp=vpp, vne=vne, vnl=vnl,
                p0=int(mydf._part.ip_off[comm.rank]),
                vj=vj.numpy()[0].copy(), vk=vk.numpy()[0].copy(), slab=mydf._slab,

@@ -87,6 +87,16 @@ def test_functional_derivatives_and_published_limits():
     assert abs(xc.f_vwn5(rr, 0 * rr) / rr - xc.eps_pw92(rs_)).max() < 6e-4
     e = lambda x: xc.f_vwn5(np.array([3 / (4 * np.pi * x**3)]), 0.0)[0] / (3 / (4 * np.pi * x**3))      # noqa: E731
     assert abs((e(2e-6) - e(1e-6)) / np.log(2.0) - 0.0310907) < 2e-4
+    # VWN fit to the RPA correlation energy (the local correlation of libxc's B3LYP) against the RPA values
+    # of the electron gas at rs = 1, 2, 5, 10 (-0.157, -0.124, -0.0844, -0.0614 Ry)
+    rpa = np.array([-0.0785, -0.0619, -0.0422, -0.0307])
+    r4 = 3 / (4 * np.pi * np.array([1.0, 2.0, 5.0, 10.0])**3)
+    assert abs(xc.f_vwn_rpa(r4, 0 * r4) / r4 - rpa).max() < 1.5e-3
+    # the hybrids' semilocal parts are the stated mixtures
+    rr_, ss_ = np.array([0.2, 1.1]), np.array([0.05, 2.0])
+    e_pbe0 = xc.eval_xc('pbe0', rr_, ss_)[0]
+    assert abs(e_pbe0 - (0.75 * xc.eval_xc('pbe,', rr_, ss_)[0] + xc.eval_xc(',pbe', rr_, ss_)[0])).max() < 1e-15
+    assert xc.HYBRID == {'pbe0': 0.25, 'b3lyp': 0.20}
     # densities below the threshold give zeros, not NaNs
     e0, v0, s0 = xc.eval_xc('pbe', np.array([0.0, 1e-20]), np.array([0.0, 1e-30]))
     assert (e0 == 0).all() and (v0 == 0).all() and (s0 == 0).all()

@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, 'emul', 'xc_emul.cpp')
 OUT = os.path.join(HERE, 'emul', '_build', 'libxc_emul.so')
 DEPS = [SRC, os.path.join(HERE, '..', 'pyscf_isdf_b200', 'csrc', 'xc_core.cuh')]
-CODES = {'lda,': 1, 'blyp': 2, 'pbe': 3, 'lda,vwn': 4}
+CODES = {'lda,': 1, 'blyp': 2, 'pbe': 3, 'lda,vwn': 4, 'pbe0': 5, 'b3lyp': 6}
 
 
 @pytest.fixture(scope='module')
@@ -32,7 +32,7 @@ def _eval(lib, code, rho, sigma):
     return rc, out
 
 
-@pytest.mark.parametrize('name', ['lda,', 'blyp', 'pbe', 'lda,vwn'])
+@pytest.mark.parametrize('name', ['lda,', 'blyp', 'pbe', 'lda,vwn', 'pbe0', 'b3lyp'])
 def test_dual_number_functionals_match_the_oracle(lib, name):
     rng = np.random.default_rng(11)
     n = 4000

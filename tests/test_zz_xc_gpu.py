@@ -48,7 +48,7 @@ def test_ao_gradients_match_oracle_and_value_plane_matches_eval_ao(which):
     assert abs(part.cpu().numpy()[:, :, :g1 - g0] - ref[:, :, g0:g1]).max() < 1e-12
 
 
-@pytest.mark.parametrize('name', ['pbe', 'blyp', 'lda,', 'lda,vwn'])
+@pytest.mark.parametrize('name', ['pbe', 'blyp', 'lda,', 'lda,vwn', 'pbe0', 'b3lyp'])
 def test_nr_rks_matches_oracle(name):
     cell = _cells()['c8']
     dm = rand_dm(cell.nao) * 0.05
