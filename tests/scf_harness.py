@@ -49,9 +49,11 @@ def rhf_gamma(hcore, ovlp, nelec, enuc, get_jk, conv_tol=1e-11, max_cycle=60):
     raise RuntimeError('SCF not converged')
 
 
-def rks_gamma(hcore, ovlp, nelec, enuc, get_j, nr_rks, conv_tol=1e-10, max_cycle=80):
-    """Restricted Kohn-Sham with a pure functional: get_j(dm) -> vj, nr_rks(dm) -> (nelec, exc, vxc);
-    E = Tr[D h] + 1/2 Tr[D J] + Exc + E_nuc (pyscf/pbc/dft/rks.py:44-125).  Returns (e_tot, dm, ncycle)."""
+def rks_gamma(hcore, ovlp, nelec, enuc, get_j, nr_rks, conv_tol=1e-10, max_cycle=80, get_k=None, hyb=0.0):
+    """Restricted Kohn-Sham: get_j(dm) -> vj, nr_rks(dm) -> (nelec, exc, vxc) of the semilocal part; for a
+    hybrid also get_k(dm) -> vk and its exact-exchange fraction hyb.
+    E = Tr[D h] + 1/2 Tr[D J] + Exc - hyb/4 Tr[D K] + E_nuc,  F = h + J + Vxc - hyb/2 K
+    (pyscf/pbc/dft/rks.py:44-125).  Returns (e_tot, dm, ncycle)."""
     nocc = nelec // 2
 
     def density(f):
@@ -67,6 +69,10 @@ def rks_gamma(hcore, ovlp, nelec, enuc, get_j, nr_rks, conv_tol=1e-10, max_cycle
         _, exc, vxc = nr_rks(dm)
         f = hcore + vj + vxc
         e_tot = np.einsum('ij,ji->', dm, hcore) + 0.5 * np.einsum('ij,ji->', dm, vj) + exc + enuc
+        if hyb:
+            vk = get_k(dm)
+            f = f - 0.5 * hyb * vk
+            e_tot -= 0.25 * hyb * np.einsum('ij,ji->', dm, vk)
         err = f.dot(dm).dot(ovlp)
         err = err - err.T
         focks.append(f)

@@ -119,3 +119,28 @@ def test_product_overlap_kinetic_match_the_oracle():
         S, T = pint.overlap_kinetic(cell)
         assert abs(S - S0).max() < 1e-13 and abs(T - T0).max() < 1e-13
         assert np.linalg.eigvalsh(S).min() > 0
+
+
+def test_hybrid_functional_with_isdf_exchange():
+    """PBE0 on the primitive diamond cell: semilocal part from nr_rks('pbe0'), exact exchange with its
+    fraction from the hybrid table -- once with the exact FFT K, once with ISDF J/K at full pair rank
+    (c = 20 > (nao+1)/2): the two total energies agree to 1e-9 Ha, and dropping the exchange fraction moves
+    the energy by far more (the pieces really are combined)."""
+    from oracle import xc
+    from scf_harness import rks_gamma
+    cell = diamond_primitive([13] * 3)
+    S, hcore, ao4 = oracle_rks_pieces(cell)
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    w = cell.vol / ao4.shape[1]
+    mad = madelung(cell)
+    hyb = xc.HYBRID['pbe0']
+    nr = lambda dm: xc.nr_rks(ao4, w, 'pbe0', dm)                        # noqa: E731
+    exact = lambda dm: oracle.fftdf_get_jk(ao4[0], dm, a, mesh, exxdiv='ewald', ovlp=S, madelung=mad)   # noqa: E731
+    e0 = rks_gamma(hcore, S, cell.nelectron, cell.ewald(), lambda dm: exact(dm)[0], nr,
+                   get_k=lambda dm: exact(dm)[1], hyb=hyb)[0]
+    ref = oracle.isdf_build(np.ascontiguousarray(ao4[0].T), a, mesh, 20 * cell.nao)
+    isdf = lambda dm: oracle.isdf_get_jk(ref['X'], ref['W'], dm, exxdiv='ewald', ovlp=S, madelung=mad)  # noqa: E731
+    e1 = rks_gamma(hcore, S, cell.nelectron, cell.ewald(), lambda dm: isdf(dm)[0], nr,
+                   get_k=lambda dm: isdf(dm)[1], hyb=hyb)[0]
+    e2 = rks_gamma(hcore, S, cell.nelectron, cell.ewald(), lambda dm: exact(dm)[0], nr)[0]
+    assert abs(e1 - e0) < 1e-9 and abs(e2 - e0) > 1e-2
