@@ -144,3 +144,23 @@ def test_hybrid_functional_with_isdf_exchange():
                    get_k=lambda dm: isdf(dm)[1], hyb=hyb)[0]
     e2 = rks_gamma(hcore, S, cell.nelectron, cell.ewald(), lambda dm: exact(dm)[0], nr)[0]
     assert abs(e1 - e0) < 1e-9 and abs(e2 - e0) > 1e-2
+
+
+E_RHF_C2_PRIMITIVE = -10.137043711032916     # pyscf/pbc/scf/test/test_newton.py:28-59 (RHF, exxdiv='ewald', mesh 19^3)
+
+
+def diamond_primitive_bohr(mesh):
+    """Fixture of pyscf/pbc/scf/test/test_newton.py:28-45."""
+    return Cell(unit='B', atom='C 0 0 0; C 1.68506879 1.68506879 1.68506879', basis='gth-szv', pseudo='gth-pade',
+                mesh=mesh, a=[[0, 3.37013758, 3.37013758], [3.37013758, 0, 3.37013758], [3.37013758, 3.37013758, 0]]).build()
+
+
+def test_rhf_energy_of_diamond_with_pseudopotential_reproduces_the_reference():
+    """Hartree-Fock exchange with the Ewald correction on top of the GTH one-electron part: 6e-10 Ha."""
+    cell = diamond_primitive_bohr([19] * 3)
+    S, hcore, ao4 = oracle_rks_pieces(cell)
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    mad = madelung(cell)
+    e = rhf_gamma(hcore, S, cell.nelectron, cell.ewald(),
+                  lambda dm: oracle.fftdf_get_jk(ao4[0], dm, a, mesh, exxdiv='ewald', ovlp=S, madelung=mad))[0]
+    assert abs(e - E_RHF_C2_PRIMITIVE) < 1e-8

@@ -50,3 +50,15 @@ def test_rks_lda_energy_of_diamond_with_device_hcore_and_j():
 
 def test_rks_lda_energy_of_diamond_all_on_device():
     _rks_diamond(True)
+
+
+def test_rhf_energy_of_diamond_with_pseudopotential_through_the_plugin():
+    """pyscf/pbc/scf/test/test_newton.py:52-59: RHF, exxdiv='ewald', diamond primitive cell, gth-szv/gth-pade.
+    ISDF with n_ip above the pair rank (36) is exact; get_pp supplies local + non-local parts."""
+    from test_scf_cpu import E_RHF_C2_PRIMITIVE, diamond_primitive_bohr
+    cell = diamond_primitive_bohr([19] * 3)
+    S, T = int1e.overlap_kinetic(cell)
+    mydf = ISDF(cell, n_ip=60).build()
+    assert mydf.n_ip <= 36
+    e = rhf_gamma(T + mydf.get_pp(), S, cell.nelectron, cell.ewald(), lambda dm: mydf.get_jk(dm, exxdiv='ewald'))[0]
+    assert abs(e - E_RHF_C2_PRIMITIVE) < 1e-7, e - E_RHF_C2_PRIMITIVE
