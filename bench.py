@@ -494,6 +494,10 @@ def run_b200(args):
         planes = int(args.wgemm.split(':')[1]) if ':' in args.wgemm else 8
         ops = float(getattr(h, 'syrk_i8_ops', 0.0))         # int8 ops issued by this rank's last W product
         crt = os.environ.get('ISDF_SYRK_CRT')
+        try:
+            crt = None if crt is None else str(int(crt))
+        except ValueError:
+            crt = '0'                                        # the library reads it with atoi()
         form = ('digit planes: S(S+1)/2 int8 products per K chunk' if crt is not None and int(crt) <= 0 else
                 'residues modulo %d coprime moduli <= 256 (one int8 product per modulus, Garner reconstruction)'
                 % (16 if crt is None else max(8, min(16, int(crt)))))
