@@ -14,6 +14,17 @@
 
 void isdf_set_error(const char* fmt, ...);
 
+// Kernel attributes are per function AND per device, and several handles (threads, devices) may
+// share one process: these two are the only places the library sets them.
+//  isdf_func_max_smem: raises cudaFuncAttributeMaxDynamicSharedMemorySize of `func` on the current
+//    device to at least `bytes`; never lowers it (a launch in flight on another thread keeps its limit).
+//  isdf_func_attr_once: sets `attr` = `value` once per (function, device); returns the first call's result.
+int isdf_func_max_smem(const void* func, size_t bytes);
+cudaError_t isdf_func_attr_once(const void* func, int attr, int value);
+// runs `fn(arg)` once per (key, current device) under the library's set-up lock; a failing fn is retried
+// by the next call.  For constant-memory tables and similar per-device set-up.
+int isdf_once_per_device(const void* key, int (*fn)(void*), void* arg);
+
 #define CUDA_TRY(expr)                                                        \
     do {                                                                      \
         cudaError_t _e = (expr);                                              \

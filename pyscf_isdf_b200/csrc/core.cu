@@ -2,6 +2,9 @@
 #include "common.cuh"
 #include "../../include/isdf_b200.h"
 #include <cstdarg>
+#include <map>
+#include <mutex>
+#include <utility>
 
 static thread_local char g_err[1024] = "";
 
@@ -14,6 +17,56 @@ void isdf_set_error(const char* fmt, ...)
 }
 
 extern "C" const char* isdf_last_error(void) { return g_err; }
+
+// ---- per-(function, device) kernel attributes and per-device set-up, safe for several threads ----
+namespace {
+std::mutex g_setup_mutex;
+std::map<std::pair<const void*, int>, size_t> g_smem_set;                       // (func, device) -> bytes
+std::map<std::pair<std::pair<const void*, int>, int>, cudaError_t> g_attr_set;  // ((func, attr), device)
+std::map<std::pair<const void*, int>, bool> g_once_done;                        // (key, device)
+}  // namespace
+
+int isdf_func_max_smem(const void* func, size_t bytes)
+{
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_setup_mutex);
+    size_t& have = g_smem_set[std::make_pair(func, dev)];
+    if (bytes > have) {
+        CUDA_TRY(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        have = bytes;
+    }
+    return ISDF_OK;
+}
+
+cudaError_t isdf_func_attr_once(const void* func, int attr, int value)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lk(g_setup_mutex);
+    auto key = std::make_pair(std::make_pair(func, attr), dev);
+    auto it = g_attr_set.find(key);
+    if (it != g_attr_set.end()) return it->second;
+    e = cudaFuncSetAttribute(func, (cudaFuncAttribute)attr, value);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    g_attr_set[key] = e;
+    return e;
+}
+
+int isdf_once_per_device(const void* key, int (*fn)(void*), void* arg)
+{
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_setup_mutex);
+    bool& done = g_once_done[std::make_pair(key, dev)];
+    if (!done) {
+        const int rc = fn(arg);
+        if (rc) return rc;
+        done = true;
+    }
+    return ISDF_OK;
+}
 
 extern "C" int isdf_create(int device, isdf_handle** out)
 {

@@ -73,8 +73,8 @@ int make_plans(isdf_handle* h, const int* mesh, Plans& P)
 template <typename K>
 int set_smem(K kern, size_t smem)
 {
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    return ISDF_OK;
+    // per (kernel, device), raised only: several handles may launch different widths at once
+    return isdf_func_max_smem((const void*)kern, smem);
 }
 
 // launch the FUSED = false instantiation, or hand a fused plan (FftPlan::rader >= 2) to fft_fused.cu
@@ -115,15 +115,18 @@ void fill_geom(CoulGeom& g, const int* mesh, const double* a, double scale)
 // pass reads whole lines and prefers more resident CTAs (tuning knobs ISDF_FFT_SMEM_KB / _Z_KB)
 size_t fft_smem_budget(bool zpass = false)
 {
-    static size_t v[2] = {0, 0};
-    if (v[0] == 0) {
-        const char* e = getenv("ISDF_FFT_SMEM_KB");
-        const char* ez = getenv("ISDF_FFT_SMEM_Z_KB");
-        const long kb = e ? atol(e) : 64, kbz = ez ? atol(ez) : 64;
-        v[0] = (size_t)std::min(200L, std::max(8L, kb)) * 1024;
-        v[1] = (size_t)std::min(200L, std::max(8L, kbz)) * 1024;
-    }
-    return v[zpass ? 1 : 0];
+    struct Budget {
+        size_t v[2];
+        Budget() {
+            const char* e = getenv("ISDF_FFT_SMEM_KB");
+            const char* ez = getenv("ISDF_FFT_SMEM_Z_KB");
+            const long kb = e ? atol(e) : 64, kbz = ez ? atol(ez) : 64;
+            v[0] = (size_t)std::min(200L, std::max(8L, kb)) * 1024;
+            v[1] = (size_t)std::min(200L, std::max(8L, kbz)) * 1024;
+        }
+    };
+    static const Budget b;                  // initialised once, thread-safe (C++11 function-local static)
+    return b.v[zpass ? 1 : 0];
 }
 
 // lines (or columns) per CTA such that two ping-pong buffers of `nalloc` slots per line fit the budget

@@ -9,8 +9,7 @@ namespace {
 template <typename K>
 int set_smem_f(K kern, size_t smem)
 {
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    return ISDF_OK;
+    return isdf_func_max_smem((const void*)kern, smem);
 }
 
 }  // namespace

@@ -87,13 +87,8 @@ int gemm_call(isdf_handle* h, int M, int N, int K,
 
 int diag_kernel_cfg()
 {
-    static bool done = false;
     const size_t smem = sizeof(double) * CB * (CB + 1);
-    if (!done) {
-        CUDA_TRY(cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        done = true;
-    }
-    return ISDF_OK;
+    return isdf_func_max_smem((const void*)chol_diag_kernel, smem);
 }
 
 // In-place blocked Cholesky of the upper triangle of A[np, np]; Vinv gets the

@@ -253,11 +253,7 @@ int launch_cfg(isdf_handle* h, const GemmParams& p)
     constexpr int BM = 8 * MI * WM, BN = WTN * WN, NT = 32 * WM * WN;
     const size_t smem = sizeof(double) * NSTAGE * (OpTile<BM, AK>::SIZE + OpTile<BN, BKM>::SIZE);
     auto kern = dgemm_kernel<WM, WN, NSTAGE, AK, BKM, NEG, MI>;
-    static bool configured = false;
-    if (!configured) {
-        CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
-    }
+    { int rc_; if ((rc_ = isdf_func_max_smem((const void*)kern, smem))) return rc_; }
     dim3 grid((p.M + BM - 1) / BM, (p.N + BN - 1) / BN);
     const bool prof = h->prof_on && h->prof_n < h->prof_cap;
     if (prof) CUDA_TRY(cudaEventRecord(h->prof_ev[2 * h->prof_n], h->stream));

@@ -852,7 +852,7 @@ extern "C" size_t isdf_select_ip_ws_bytes(int nao, long long ng, int npts)
 
 extern "C" int isdf_select_max_rows(void) { return MCAP; }
 extern "C" int isdf_select_panel_width(void) { return NB; }
-static int g_last_panel_mode = 0;
+static thread_local int g_last_panel_mode = 0;   // per calling thread (one handle per thread)
 extern "C" int isdf_select_last_panel_mode(void) { return g_last_panel_mode; }
 extern "C" int isdf_select_row_len(int nao, int k0) { return row_len(nao, k0); }
 
@@ -1003,29 +1003,27 @@ extern "C" int isdf_select_panel(isdf_select_plan* pl, const double* blocks, int
         const int cpb = (((m + PANEL_CTAS - 1) / PANEL_CTAS) + 31) & ~31;
         int use_smem = cpb <= 192 ? 1 : 0;
         const size_t psmem = use_smem ? sizeof(double) * NB * cpb : 0;
-        static size_t psmem_cfg = 0;
-        if (psmem > psmem_cfg) {
-            CUDA_TRY(cudaFuncSetAttribute(panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(double) * NB * 192)));
-            psmem_cfg = sizeof(double) * NB * 192;
+        if (psmem > 0) {
+            int rc_;
+            if ((rc_ = isdf_func_max_smem((const void*)panel_kernel, sizeof(double) * NB * 192))) return rc_;
         }
         // opt-in: the same factorisation as one 16-CTA thread-block cluster (DSMEM exchange, hardware barrier)
         // (the variable is read at every panel so that one process can compare the forms)
-        static int cluster_ok = -1;              // -1 attributes not set yet, 0 unavailable on this device, 1 usable
+        int cluster_ok = -1;                     // 0 unavailable on this device, 1 usable
         int cluster_mode = 0;                    // 1: DSMEM reads + cluster barrier, 2: st.async pushes + mbarrier
         {
             const char* e = getenv("ISDF_PANEL_CLUSTER");
             cluster_mode = e ? atoi(e) : 0;
             if (cluster_mode < 0 || cluster_mode > 2) cluster_mode = 0;
         }
-        if (cluster_mode && cluster_ok < 0) {
-            cudaError_t e1 = cudaFuncSetAttribute(panel_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-            cudaError_t e2 = cudaFuncSetAttribute(panel_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                  (int)(sizeof(double) * NB * 192));
-            cudaError_t e3 = cudaFuncSetAttribute(panel_push_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-            cudaError_t e4 = cudaFuncSetAttribute(panel_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                  (int)(sizeof(double) * NB * PUSH_CPB_MAX));
+        if (cluster_mode) {                      // attributes: once per (kernel, device), remembered with their outcome
+            cudaError_t e1 = isdf_func_attr_once((const void*)panel_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaError_t e2 = isdf_func_attr_once((const void*)panel_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)(sizeof(double) * NB * 192));
+            cudaError_t e3 = isdf_func_attr_once((const void*)panel_push_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaError_t e4 = isdf_func_attr_once((const void*)panel_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)(sizeof(double) * NB * PUSH_CPB_MAX));
             cluster_ok = (e1 == cudaSuccess && e2 == cudaSuccess && e3 == cudaSuccess && e4 == cudaSuccess) ? 1 : 0;
-            if (!cluster_ok) cudaGetLastError();
         }
         if (cluster_ok != 1) cluster_mode = 0;
         bool launched = false;
@@ -1087,13 +1085,9 @@ extern "C" int isdf_select_flush(isdf_select_plan* pl, const double* phi, long l
     SelWs& w = pl->w;
     const int rl = row_len(pl->nao, k0), naop = pad2(pl->nao);
     const long long ngl = pl->ngl;
-    static bool sweep_cfg = false;
     const size_t sweep_smem = sizeof(double) * (NB * (NB + 1) / 2 + NB);
-    if (!sweep_cfg) {
-        CUDA_TRY(cudaFuncSetAttribute(panel_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem));
-        sweep_cfg = true;
-    }
     int rc;
+    if ((rc = isdf_func_max_smem((const void*)panel_sweep_kernel, sweep_smem))) return rc;
     double* Ltp = Lt + (long long)k0 * ldl;
     if ((rc = gemm_kc(h, nb, (int)ngl, pl->nao, w.PivRows + META, rl, phi, ldphi, 1, Ltp, ldl, nullptr, 0, EPI_SQUARE))) return rc;
     if (k0 > 0)

@@ -657,27 +657,36 @@ Chunks plan_chunks(long long K)
 }
 
 
-double g_last_ops = 0.0;      // int8 operations (2 per multiply-add) issued by the last isdf_syrk_i8 call
+thread_local double g_last_ops = 0.0;      // int8 operations (2 per multiply-add) issued by the last isdf_syrk_i8 call
+
+int upload_crt_tables(void* arg)
+{
+    isdf_handle* h = (isdf_handle*)arg;
+    int hm[isdf_crt::NM_MAX]; double hi[isdf_crt::NM_MAX];
+    for (int k = 0; k < isdf_crt::NM_MAX; ++k) { hm[k] = isdf_crt::modulus(k); hi[k] = 1.0 / (double)hm[k]; }
+    CUDA_TRY(cudaMemcpyToSymbolAsync(c_mod, hm, sizeof(hm), 0, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaMemcpyToSymbolAsync(c_invp, hi, sizeof(hi), 0, cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));    // the host copies are locals
+    return ISDF_OK;
+}
 
 int cluster_size()
 {
-    static int cl = 0;
-    if (!cl) {
+    static const int cl = [] {                                // read once, thread-safe
         const char* e = getenv("ISDF_SYRK_CLUSTER");          // tuning knob: 1, 2, 4 or 8 CTAs per cluster
-        cl = e ? atoi(e) : 4;
-        if (cl != 1 && cl != 2 && cl != 4 && cl != 8) cl = 4;
-    }
+        const int c = e ? atoi(e) : 4;
+        return (c != 1 && c != 2 && c != 4 && c != 8) ? 4 : c;
+    }();
     return cl;
 }
 
 // 2 (default): 256x256 tiles, 2x2 clusters (syrk_i8_kernel2); 1: 128x256 tiles, CL x 1 clusters
 int kernel_variant()
 {
-    static int v = 0;
-    if (!v) {
+    static const int v = [] {
         const char* e = getenv("ISDF_SYRK_KERNEL");
-        v = (e && atoi(e) == 1) ? 1 : 2;
-    }
+        return (e && atoi(e) == 1) ? 1 : 2;
+    }();
     return v;
 }
 
@@ -712,7 +721,7 @@ int launch_syrk2(isdf_handle* h, const SyrkArgs& a, int& nclusters, cudaStream_t
 {
     if (!stream) stream = h->stream;
     if (nclusters == 0) {
-        CUDA_TRY(cudaFuncSetAttribute(syrk_i8_kernel2<CRT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM2));
+        { int rc_; if ((rc_ = isdf_func_max_smem((const void*)syrk_i8_kernel2<CRT>, SMEM2))) return rc_; }
         int fit = h->num_sms / 4;
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(h->num_sms / 4 * 4); cfg.blockDim = dim3(NTHREADS2); cfg.dynamicSmemBytes = SMEM2;
@@ -733,7 +742,7 @@ int launch_syrk(isdf_handle* h, const SyrkArgs& a, int& nclusters)
 {
     auto kern = syrk_i8_kernel<CL>;
     if (nclusters == 0) {
-        CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+        { int rc_; if ((rc_ = isdf_func_max_smem((const void*)kern, SMEM_BYTES))) return rc_; }
         int fit = h->num_sms / CL;
         if (CL > 1) {                                          // how many clusters are co-resident on this GPU
             cudaLaunchConfig_t cfg = {};
@@ -860,15 +869,10 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     g_last_ops = 0.0;
     int nclusters = 0;
     if (nm_max) {
-        static bool tables = false;
-        if (!tables) {
-            int hm[isdf_crt::NM_MAX]; double hi[isdf_crt::NM_MAX];
-            for (int k = 0; k < isdf_crt::NM_MAX; ++k) { hm[k] = isdf_crt::modulus(k); hi[k] = 1.0 / (double)hm[k]; }
-            CUDA_TRY(cudaMemcpyToSymbolAsync(c_mod, hm, sizeof(hm), 0, cudaMemcpyHostToDevice, h->stream));
-            CUDA_TRY(cudaMemcpyToSymbolAsync(c_invp, hi, sizeof(hi), 0, cudaMemcpyHostToDevice, h->stream));
-            CUDA_TRY(cudaStreamSynchronize(h->stream));    // the host copies are locals
-            tables = true;
-        }
+        // the moduli tables live in constant memory: one upload per device, under the set-up lock
+        static const char tables_key = 0;
+        int rc_;
+        if ((rc_ = isdf_once_per_device(&tables_key, upload_crt_tables, h))) return rc_;
     }
     if (overlap) {
         // Same kernels, same order per buffer and the same order of the updates of C as the loop below; only

@@ -237,3 +237,57 @@ def test_get_jk_matches_oracle(handle):
     handle.get_jk(dX, dW, ddm, 2, nao, npts, False, True, None, vk2)
     torch.cuda.synchronize()
     assert np.array_equal(vk2.cpu().numpy(), vk.cpu().numpy())
+
+
+def test_three_threads_launch_x_passes_of_different_widths(handle):
+    """Several handles driven by threads of one process (SURVEY 8b's threading row): kernel attributes are
+    per (function, device), so launches of different shared-memory sizes must not disturb each other.
+    Three threads run the fused x pass on column slabs of different widths 200 times each (round 1's
+    driver run failed exactly here: fft.cu set the attribute to each launch's own size)."""
+    import threading
+    import torch
+    from pyscf_isdf_b200._lib import Handle
+    mesh = [15, 14, 12]
+    a = np.array([[5.0, 0.3, 0.1], [0.2, 4.5, -0.4], [0.0, 0.6, 6.0]])
+    nx, ncols = mesh[0], mesh[1] * (mesh[2] // 2 + 1)
+    widths = [(0, 33), (33, 33), (66, 32)]            # the 33/33/32 split of three ranks on this mesh
+    assert widths[-1][0] + widths[-1][1] == ncols
+    nvec = 3
+    rng = np.random.default_rng(21)
+    spec = rng.standard_normal((nvec, nx, ncols)) + 1j * rng.standard_normal((nvec, nx, ncols))
+    G2 = oracle.get_coulG(a, mesh).reshape(mesh)[:, :, :mesh[2] // 2 + 1].reshape(nx, ncols)
+    wz = np.full(mesh[2] // 2 + 1, 2.0); wz[0] = 1.0
+    if mesh[2] % 2 == 0:
+        wz[-1] = 1.0
+    wgt = np.sqrt(G2 * np.tile(wz, mesh[1])[None, :])
+    ref = np.fft.fft(spec, axis=1) * wgt[None]
+    errs, outs = [], [None] * 3
+    start = threading.Barrier(3)
+
+    def work(r):
+        try:
+            c0, ncl = widths[r]
+            with torch.cuda.stream(torch.cuda.Stream()):
+                h2 = Handle(0)                                        # bound to this thread's stream
+                src = torch.from_numpy(np.ascontiguousarray(spec[:, :, c0:c0 + ncl])).to(h2.torch_device)
+                start.wait()
+                for it in range(200):
+                    Y = src.clone()
+                    h2.fft_x_coulomb(Y, nx * ncl, nvec, mesh, a, c0, ncl)
+                torch.cuda.current_stream().synchronize()
+                outs[r] = Y.cpu().numpy()
+        except Exception as e:            # noqa: BLE001
+            errs.append(e)
+            start.abort()
+
+    ths = [threading.Thread(target=work, args=(r,)) for r in range(3)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join(timeout=300)
+    if errs:
+        raise errs[0]
+    for r, (c0, ncl) in enumerate(widths):
+        got, want = outs[r], ref[:, :, c0:c0 + ncl]
+        nz = abs(want) > 0
+        assert abs(got - want)[nz].max() < 1e-10 * abs(want).max(), r

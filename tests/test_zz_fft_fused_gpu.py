@@ -7,7 +7,7 @@ the kernels that call them.  First run on a B200 at the end of round 1: all pass
 import os
 import numpy as np
 import pytest
-import test_stages_gpu as stages
+import test_g1_stages_gpu as stages
 
 pytestmark = pytest.mark.gpu
 

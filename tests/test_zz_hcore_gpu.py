@@ -60,7 +60,7 @@ def test_get_pp_without_projectors_is_complete():
 def test_sharded_local_potential():
     """Grid sharded over 3 ranks (threads on one GPU): slab contractions summed."""
     import threading
-    from test_dist_gpu import ThreadComm
+    from test_zzy_dist_gpu import ThreadComm
     cell = diamond_c8([13, 10, 12], basis='gth-szv', jitter=0.2)
     vpp0, _ = _ref(cell)
     n = 3

@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 from oracle import c_oracle
 from util import diamond_c8, oracle_phi
-from test_stages_gpu import _select
+from test_g1_stages_gpu import _select
 
 pytestmark = [pytest.mark.gpu,
               pytest.mark.skipif(os.environ.get('ISDF_TEST_EXPERIMENTAL') != '1',

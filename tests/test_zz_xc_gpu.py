@@ -80,7 +80,7 @@ def test_nr_rks_errors():
 def test_nr_rks_sharded_grid():
     """Grid sharded over 3 ranks (threads on one GPU): slab results summed."""
     import threading
-    from test_dist_gpu import ThreadComm
+    from test_zzy_dist_gpu import ThreadComm
     cell = diamond_c8([13, 10, 12], basis='gth-szv', jitter=0.2)
     dm = rand_dm(cell.nao) * 0.1
     ao4 = _oracle_ao4(cell)

@@ -2,7 +2,7 @@
 # Last GPU seconds of round 1: the opt-in kernel forms written after the main GPU sessions -- tests, then one
 # exploratory C64 bench line each (1 warm-up + 1 step: for comparing stage times, not a reportable number).
 # Kept as the record of what ran (profiles/r01_optin_forms.md); tests/test_zz_syrk_crt_gpu.py was folded into
-# tests/test_syrk_i8_gpu.py afterwards, when the residue form became the default.
+# tests/test_g2_syrk_i8_gpu.py afterwards, when the residue form became the default.
 mkdir -p gpurun_out
 B="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e"
 ISDF_TEST_EXPERIMENTAL=1 timeout 50 python -m pytest tests/test_zz_fft_fused_gpu.py tests/test_zz_syrk_crt_gpu.py -m gpu -q -rf -p no:cacheprovider > gpurun_out/r1_tail_tests1.log 2>&1; echo "tests fft-fused+crt rc=$?"; tail -4 gpurun_out/r1_tail_tests1.log

@@ -12,7 +12,7 @@ ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_fft_fused_gp
 ISDF_TEST_EXPERIMENTAL=1 timeout 600 python -m pytest tests/test_zz_xc_gpu.py tests/test_zz_scf_gpu.py -m gpu -q > gpurun_out/pytest_xc.log 2>&1; echo "xc rc=$?"; tail -15 gpurun_out/pytest_xc.log
 # memory checker on the small experimental tests (slow: only these files)
 ISDF_TEST_EXPERIMENTAL=1 timeout 900 compute-sanitizer --tool memcheck --error-exitcode 9 python -m pytest \
-    tests/test_zz_panel_forms_gpu.py tests/test_syrk_i8_gpu.py tests/test_zz_xc_gpu.py -m gpu -q -x -k "bit_exact or 200-300 or 128-128 or he_c or lda" \
+    tests/test_zz_panel_forms_gpu.py tests/test_g2_syrk_i8_gpu.py tests/test_zz_xc_gpu.py -m gpu -q -x -k "bit_exact or 200-300 or 128-128 or he_c or lda" \
     > gpurun_out/sanitizer.log 2>&1; echo "sanitizer rc=$?"; grep -E "ERROR SUMMARY|passed|failed" gpurun_out/sanitizer.log | tail -5
 for mode in 0 1 2; do
   ISDF_PANEL_CLUSTER=$mode ISDF_PROFILE_SELECT=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
@@ -58,7 +58,7 @@ except Exception as e:
     print('xc: no line', e)
 PY
 # two-stream form of the residue product (ISDF_SYRK_OVERLAP=1): bit-identity test, then a C64 line
-ISDF_TEST_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_syrk_i8_gpu.py -m gpu -q -k overlapped > gpurun_out/pytest_overlap.log 2>&1; echo "overlap rc=$?"; tail -5 gpurun_out/pytest_overlap.log
+ISDF_TEST_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_g2_syrk_i8_gpu.py -m gpu -q -k overlapped > gpurun_out/pytest_overlap.log 2>&1; echo "overlap rc=$?"; tail -5 gpurun_out/pytest_overlap.log
 ISDF_SYRK_OVERLAP=1 timeout 600 python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e \
     > gpurun_out/bench_overlap.json 2> gpurun_out/bench_overlap.err; echo "bench overlap rc=$?"
 python - <<PY
