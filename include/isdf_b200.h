@@ -239,6 +239,21 @@ int isdf_get_jk_block(isdf_handle* h, const double* X, const double* Wrows, long
                       int with_j, int with_k, double* vj, double* vk,
                       void* ws, size_t ws_bytes);
 
+/* isdf_get_jk for callers that cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments and result as isdf_get_jk without the workspace: the
+ * scratch is a fixed device array inside the library (isdf_get_jk_static_max_bytes() = 32 MiB per
+ * GPU that loads the library, held until exit), and the call makes no cudaMalloc / cudaFree /
+ * allocating library call.  Sizes with isdf_get_jk_ws_bytes(nao, np) above that maximum are
+ * rejected with ISDF_ERR_WS (-3) and a message naming both numbers.  The handle's device must be
+ * current.  All calls on one device share the array: calls that overlap on the GPU race, so
+ * serialise them (one stream, or events between streams).  It keeps the last call's contents;
+ * nothing in it needs clearing, every part is rewritten before it is read. */
+size_t isdf_get_jk_static_max_bytes(void);
+int isdf_get_jk_static(isdf_handle* h, const double* X, const double* W,
+                       const double* dm, int nset, int nao, int np,
+                       int with_j, int with_k, double* vj, double* vk);
+
 /* Generic FP64 GEMM used by every stage (exposed for tests / bench):
  * C[m,n] = epi( Cin[m,n] -/+ sum_k opA(k,m) opB(k,n) ), one FMA chain per
  * element in ascending k.  a_kmajor: A[k*lda+m] else A[m*lda+k]; same for B.

@@ -78,6 +78,8 @@ SIGNATURES = {
     'isdf_get_jk_ws_bytes': (c_sz, [c_int, c_int]),
     'isdf_get_jk': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int,
                             c_vp, c_vp, c_vp, c_sz]),
+    'isdf_get_jk_static_max_bytes': (c_sz, []),
+    'isdf_get_jk_static': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
                            c_vp, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_int, c_int]),
     'isdf_set_gemm_tile': (c_int, [c_vp, c_int]),
@@ -335,6 +337,13 @@ class Handle:
                                    c_vp(vj.data_ptr()) if vj is not None else None,
                                    c_vp(vk.data_ptr()) if vk is not None else None,
                                    c_vp(ws.data_ptr()), ws.numel()))
+
+    def get_jk_static(self, X, W, dm, nset, nao, npts, with_j, with_k, vj, vk):
+        """isdf_get_jk with the library's built-in scratch array: allocates nothing (include/isdf_b200.h)."""
+        check(self.lib.isdf_get_jk_static(self.h, c_vp(X.data_ptr()), c_vp(W.data_ptr()), c_vp(dm.data_ptr()),
+                                          nset, nao, npts, int(with_j), int(with_k),
+                                          c_vp(vj.data_ptr()) if vj is not None else None,
+                                          c_vp(vk.data_ptr()) if vk is not None else None))
 
     def dgemm(self, M, N, K, A, lda, a_kmajor, B, ldb, b_kmajor, C, ldc,
               Cin=None, ldcin=0, E=None, lde=0, alpha=1.0, neg=0, epi=0, upper_only=0):

@@ -124,6 +124,62 @@ extern "C" int isdf_get_jk(isdf_handle* h, const double* X, const double* W,
     return isdf_get_jk_block(h, X, W, np, 0, np, dm, nset, nao, np, with_j, with_k, vj, vk, ws, ws_bytes);
 }
 
+// ---- J/K for callers that must not allocate ------------------------------------------------------
+// Same contraction as isdf_get_jk, with its scratch in a fixed file-scope device array instead of a
+// caller workspace: no cudaMalloc / cudaFree / allocating library routine anywhere on this path (for
+// code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  The array
+// exists once per GPU that loads the library and is held until the process exits.  Every call on a
+// device shares it: calls that overlap on the GPU (two streams, two handles of one device) race.
+// It keeps the previous call's contents; nothing in it has to start at zero, because every buffer
+// carved from it (T, Ub, Vb, Nm, rho, v) is written in full by the kernels of a call before it is read.
+#define ISDF_JK_STATIC_SCRATCH_BYTES (32u << 20)
+static __device__ __align__(256) unsigned char g_jk_scratch[ISDF_JK_STATIC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int JK_MAX_DEVICES = 64;
+void* g_jk_scratch_ptr[JK_MAX_DEVICES];      // device address of g_jk_scratch per device, set under the set-up lock
+
+// In host code `g_jk_scratch` is only a stand-in for the symbol: the device address comes from the runtime,
+// once per device, with that device current.
+int resolve_jk_scratch(void* arg)
+{
+    const int dev = *(const int*)arg;
+    void* ptr = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress((void**)&ptr, g_jk_scratch));
+    if (ptr == nullptr) { isdf_set_error("cudaGetSymbolAddress returned a null scratch address on device %d", dev); return ISDF_ERR_CUDA; }
+    g_jk_scratch_ptr[dev] = ptr;
+    return ISDF_OK;
+}
+
+}  // namespace
+
+extern "C" size_t isdf_get_jk_static_max_bytes(void) { return (size_t)ISDF_JK_STATIC_SCRATCH_BYTES; }
+
+extern "C" int isdf_get_jk_static(isdf_handle* h, const double* X, const double* W,
+                                  const double* dm, int nset, int nao, int np,
+                                  int with_j, int with_k, double* vj, double* vk)
+{
+    ARG_CHECK(h && nao > 0 && np > 0);
+    const size_t need = isdf_get_jk_ws_bytes(nao, np);
+    if (need > (size_t)ISDF_JK_STATIC_SCRATCH_BYTES) {
+        isdf_set_error("isdf_get_jk_static: nao=%d np=%d needs %zu bytes of scratch, the built-in array holds %zu; "
+                       "use isdf_get_jk with a caller workspace", nao, np, need, (size_t)ISDF_JK_STATIC_SCRATCH_BYTES);
+        return ISDF_ERR_WS;
+    }
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev != h->device || dev < 0 || dev >= JK_MAX_DEVICES) {
+        isdf_set_error("isdf_get_jk_static: current device %d is not the handle's device %d", dev, h->device);
+        return ISDF_ERR_ARG;
+    }
+    static const char key = 0;
+    int rc;
+    if ((rc = isdf_once_per_device(&key, resolve_jk_scratch, &dev))) return rc;
+    return isdf_get_jk_block(h, X, W, np, 0, np, dm, nset, nao, np, with_j, with_k, vj, vk,
+                             g_jk_scratch_ptr[dev], (size_t)ISDF_JK_STATIC_SCRATCH_BYTES);
+}
+
 // ---- exact-density J on the FFT grid (the FFTDF route, pyscf/pbc/df/fft_jk.py:33-109) ----------
 // rho_g = sum_{mu nu} phi[mu,g] D[mu,nu] phi[nu,g] on a slab of grid points;
 // the caller solves vR = ifft(coulG * fft(rho)).real (isdf_coulomb_apply on the whole grid) and
