@@ -91,6 +91,7 @@ class ISDF:
         self._part = None
         self._slab = None
         self._aoR4 = None          # AO values + gradients of nr_rks
+        self._pinned = None        # pinned host staging buffers of get_jk
         return self
 
     def release_buffers(self):
@@ -214,15 +215,16 @@ class ISDF:
         available here, and for GTH bases the grid quadrature is exact to the
         mesh's precision.)"""
         if self._ovlp is None:
-            if self.aoR is None:
-                raise RuntimeError('overlap needs the AO matrix: build with keep_aoR=True')
             h = self.handle
-            nao = self.aoR.shape[0]
+            # the build's AO matrix when it was kept; otherwise (keep_aoR=False, or after load())
+            # stage 1 is evaluated again for this one product
+            phi, ld = self._ao_on_grid()
+            nao = phi.shape[0]
             ng = int(np.prod(self.mesh))
             S = h.empty((nao, nao))
             # with a sharded grid every rank sums its slab, then the partial overlaps are added
             g0, g1 = self._slab if self._slab is not None else (0, ng)
-            h.dgemm(nao, nao, g1 - g0, self.aoR, self._ld, 0, self.aoR, self._ld, 0, S, nao,
+            h.dgemm(nao, nao, g1 - g0, phi, ld, 0, phi, ld, 0, S, nao,
                     alpha=self.cell.vol / ng)
             if self.comm is not None:
                 self.comm.all_reduce_sum(S)
@@ -256,16 +258,51 @@ class ISDF:
             if abs(dm0.imag).max() > 1e-12:
                 raise NotImplementedError('complex density matrices (Gamma point only)')
             dm0 = dm0.real
-        dms = np.ascontiguousarray(dm0.reshape(-1, nao, nao), dtype=np.float64)   # df_jk.py:1411-1416
+        dms = dm0.reshape(-1, nao, nao)                                           # df_jk.py:1411-1416
         nset = dms.shape[0]
+        t0 = (time.process_time(), time.perf_counter())
 
-        d_dm = torch.from_numpy(dms).pin_memory().to(h.torch_device, non_blocking=True)
-        vj, vk = self.get_jk_device(d_dm, with_j, with_k, exxdiv)
-        out_j = vj.cpu().numpy().reshape(dm0.shape) if with_j else None
-        out_k = vk.cpu().numpy().reshape(dm0.shape) if with_k else None
+        # pinned staging buffers live with the object: one host->device copy in, one device->host copy out
+        stage = self._pinned
+        if stage is None or stage[0].shape[0] < nset or stage[0].shape[1] != nao:
+            stage = self._pinned = (torch.empty((nset, nao, nao), dtype=torch.float64).pin_memory(),
+                                    torch.empty((2, nset, nao, nao), dtype=torch.float64).pin_memory())
+        h_in, h_out = stage[0][:nset], stage[1][:, :nset]
+        h_in.numpy()[...] = dms                                                   # casts integer DMs to float64
+        d_dm = h_in.to(h.torch_device, non_blocking=True)
+        self.h2d_bytes = h_in.numel() * 8
+        vj, vk = self.get_jk_device(d_dm, with_j, with_k, exxdiv, mo=self._mo_tags(dm, dm0, nset, nao))
+        self.d2h_bytes = 0
+        if with_j:
+            h_out[0].copy_(vj, non_blocking=True)
+            self.d2h_bytes += vj.numel() * 8
+        if with_k:
+            h_out[1].copy_(vk, non_blocking=True)
+            self.d2h_bytes += vk.numel() * 8
+        torch.cuda.current_stream(h.torch_device).synchronize()
+        out_j = h_out[0].numpy().reshape(dm0.shape).copy() if with_j else None
+        out_k = h_out[1].numpy().reshape(dm0.shape).copy() if with_k else None
+        self._timer('vj and vk', t0)
         return out_j, out_k
 
-    def get_jk_device(self, d_dm, with_j=True, with_k=True, exxdiv=None):
+    @staticmethod
+    def _mo_tags(dm, dm0, nset, nao):
+        """(mo_coeff, mo_occ) carried by a tagged density matrix (pyscf/lib/numpy_helper.py tag_array; read by
+        the reference's K build at pyscf/pbc/df/fft_jk.py:206-210): real orbitals with non-negative occupations
+        of a single Gamma-point density matrix, else None."""
+        mo_coeff, mo_occ = getattr(dm, 'mo_coeff', None), getattr(dm, 'mo_occ', None)
+        if mo_coeff is None or mo_occ is None or nset != 1:
+            return None
+        C, occ = np.asarray(mo_coeff), np.asarray(mo_occ)
+        if C.ndim == 3 and C.shape[0] == 1:
+            C, occ = C[0], occ.reshape(1, -1)[0]
+        if C.ndim != 2 or C.shape[0] != nao or occ.shape != (C.shape[1],) or np.iscomplexobj(C):
+            return None
+        if (occ < 0).any():
+            return None
+        return C, occ
+
+    def get_jk_device(self, d_dm, with_j=True, with_k=True, exxdiv=None, mo=None):
         """Stage 5 on a device-resident density matrix [nset, nao, nao]; returns
         device tensors (no host copies; asynchronous on the handle's stream)."""
         if self.W is None:
@@ -306,25 +343,23 @@ class ISDF:
         Poisson problem on the whole grid and contracts its slab; J is summed over ranks."""
         if self.W is None:
             self.build()
-        if self.aoR is None:
-            raise RuntimeError('exact J needs the AO matrix on the grid: build with keep_aoR=True')
         h = self.handle
-        nao = self.aoR.shape[0]
+        aoR, ld = self._ao_on_grid()
+        nao = aoR.shape[0]
         nset = d_dm.shape[0]
         ng = int(np.prod(self.mesh))
         g0, g1 = self._slab if self._slab is not None else (0, ng)
         ngl = g1 - g0
-        ld = self._ld
         ws = h.workspace(h.lib.isdf_grid_j_ws_bytes(nao, ld))
         ngp = _lib.pad8(ng)
         rho = h.zeros((nset, ngp))
-        h.density_on_grid(self.aoR, ld, nao, ngl, d_dm, nset, rho[:, g0:], ngp, ws=ws)
+        h.density_on_grid(aoR, ld, nao, ngl, d_dm, nset, rho[:, g0:], ngp, ws=ws)
         if self.comm is not None and self.comm.size > 1:
             self.comm.all_reduce_sum(rho)           # slabs are disjoint: the sum is the gather
         vR = h.empty((nset, ngp))
         h.coulomb_apply(rho, ngp, nset, self.mesh, self.cell.lattice_vectors(), vR, ngp)
         vj = h.empty((nset, nao, nao))
-        h.j_from_potential(self.aoR, ld, nao, ngl, vR[:, g0:], ngp, nset, self.cell.vol / ng, vj, ws=ws)
+        h.j_from_potential(aoR, ld, nao, ngl, vR[:, g0:], ngp, nset, self.cell.vol / ng, vj, ws=ws)
         if self.comm is not None and self.comm.size > 1:
             self.comm.all_reduce_sum(vj)
         return vj
@@ -335,22 +370,26 @@ class ISDF:
             raise NotImplementedError('ISDF is Gamma-point only')
 
     def _ao_on_grid(self):
-        """AO values of this rank's grid slab: the build's copy when it was kept, else stage 1 alone."""
+        """AO values of this rank's grid slab: the build's copy when it was kept, else stage 1 alone
+        (keep_aoR=False, or an object restored by load())."""
         if self.aoR is not None:
             return self.aoR, self._ld
         h = self.handle
         cell = self.cell
-        if self.comm is not None and self.comm.size > 1:
-            raise RuntimeError('the AO matrix was not kept (keep_aoR=False) on a sharded grid')
         ng = int(np.prod(self.mesh))
-        ld = _lib.pad8(ng)
+        if self.comm is not None and self.comm.size > 1 and self._slab is None:
+            raise RuntimeError('the grid slabs are assigned by build() or load() on a sharded grid')
+        g0, g1 = self._slab if self._slab is not None else (0, ng)
+        ld = _lib.pad8(g1 - g0)
         rcut, Ls = cell.ao_eval_params()
         phi = h.empty((cell.nao_nr(), ld))
-        if ld > ng:
-            phi[:, ng:].zero_()
+        if ld > g1 - g0:
+            phi[:, g1 - g0:].zero_()
         h.eval_ao(cell._atm, cell._bas, cell._env,
                   np.ascontiguousarray(cell.lattice_vectors(), dtype=np.float64),
-                  np.asarray(cell.mesh, dtype=np.int32), Ls, rcut, 0, ng, phi, ld)
+                  np.asarray(cell.mesh, dtype=np.int32), Ls, rcut, g0, g1, phi, ld)
+        if self.keep_aoR:                       # e.g. after load(): evaluated once, then kept like build() does
+            self.aoR, self._ld = phi, ld
         return phi, ld
 
     def potential_matrix_device(self, vR):
@@ -501,24 +540,127 @@ class ISDF:
     def get_k(self, dm, hermi=1, kpts=None, kpts_band=None, omega=None, exxdiv=None):
         return self.get_jk(dm, hermi, kpts, kpts_band, False, True, omega, exxdiv)[1]
 
+    # -- the rest of FFTDF's surface (pyscf/pbc/df/fft.py:246-272, :317-359): not part of the J/K hot path.
+    # Named here so that a caller reaching them through `mf.with_df` gets the reason, not an AttributeError
+    # (pyscf/pbc/scf/hf.py:676-679 calls get_ao_eri whenever `_is_mem_enough()` was not patched by update_mf).
+    def _unsupported(self, name, why):
+        raise NotImplementedError('ISDF.%s: %s' % (name, why))
+
+    def get_ao_eri(self, *args, **kwargs):
+        self._unsupported('get_ao_eri', 'the 4-index integrals are never formed; J/K come from get_jk '
+                          '(attach with ISDF.update_mf(mf) so that SCF does not take its in-core ERI shortcut)')
+
+    get_eri = get_ao_eri
+
+    def get_mo_eri(self, *args, **kwargs):
+        self._unsupported('get_mo_eri', 'integral transformation is outside the ISDF J/K path')
+
+    ao2mo = get_mo_eri
+
+    def ao2mo_7d(self, *args, **kwargs):
+        self._unsupported('ao2mo_7d', 'integral transformation is outside the ISDF J/K path')
+
+    def get_ao_pairs_G(self, *args, **kwargs):
+        self._unsupported('get_ao_pairs_G', 'pair densities are replaced by the interpolation (aoR_ip, W)')
+
+    get_ao_pairs = get_ao_pairs_G
+
+    def get_mo_pairs_G(self, *args, **kwargs):
+        self._unsupported('get_mo_pairs_G', 'pair densities are replaced by the interpolation (aoR_ip, W)')
+
+    get_mo_pairs = get_mo_pairs_G
+
+    def aoR_loop(self, grids=None, kpts=None, deriv=0):
+        self._unsupported('aoR_loop', 'the AO values stay on the device (ISDF.aoR, [nao, grid]); use aoR_host()')
+
+    def loop(self, blksize=None):
+        self._unsupported('loop', 'no 3-index tensor exists in ISDF')
+
+    def range_coulomb(self, omega):
+        self._unsupported('range_coulomb', 'range-separated Coulomb (omega) is not supported')
+
+    def get_jk_e1(self, *args, **kwargs):
+        self._unsupported('get_jk_e1', 'nuclear gradients are outside the ISDF J/K path')
+
+    get_j_e1 = get_k_e1 = get_jk_e1
+
+    def get_naoaux(self):
+        """Number of auxiliary functions = interpolation points (FFTDF returns 2 ngrids, fft.py:350-353)."""
+        if self.n_ip:
+            return int(self.n_ip)
+        return min(int(self.c * self.cell.nao_nr()), int(np.prod(self.mesh)))
+
+    @property
+    def grids(self):
+        self._unsupported('grids', 'the uniform grid is generated on the device from the mesh; coordinates: cell.get_uniform_grids()')
+
+    @property
+    def _numint(self):
+        return self.numint()
+
+    def _timer(self, msg, t0):
+        """The reference's `logger.timer` line (pyscf/lib/logger.py:167-180; call sites
+        pyscf/pbc/scf/hf.py:666,697, pyscf/pbc/df/fft_jk.py:249,292), printed at verbose >= 5 (DEBUG)."""
+        t1 = (time.process_time(), time.perf_counter())
+        if self.verbose >= 5:
+            self.stdout.write('    CPU time for %s %9.2f sec, wall time %9.2f sec\n' % (msg, t1[0] - t0[0], t1[1] - t0[1]))
+        return t1
+
     # -- persistence ("next" row 3 of SURVEY 8f) ---------------------------------------------
+    @staticmethod
+    def _shard_path(path, rank, size):
+        path = str(path)
+        base = path[:-4] if path.endswith('.npz') else path
+        return path if size == 1 else '%s.r%dof%d.npz' % (base, rank, size)
+
     def save(self, path):
-        if self.comm is not None and self.comm.size > 1:
-            raise NotImplementedError('save() of a sharded ISDF object (W is distributed over ranks)')
-        np.savez(path, ip_index=self.ip_index, ip_resid=self.ip_resid,
+        """Interpolation points, X = Phi[:, ip], the overlap (when it has been formed) and W.  With several
+        ranks every rank writes its own file `<path>.r<rank>of<size>.npz` holding its row block of W
+        (the role of the reference's `_cderi` cache, examples/pbc/11-gamma_point_all_electron_scf.py:66-75)."""
+        if self.W is None:
+            raise RuntimeError('nothing to save: build() first')
+        rank, size = (self.comm.rank, self.comm.size) if self.comm is not None else (0, 1)
+        p0 = int(self._part.ip_off[rank]) if (size > 1 and self._part is not None) else 0
+        extra = {}
+        if self._ovlp is not None:
+            extra['ovlp'] = self._ovlp.cpu().numpy()
+        np.savez(self._shard_path(path, rank, size), ip_index=self.ip_index, ip_resid=self.ip_resid,
                  W=self.W.cpu().numpy(), aoR_ip=self.aoR_ip.cpu().numpy(),
-                 mesh=np.asarray(self.mesh), n_ip=self.n_ip)
+                 mesh=np.asarray(self.mesh), n_ip=self.n_ip, nao=self.cell.nao_nr(),
+                 rank=rank, size=size, p0=p0, **extra)
 
     def load(self, path):
+        """Restore what save() wrote.  The AO matrix on the grid is not stored: the pieces that need it
+        (overlap for exxdiv='ewald' when it was not saved, exact_j, get_pp, nr_rks) evaluate stage 1 again."""
         import torch
-        z = np.load(path)
+        from .dist import SlabPartition
+        rank, size = (self.comm.rank, self.comm.size) if self.comm is not None else (0, 1)
+        z = np.load(self._shard_path(path, rank, size))
         if not np.array_equal(z['mesh'], np.asarray(self.mesh)):
             raise ValueError('mesh of the saved ISDF object does not match the cell')
+        nao = self.cell.nao_nr()
+        npts = int(z['n_ip'])
+        if z['aoR_ip'].shape != (nao, npts):
+            raise ValueError('saved ISDF object has %d AOs x %d points; the cell has %d AOs'
+                             % (z['aoR_ip'].shape + (nao,)))
+        fsize = int(z['size']) if 'size' in z.files else 1
+        frank = int(z['rank']) if 'rank' in z.files else 0
+        if (frank, fsize) != (rank, size):
+            raise ValueError('file was written by rank %d of %d, this is rank %d of %d' % (frank, fsize, rank, size))
+        part = SlabPartition(self.mesh, size, npts)
+        p0, p1 = int(part.ip_off[rank]), int(part.ip_off[rank + 1])
+        if z['W'].shape != (p1 - p0, npts) or len(z['ip_index']) != npts:
+            raise ValueError('saved W has shape %s, expected %s' % (z['W'].shape, (p1 - p0, npts)))
+        self.reset()
         h = self.handle
-        self.ip_index, self.ip_resid, self.n_ip = z['ip_index'], z['ip_resid'], int(z['n_ip'])
+        self.ip_index, self.ip_resid, self.n_ip = z['ip_index'], z['ip_resid'], npts
         self.W = torch.from_numpy(z['W']).to(h.torch_device)
         self.aoR_ip = torch.from_numpy(z['aoR_ip']).to(h.torch_device)
-        self._jk_ws = None
+        if 'ovlp' in z.files:
+            self._ovlp = torch.from_numpy(z['ovlp']).to(h.torch_device)
+        if size > 1:
+            self._part = part
+            self._slab = part.grid_range(rank)
         return self
 
 

@@ -255,7 +255,10 @@ def test_three_threads_launch_x_passes_of_different_widths(handle):
     nvec = 3
     rng = np.random.default_rng(21)
     spec = rng.standard_normal((nvec, nx, ncols)) + 1j * rng.standard_normal((nvec, nx, ncols))
-    G2 = oracle.get_coulG(a, mesh).reshape(mesh)[:, :, :mesh[2] // 2 + 1].reshape(nx, ncols)
+    # the kernel's weight at a Nyquist index is the mean of coulG(G) and coulG(-G) (same quadratic form on real fields)
+    G2f = oracle.get_coulG(a, mesh).reshape(mesh)
+    G2m = G2f[(-np.arange(mesh[0])) % mesh[0]][:, (-np.arange(mesh[1])) % mesh[1]][:, :, (-np.arange(mesh[2])) % mesh[2]]
+    G2 = (0.5 * (G2f + G2m))[:, :, :mesh[2] // 2 + 1].reshape(nx, ncols)
     wz = np.full(mesh[2] // 2 + 1, 2.0); wz[0] = 1.0
     if mesh[2] % 2 == 0:
         wz[-1] = 1.0
