@@ -15,6 +15,7 @@ def lib():
         _lib = ctypes.CDLL(_PATH)
         _lib.oracle_select_ip.restype = ctypes.c_long
         _lib.oracle_select_ip_exact.restype = ctypes.c_long
+        _lib.oracle_select_ip_blocked.restype = ctypes.c_long
         _lib.oracle_recon_parts.restype = ctypes.c_double
     return _lib
 
@@ -33,6 +34,22 @@ def select_ip_chain(aoR, npts, tol=-1.0, return_factor=False):
     rank = lib().oracle_select_ip(_p(aoR), ctypes.c_int(nao), ctypes.c_long(ng), ctypes.c_long(ng),
                                   ctypes.c_int(npts), ctypes.c_double(tol), _p(Lt), ctypes.c_long(ng),
                                   _p(ip), _p(resid))
+    if return_factor:
+        return ip[:rank].copy(), resid[:rank].copy(), Lt[:rank]
+    return ip[:rank].copy(), resid[:rank].copy()
+
+
+def select_ip_blocked(aoR, npts, tol=-1.0, return_factor=False):
+    """The same selection as select_ip_chain, bit for bit (tests/test_oracle_blocked_cpu.py), evaluated in
+    panels with OpenMP threads (oracle/c/isdf_oracle_blocked.c): the form that finishes at the BASELINE sizes."""
+    aoR = np.ascontiguousarray(aoR, dtype=np.float64)
+    nao, ng = aoR.shape
+    Lt = np.zeros((npts, ng))
+    ip = np.zeros(npts, dtype=np.int64)
+    resid = np.zeros(npts)
+    rank = lib().oracle_select_ip_blocked(_p(aoR), ctypes.c_int(nao), ctypes.c_long(ng), ctypes.c_long(ng),
+                                          ctypes.c_int(npts), ctypes.c_double(tol), _p(Lt), ctypes.c_long(ng),
+                                          _p(ip), _p(resid))
     if return_factor:
         return ip[:rank].copy(), resid[:rank].copy(), Lt[:rank]
     return ip[:rank].copy(), resid[:rank].copy()
