@@ -43,6 +43,11 @@ def parse_args():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--jk-reps', type=int, default=5)
     ap.add_argument('--no-e2e', action='store_true', help='exploratory runs only: skip the host-API leg')
+    ap.add_argument('--no-parity', action='store_true', help='skip the C8-vs-oracle parity block (N = 1 only)')
+    ap.add_argument('--no-extra', action='store_true',
+                    help='skip the one-off runs of the larger configs (h2o32 at >= 4 GPUs, si216 at 8 GPUs)')
+    ap.add_argument('--exxdiv', default='ewald', choices=['ewald', 'none'],
+                    help="exchange divergence treatment of the timed J/K: 'ewald' is the pbc.scf.RHF default")
     ap.add_argument('--xc', default=None,
                     help="also time ISDF.nr_rks(XC, dm) per SCF iteration ('pbe' for BASELINE configs[1]); reported "
                          "beside the headline under 'xc', never part of 'value'")
@@ -106,6 +111,54 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------- CPU arm
+_POOL_LIMIT = None
+
+
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1 when it starts more than one process per node, and NumPy's BLAS
+    reads that at import: lift the BLAS / OpenMP pools back to every host core for the CPU legs."""
+    global _POOL_LIMIT
+    ncores = os.cpu_count() or 1
+    try:
+        import threadpoolctl
+        _POOL_LIMIT = threadpoolctl.threadpool_limits(limits=ncores)      # kept alive for the whole run
+    except Exception:                                                     # noqa: BLE001
+        pass
+    os.environ['OMP_NUM_THREADS'] = str(ncores)                           # for libgomp (the C oracle) if not yet loaded
+    try:
+        import ctypes
+        ctypes.CDLL('libgomp.so.1').omp_set_num_threads(ncores)
+    except OSError:
+        pass
+    return ncores
+
+
+def cpu_blocked_select_seconds(phi_slab, npts, ng, nb=128):
+    """Seconds of the PANEL-BLOCKED selection on the host BLAS (the algorithm of csrc/select.cu and
+    oracle/c/isdf_oracle_blocked.c: per panel of 128 pivots one pair-density GEMM and one flush GEMM that streams
+    the finished factor columns once), measured on a slab of grid points and scaled to the grid: the two
+    GEMMs of a panel at k0 = Np/8, 3Np/8, 5Np/8, 7Np/8 (cost affine in k0: the midpoint rule is exact),
+    best of 3 each.  The sequential pivot search on the candidates is not included (<2 % of the flops)."""
+    import scipy.linalg.blas as blas
+    nao, ngs = phi_slab.shape
+    rng = np.random.default_rng(3)
+    Lt = np.asfortranarray(rng.standard_normal((ngs, npts)) * 1e-3)      # [grid, column]: dgemm reads it as is
+    per_panel = []
+    for frac in (1, 3, 5, 7):
+        k0 = max(nb, npts * frac // 8)
+        P = np.asfortranarray(rng.standard_normal((k0, nb)))
+        X = np.asfortranarray(rng.standard_normal((nao, nb)))
+        best = 1e30
+        for _ in range(3):
+            t0 = time.perf_counter()
+            G = blas.dgemm(1.0, phi_slab, X, trans_a=True)                # pair densities [ngs, nb]
+            G *= G
+            blas.dgemm(-1.0, Lt[:, :k0], P, beta=1.0, c=G, overwrite_c=True)   # flush
+            best = min(best, time.perf_counter() - t0)
+        per_panel.append(best)
+    return float(np.mean(per_panel)) * (npts / nb) * (ng / ngs)
+
+
 def cpu_sample_target(cell, npts, seed=5):
     """One bounded sample of the CPU port on the TARGET workload itself (its cell, nao, mesh, Np):
     every stage of the NumPy/SciPy oracle is run on a slab of that workload's own arrays and the
@@ -172,8 +225,10 @@ def cpu_sample_target(cell, npts, seed=5):
         t_half = one_step(phi_half, Lt_half, d_half, k)
         slope = max(t_full - t_half, 0.0) / (ngsel - half)
         per_pivot.append(t_full + slope * (ng - ngsel))
-    t['select'] = float(np.mean(per_pivot)) * npts
+    t['select_unblocked'] = float(np.mean(per_pivot)) * npts
     del Lt, Lt_half, phi_sel, phi_half
+    # the same selection panel-blocked on the host BLAS: this is the figure the CPU total uses
+    t['select'] = cpu_blocked_select_seconds(np.ascontiguousarray(np.tile(phi_s, (1, 4))), npts, ng)
     # stage 3 (the oracle's route: Cholesky of A, two triangular solves)
     ipx = rng.integers(ngs, size=npts)
     X = np.ascontiguousarray(phi_s[:, ipx])
@@ -211,8 +266,9 @@ def cpu_sample_target(cell, npts, seed=5):
     t0 = time.perf_counter()
     oracle.isdf_get_jk(X, W, dm)
     t['jk'] = time.perf_counter() - t0
-    desc = ('NumPy/SciPy oracle on slabs of the workload itself: AO on ng/64 (%d points), pivot steps (best of 7) '
-            'at k=Np/8..7Np/8 on ng/16 (%d points) and ng/32 (slope in the grid size extended to ng), full A=(X^T X)^2 + Cholesky (Np=%d), triangular solves '
+    desc = ('NumPy/SciPy oracle on slabs of the workload itself: AO on ng/64 (%d points), selection = panel-blocked form on the host BLAS '
+            '(pair-density + flush dgemm of a 128-pivot panel at k0=Np/8..7Np/8 on ng/16 = %d points, scaled); the unblocked GEMV loop is '
+            'timed beside it (select_unblocked, not part of the total), full A=(X^T X)^2 + Cholesky (Np=%d), triangular solves '
             'and metric product on ng/256 (%d points), FFT+coulG+iFFT of %d aux functions, one full J/K; '
             'other slab times multiplied by the slab count' % (ngs, ngsel, npts, n3, nvec))
     return t, desc
@@ -229,9 +285,14 @@ def cpu_full_run(cell, npts):
     t0 = time.perf_counter()
     phi = np.ascontiguousarray(oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut).T)
     t['ao'] = time.perf_counter() - t0
+    from oracle import c_oracle
     t0 = time.perf_counter()
-    ip, resid = isdf_ref.select_ip(phi, npts)
+    ip, resid = c_oracle.select_ip_blocked(phi, npts)       # panel-blocked, OpenMP (bit-equal to the loop below)
     t['select'] = time.perf_counter() - t0
+    if float(phi.shape[1]) * npts * npts <= 2e10:           # the unblocked NumPy loop beside it while that is cheap
+        t0 = time.perf_counter()
+        isdf_ref.select_ip(phi, npts)
+        t['select_unblocked'] = time.perf_counter() - t0
     t0 = time.perf_counter()
     zeta = isdf_ref.fit_aux(phi, ip)
     t['fit'] = time.perf_counter() - t0
@@ -251,8 +312,8 @@ def cpu_full_run(cell, npts):
 def cpu_baseline_run(cell, npts):
     """(total s, build s, J/K s, per-stage s, description, cores) of one bounded CPU sample."""
     from oracle import pbc_tools
-    ncores = os.cpu_count() or 1
-    pbc_tools.FFT_WORKERS = ncores          # BLAS already uses every core; give the FFTs the same
+    ncores = use_all_host_threads()
+    pbc_tools.FFT_WORKERS = ncores          # BLAS uses every core; give the FFTs the same
     # the sample holds [Np, ng/16] and [Np, Np] arrays: above the C64 size it is taken at Np = 12480
     # and the Np-dependence of each stage's work model is applied on top (said in the description)
     nps = npts if npts <= 16384 else 12480
@@ -266,8 +327,8 @@ def cpu_baseline_run(cell, npts):
         pbc_tools.FFT_WORKERS = 1
     if nps != npts:
         r = npts / nps
-        t = {'ao': t['ao'], 'select': t['select'] * r ** 2, 'fit': t['fit'] * r ** 2, 'fft': t['fft'] * r,
-             'wgemm': t['wgemm'] * r ** 2, 'jk': t['jk'] * r ** 2}
+        power = {'ao': 0, 'fft': 1}
+        t = {k: v * r ** power.get(k, 2) for k, v in t.items()}
         desc += '; sampled at Np=%d and scaled to Np=%d by each stage\'s leading power of Np (EXTRAPOLATED in Np)' % (nps, npts)
     build = t['ao'] + t['select'] + t['fit'] + t['fft'] + t['wgemm']
     return build + t['jk'], build, t['jk'], t, desc, ncores
@@ -300,6 +361,17 @@ def run_reference(args):
         last = (desc, b, j, per)
     val = float(np.mean(tot))
     sample = last[0] + ' (%s, nao=%d Ng=%d Np=%d)' % (name, nao, ng, npts)
+    sampled = float(ng) * npts * npts > 2e11
+    check = None
+    if sampled and args.gpus == 1:
+        # error bar of the slab extrapolation: BASELINE configs[0] (C8) timed in full AND through the same
+        # sampling code; ratio = sampled estimate / measured, per stage
+        c8 = workloads.make_cell('c8')
+        n8 = int(args.c * c8.nao)
+        full, _ = cpu_full_run(c8, n8)
+        est, _ = cpu_sample_target(c8, n8)
+        check = {'workload': workloads.describe('c8'), 'measured_s': full, 'sampled_estimate_s': est,
+                 'ratio': {k: (est[k] / full[k] if full.get(k) else None) for k in est if k in full}}
     line = {
         'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 's', 'n_gpus': args.gpus,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': val * 1e3,
@@ -307,6 +379,10 @@ def run_reference(args):
         'data': 'synthetic',
         'config': {'workload': workloads.describe(name), 'c': args.c, 'nao': nao, 'ngrids': ng, 'n_ip': npts},
         'build_s': last[1], 'jk_s': last[2], 'stages_s': last[3],
+        # a step of this arm is a BOUNDED SAMPLE: for workloads above C8 `value` is the slab times scaled to the
+        # whole workload (it does not fit in this run's wall time by construction); selection enters as the
+        # panel-blocked BLAS form, the unblocked loop is listed beside it in stages_s
+        'extrapolated': sampled, 'extrapolation_check': check,
         'cpu_baseline': {'value': val, 'unit': 's', 'cores': ncores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': val, 'unit': 's', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
@@ -334,6 +410,90 @@ def measure_fp64_peak(torch, dev, n=8192, reps=10):
     return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
+def parity_block(device):
+    """BASELINE configs[0] (C8, mesh 35^3, c = 15) through the product path against the CPU oracle, outside
+    every timed region: interpolation points bit-equal to the C oracle fed the device's AO values; J/K of a
+    synthetic density matrix against the oracle's own build (Cholesky fit, NumPy FFT)."""
+    import oracle
+    from oracle import c_oracle, isdf_ref
+    from pyscf_isdf_b200 import workloads
+    from pyscf_isdf_b200.isdf import ISDF
+    cell = workloads.make_cell('c8')
+    nao = cell.nao
+    mydf = ISDF(cell, c=15, device=device).build()
+    dm = workloads.synthetic_dm(nao)
+    vj, vk = mydf.get_jk(dm, exxdiv=None)
+    aoR = mydf.aoR_host()
+    ip, resid = c_oracle.select_ip_blocked(aoR, int(15 * nao))
+    rcut, Ls = cell.ao_eval_params()
+    phi = np.ascontiguousarray(oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut).T)
+    W = isdf_ref.build_W(isdf_ref.fit_aux(phi, ip), cell.lattice_vectors(), cell.mesh)
+    vj0, vk0 = oracle.isdf_get_jk(np.ascontiguousarray(phi[:, ip]), W, dm)
+    return {'config': workloads.describe('c8') + ', c=15', 'n_ip': int(mydf.n_ip),
+            'ip_equal': bool(np.array_equal(ip, mydf.ip_index)),
+            'resid_equal': bool(np.array_equal(resid, mydf.ip_resid)),
+            'max_dAO': float(abs(aoR - phi).max()), 'max_dJ': float(abs(vj - vj0).max()),
+            'max_dK': float(abs(vk - vk0).max()), 'tolerance': 1e-8,
+            'oracle': 'oracle/c/isdf_oracle_blocked.c (points), oracle/isdf_ref.py (fit, W, J/K); parity unpinned: no ISDF in the reference'}
+
+
+def extra_workload(name, args, local, comm, world, torch, dist):
+    """One build + J/K of a larger BASELINE config on the same ranks (not part of `value`): 1 warm-up build,
+    1 timed build, 5 J/K; stage times and the FP64 GEMM rate of the timed build."""
+    from pyscf_isdf_b200 import workloads
+    from pyscf_isdf_b200.isdf import ISDF
+    dev = torch.device('cuda', local)
+    try:
+        cell = workloads.make_cell(name)
+        nao = cell.nao
+        mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=False, comm=comm, wgemm=args.wgemm)
+        h = mydf.handle
+        d_dm = torch.from_numpy(workloads.synthetic_dm(nao)[None]).to(dev)
+        mydf.build()
+        mydf.reset()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        h.gemm_profile(True)
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(); mydf.build(); e1.record()
+        torch.cuda.synchronize(dev)
+        gflops, gms, gcount = h.gemm_profile_read()
+        h.gemm_profile(False)
+        build_ms = e0.elapsed_time(e1)
+        jk = []
+        for _ in range(6):
+            a0 = torch.cuda.Event(enable_timing=True); a1 = torch.cuda.Event(enable_timing=True)
+            a0.record(); mydf.get_jk_device(d_dm, True, True, None); a1.record()
+            torch.cuda.synchronize(dev)
+            jk.append(a0.elapsed_time(a1))
+        tt = torch.tensor([build_ms, float(np.median(jk[1:]))], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        out = {'workload': workloads.describe(name), 'nao': nao, 'ngrids': int(np.prod(cell.mesh)), 'n_ip': int(mydf.n_ip),
+               'n_gpus': world, 'build_s': float(tt[0]) / 1e3, 'jk_s': float(tt[1]) / 1e3,
+               'value': (float(tt[0]) + float(tt[1])) / 1e3, 'unit': 's', 'timed': '1 warm-up build, 1 timed build, median of 5 J/K; max over ranks',
+               'stages_ms': {k: float(v) for k, v in mydf.timings.items() if k.endswith('_ms')},
+               'fp64_gemm_tflops_rank0': gflops / (gms * 1e-3) / 1e12 if gms > 0 else None}
+        mydf.release_buffers()
+        del mydf
+        torch.cuda.empty_cache()
+        return out
+    except Exception as e:                    # noqa: BLE001 -- an extra must never take the headline line down
+        torch.cuda.empty_cache()
+        return {'workload': name, 'error': '%s: %s' % (type(e).__name__, str(e)[:300])}
+
+
+def kernel_traffic(kernel):
+    """DRAM bytes per launch of the roofline kernel, read from the committed ncu summary of this round."""
+    path = os.path.join(ROOT, 'profiles', 'kernel_traffic.json')
+    try:
+        with open(path) as f:
+            return json.load(f).get(kernel)
+    except (OSError, ValueError):
+        return None
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -356,7 +516,8 @@ def run_b200(args):
     if world > 1:
         from pyscf_isdf_b200.dist import Comm
         comm = Comm()                 # grid sharded by x-planes, one rank per GPU (pyscf_isdf_b200/dist.py)
-    mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=False, comm=comm, wgemm=args.wgemm)
+    exxdiv = None if args.exxdiv == 'none' else args.exxdiv
+    mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=(exxdiv == 'ewald'), comm=comm, wgemm=args.wgemm)
     h = mydf.handle
     dm_host = workloads.synthetic_dm(nao)[None]
     dm_pinned = torch.from_numpy(dm_host).pin_memory()
@@ -370,12 +531,12 @@ def run_b200(args):
     def step_device():
         mydf.reset()
         mydf.build()
-        return mydf.get_jk_device(d_dm, True, True, None)
+        return mydf.get_jk_device(d_dm, True, True, exxdiv)
 
     def step_e2e():
         mydf.reset()
         mydf.build()
-        return mydf.get_jk(dm_host[0], exxdiv=None)
+        return mydf.get_jk(dm_host[0], exxdiv=exxdiv)
 
     fp64_peak = measure_fp64_peak(torch, dev) if rank == 0 else None
 
@@ -409,7 +570,7 @@ def run_b200(args):
     jk_ms = []
     for _ in range(args.jk_reps + 2):
         a0 = torch.cuda.Event(enable_timing=True); a1 = torch.cuda.Event(enable_timing=True)
-        a0.record(); mydf.get_jk_device(d_dm, True, True, None); a1.record()
+        a0.record(); mydf.get_jk_device(d_dm, True, True, exxdiv); a1.record()
         torch.cuda.synchronize(dev)
         jk_ms.append(a0.elapsed_time(a1))
     jk_ms = float(np.median(jk_ms[2:]))
@@ -432,26 +593,41 @@ def run_b200(args):
 
     # end to end through the plugin's host API
     if args.no_e2e:
-        vj, vk = mydf.get_jk(dm_host[0], exxdiv=None)
+        vj, vk = mydf.get_jk(dm_host[0], exxdiv=exxdiv)
         e2e_s = float('nan')
     else:
         step_e2e()
         barrier()
         t0 = time.perf_counter()
-        e2e_steps = max(1, min(args.steps, 2))
-        for _ in range(e2e_steps):
+        for _ in range(args.steps):                  # all K steps, every one a full build + J/K through host buffers
             vj, vk = step_e2e()
         barrier()
-        e2e_s = (time.perf_counter() - t0) / e2e_steps
+        e2e_s = (time.perf_counter() - t0) / args.steps
+    # bytes that cross the PCIe link per step: the cell tables and lattice images isdf_eval_ao takes as host
+    # arrays, the density matrix through the object's pinned staging buffer (counted where it is copied,
+    # ISDF.get_jk) on the way in; J, K (counted likewise) and the selected points + residuals on the way out
     rcut, Ls = cell.ao_eval_params()
     h2d = int(cell._atm.nbytes + cell._bas.nbytes + cell._env.nbytes + np.asarray(Ls).nbytes +
-              np.asarray(rcut).nbytes + dm_host.nbytes + 8 * mydf.n_ip)
-    d2h = int(vj.nbytes + vk.nbytes + 16 * mydf.n_ip)
+              np.asarray(rcut).nbytes + mydf.h2d_bytes)
+    d2h = int(mydf.d2h_bytes + 16 * mydf.n_ip)
 
     tt = torch.tensor([total_ms, jk_ms, e2e_s], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     total_ms, jk_ms, e2e_s = [float(x) for x in tt.tolist()]
+
+    # one-off runs of the larger BASELINE configs on the same ranks (never part of `value`): the north_star
+    # target Si216 needs the 8-GPU sharding (its factor alone is 424 GB), the water box fits from 4 GPUs up
+    extra = {}
+    if not args.no_extra and name == 'c64':
+        headline = (mydf.n_ip, mydf.timings)
+        mydf.reset(); mydf.release_buffers()
+        torch.cuda.empty_cache()
+        if world >= 4:
+            extra['h2o32'] = extra_workload('h2o32', args, local, comm, world, torch, dist)
+        if world >= 8:
+            extra['si216'] = extra_workload('si216', args, local, comm, world, torch, dist)
+        mydf.n_ip = headline[0]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -471,9 +647,10 @@ def run_b200(args):
         'gemm_ms_per_step': gms / args.steps, 'gemm_share_of_step': gms / total_ms,
         # DRAM bytes of one representative launch of this kernel from an `ncu --set full` capture
         # (flush GEMM M=128 N=357912 K=6240: 19.3 GB against 18.6 GB algorithmic, profiles/r01_ncu_final.md)
-        'traffic': 1.93e10 if name == 'c64' else None,
-        'traffic_launch': 'C[128,357912] -= A^T B, K=6240 (selection flush): algorithmic 1.86e10 B' if name == 'c64' else None,
     }
+    tr = kernel_traffic('dgemm_kernel') if name == 'c64' else None
+    roofline['traffic'] = tr['dram_bytes'] if tr else None
+    roofline['traffic_launch'] = ('%s: algorithmic %.3g B (%s)' % (tr['launch'], tr['algorithmic_bytes'], tr['source'])) if tr else None
     line = {
         'metric': METRIC, 'value': step_ms / 1e3, 'unit': 's', 'n_gpus': world,
         'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': step_ms,
@@ -481,6 +658,7 @@ def run_b200(args):
         'data': 'synthetic',
         'config': {'workload': workloads.describe(name), 'c': args.c, 'nao': nao, 'ngrids': ng,
                    'n_ip': int(mydf.n_ip), 'fit': args.fit, 'wgemm': args.wgemm, 'l2': 'inputs_exceed_l2' if 8.0 * ng * nao > 126e6 else 'inputs_fit_l2',
+                   'exxdiv': args.exxdiv,
                    'parallelism': 'single' if world == 1 else 'grid-slab x%d (all-gather/all-to-all/all-reduce over NCCL)' % world},
         'build_s': build_s, 'jk_s': jk_ms / 1e3, 'stages_ms': stages_ms,
         'each_step_ms': each_ms,
@@ -507,6 +685,13 @@ def run_b200(args):
                             'fp64_equivalent_tflops': fm['coulomb_gemm'] / world / (stages_ms['wgemm_ms'] * 1e-3) / 1e12}
     if xc_info is not None:
         line['xc'] = xc_info
+    if extra:
+        line['extra'] = extra
+    if world == 1 and not args.no_parity:
+        try:
+            line['parity'] = parity_block(local)
+        except Exception as e:                # noqa: BLE001
+            line['parity'] = {'error': '%s: %s' % (type(e).__name__, str(e)[:300])}
     if world == 1 and not args.no_cpu_baseline:
         v, b, j, per, desc, ncores = cpu_baseline_run(cell, int(mydf.n_ip))
         line['cpu_baseline'] = {'value': v, 'unit': 's', 'cores': ncores, 'kind': 'port', 'sample': desc,

@@ -62,6 +62,7 @@ class ISDF:
         # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
         self.comm = comm
         self._rsh_df = {}
+        self.h2d_bytes = self.d2h_bytes = 0      # bytes the last get_jk() copied over PCIe (counted at the copies)
         self.timings = {}
         self.reset()
 
