@@ -61,6 +61,11 @@ struct isdf_handle {
     cudaEvent_t* prof_ev;      // 2 * prof_cap events
     double prof_flops;
     int gemm_force;            // 0 auto, 2..5: CTA tile / ring depth (tuning knob, see isdf_set_gemm_tile)
+    // tables of the stage-4 transforms (twiddles, DFT matrices, Coulomb weights), kept between calls for the
+    // last mesh so that the per-batch calls of a build do not allocate, copy and synchronise each time;
+    // owned by fft.cu, released through fft_cache_free by isdf_destroy
+    void* fft_cache;
+    void (*fft_cache_free)(void*);
 };
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

@@ -105,6 +105,7 @@ extern "C" int isdf_destroy(isdf_handle* h)
         cudaEventDestroy(h->ev0[i]);
         cudaEventDestroy(h->ev1[i]);
     }
+    if (h->fft_cache && h->fft_cache_free) h->fft_cache_free(h->fft_cache);
     cudaFree(h->d_small);
     cudaFreeHost(h->h_pinned);
     for (int i = 0; i < 2 * h->prof_cap; ++i) cudaEventDestroy(h->prof_ev[i]);

@@ -34,7 +34,9 @@ __global__ void symmetrize_upper_kernel(double* __restrict__ W, long long ld, in
 // ---- host side -----------------------------------------------------------------
 struct Plans {
     FftPlan ax[3];
-    double2* d_tw;      // one allocation: twiddles, Rader kernels, permutations
+    double2* d_tw;      // one allocation: twiddles, Rader kernels, permutations, DFT tables
+    DftAxis dft[3];     // dense-DFT form of an axis (dft_gemm.cu); use_dft[d] says whether the forward pass takes it
+    bool use_dft[3];
 };
 
 // ISDF_FFT_FUSED=1 (opt-in): Rader lines through rader_fused_smem (fft_core.cuh)
@@ -44,12 +46,43 @@ int fft_fused_requested()
     return (e && atoi(e) > 0) ? 1 : 0;
 }
 
+// What a handle keeps between calls: the plans of the last mesh (device tables allocated once with cudaMalloc)
+// and the last Coulomb-weight table.  A build calls the transforms dozens of times on one mesh; allocating,
+// uploading and synchronising per call showed up as occasional 0.3 s stalls in the stage (round 1).
+struct FftCache {
+    int mesh[3] = {0, 0, 0};
+    int fused = -1;
+    Plans P;
+    void* d_tab = nullptr; size_t tab_cap = 0;
+    double* d_w = nullptr; size_t w_cap = 0;          // sqrt(w coulG) table of the x pass
+    CoulGeom w_geo; int w_nx = 0, w_ncl = 0; bool w_valid = false;
+};
+
+void fft_cache_free(void* p)
+{
+    FftCache* c = (FftCache*)p;
+    if (c->d_tab) cudaFree(c->d_tab);
+    if (c->d_w) cudaFree(c->d_w);
+    delete c;
+}
+
+FftCache* cache_of(isdf_handle* h)
+{
+    if (!h->fft_cache) { h->fft_cache = new FftCache(); h->fft_cache_free = fft_cache_free; }
+    return (FftCache*)h->fft_cache;
+}
+
 int make_plans(isdf_handle* h, const int* mesh, Plans& P)
 {
+    FftCache* fc = cache_of(h);
+    const int fused = fft_fused_requested();
+    if (fc->d_tab && fc->fused == fused && fc->mesh[0] == mesh[0] && fc->mesh[1] == mesh[1] && fc->mesh[2] == mesh[2]) {
+        P = fc->P;
+        return ISDF_OK;
+    }
     std::vector<double2> tw;          // complex tables, offsets in double2 units
     std::vector<int> iv;              // integer tables
     AxisOffsets off[3];
-    const int fused = fft_fused_requested();
     for (int d = 0; d < 3; ++d) {
         const int n = mesh[d];
         ARG_CHECK(n >= 1 && n <= 1024);
@@ -58,15 +91,69 @@ int make_plans(isdf_handle* h, const int* mesh, Plans& P)
             return ISDF_ERR_ARG;
         }
     }
+    std::vector<double> dtab;         // cosine / sine tables of the dense-DFT passes
+    size_t off_c[3] = {0, 0, 0}, off_s[3] = {0, 0, 0};
+    for (int d = 0; d < 3; ++d) {
+        P.use_dft[d] = dft_enabled(mesh[d]);
+        if (P.use_dft[d]) dft_build_tables(mesh[d], P.dft[d], dtab, off_c[d], off_s[d]);
+    }
     const size_t bytes_tw = align_up(sizeof(double2) * tw.size(), 256);
-    const size_t bytes_iv = sizeof(int) * std::max<size_t>(iv.size(), 1);
-    CUDA_TRY(cudaMallocAsync((void**)&P.d_tw, bytes_tw + bytes_iv, h->stream));
+    const size_t bytes_iv = align_up(sizeof(int) * std::max<size_t>(iv.size(), 1), 256);
+    const size_t bytes_dft = sizeof(double) * std::max<size_t>(dtab.size(), 1);
+    const size_t need = bytes_tw + bytes_iv + bytes_dft;
+    // the previous tables may still be in use by kernels in flight on this handle's stream
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    fc->fused = -1;
+    if (need > fc->tab_cap) {
+        if (fc->d_tab) CUDA_TRY(cudaFree(fc->d_tab));
+        fc->d_tab = nullptr; fc->tab_cap = 0;
+        CUDA_TRY(cudaMalloc(&fc->d_tab, need));
+        fc->tab_cap = need;
+    }
+    P.d_tw = (double2*)fc->d_tab;
     int* d_iv = (int*)((char*)P.d_tw + bytes_tw);
+    double* d_dft = (double*)((char*)P.d_tw + bytes_tw + bytes_iv);
     CUDA_TRY(cudaMemcpyAsync(P.d_tw, tw.data(), sizeof(double2) * tw.size(), cudaMemcpyHostToDevice, h->stream));
     if (!iv.empty())
         CUDA_TRY(cudaMemcpyAsync(d_iv, iv.data(), sizeof(int) * iv.size(), cudaMemcpyHostToDevice, h->stream));
-    CUDA_TRY(cudaStreamSynchronize(h->stream));
-    for (int d = 0; d < 3; ++d) bind_axis_tables(P.ax[d], P.d_tw, d_iv, off[d]);
+    if (!dtab.empty())
+        CUDA_TRY(cudaMemcpyAsync(d_dft, dtab.data(), sizeof(double) * dtab.size(), cudaMemcpyHostToDevice, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));          // the host vectors are locals
+    for (int d = 0; d < 3; ++d) {
+        bind_axis_tables(P.ax[d], P.d_tw, d_iv, off[d]);
+        if (P.use_dft[d]) { P.dft[d].C = d_dft + off_c[d]; P.dft[d].S = d_dft + off_s[d]; }
+    }
+    fc->P = P; fc->fused = fused;
+    fc->mesh[0] = mesh[0]; fc->mesh[1] = mesh[1]; fc->mesh[2] = mesh[2];
+    fc->w_valid = false;
+    return ISDF_OK;
+}
+
+// sqrt(w coulG) for the x pass over the column slab geo.col0 .. +ncl: the handle's cached table when the
+// geometry is the one it was filled for, else refilled (stream-ordered; the old content has no reader left
+// once the fill kernel is enqueued behind them on the same stream)
+int coul_weight_table(isdf_handle* h, const CoulGeom& geo, int nx, int ncl, double** out)
+{
+    FftCache* fc = cache_of(h);
+    const size_t need = sizeof(double) * (size_t)nx * ncl;
+    if (fc->w_valid && fc->w_nx == nx && fc->w_ncl == ncl && memcmp(&fc->w_geo, &geo, sizeof(geo)) == 0) {
+        *out = fc->d_w;
+        return ISDF_OK;
+    }
+    fc->w_valid = false;
+    if (need > fc->w_cap) {
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        if (fc->d_w) CUDA_TRY(cudaFree(fc->d_w));
+        fc->d_w = nullptr; fc->w_cap = 0;
+        CUDA_TRY(cudaMalloc((void**)&fc->d_w, need));
+        fc->w_cap = need;
+    }
+    int rc;
+    if ((rc = dft_coul_weights(h->stream, geo, nx, ncl, fc->d_w))) return rc;
+    h->other_launches++;
+    memcpy(&fc->w_geo, &geo, sizeof(geo));
+    fc->w_nx = nx; fc->w_ncl = ncl; fc->w_valid = true;
+    *out = fc->d_w;
     return ISDF_OK;
 }
 
@@ -95,6 +182,7 @@ int set_smem(K kern, size_t smem)
 
 void fill_geom(CoulGeom& g, const int* mesh, const double* a, double scale)
 {
+    memset(&g, 0, sizeof(g));             // padding bytes too: the weight-table cache compares the struct bytewise
     // reciprocal vectors b = 2 pi inv(a^T): rows b_i with a_i . b_j = 2 pi delta_ij
     const double a00 = a[0], a01 = a[1], a02 = a[2], a10 = a[3], a11 = a[4], a12 = a[5], a20 = a[6], a21 = a[7], a22 = a[8];
     const double det = a00 * (a11 * a22 - a12 * a21) - a01 * (a10 * a22 - a12 * a20) + a02 * (a10 * a21 - a11 * a20);
@@ -140,21 +228,31 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
     const int nx = mesh[0], ny = mesh[1], nz = mesh[2], nzh = nz / 2 + 1;
     cudaStream_t s = h->stream;
     const size_t budget = fft_smem_budget();
-    {
+    int rc;
+    if (P.use_dft[2]) {
+        if ((rc = dft_z_r2c(s, in, ldin, spec, lds, nvec, nx * ny, P.dft[2]))) return rc;
+    } else {
         const int LB = pick_lb(P.ax[2].lalloc(), fft_smem_budget(true));
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         dim3 grid((nx * ny + 2 * LB - 1) / (2 * LB), nvec);
         FFT_RUN_Z((P.ax[2].rader >= 2), fft_z_r2c_kernel, fused_z_r2c, grid, smem, s, in, ldin, spec, lds, P.ax[2], nx * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
-    {
+    if (P.use_dft[1]) {
+        if ((rc = dft_cols(s, spec, lds, nvec, nx, (long long)ny * nzh, nzh, nzh, P.dft[1], nullptr, 0))) return rc;
+    } else {
         const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
         dim3 grid((nzh + CH - 1) / CH, nx, nvec);
         FFT_RUN_COLS((P.ax[1].rader >= 2), 0, grid, smem, s, spec, lds, (long long)ny * nzh, P.ax[1], nzh, CH, geo);
         CUDA_TRY(cudaGetLastError());
     }
-    {
+    if (P.use_dft[0] && xmode != 2) {
+        const int ncols = ny * nzh;
+        double* wtab = nullptr;
+        if (xmode == 1 && (rc = coul_weight_table(h, geo, nx, ncols, &wtab))) return rc;
+        if ((rc = dft_cols(s, spec, lds, nvec, 1, 0, ncols, ncols, P.dft[0], wtab, ncols))) return rc;
+    } else {
         const int ncols = ny * nzh;
         const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncols);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
@@ -223,7 +321,6 @@ extern "C" int isdf_coulomb_apply(isdf_handle* h, const double* in, long long ld
     }
     CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FFT], h->stream));
     h->ev_used[ISDF_STAGE_FFT] = true;
-    CUDA_TRY(cudaFreeAsync(P.d_tw, h->stream));
     return ISDF_OK;
 }
 
@@ -270,7 +367,6 @@ extern "C" int isdf_build_W(isdf_handle* h, const double* zeta, int np, long lon
     h->other_launches++;
     CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_COULOMB], s));
     h->ev_used[ISDF_STAGE_COULOMB] = true;
-    CUDA_TRY(cudaFreeAsync(P.d_tw, s));
     return ISDF_OK;
 }
 
@@ -312,14 +408,18 @@ extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int
     cudaStream_t s = h->stream;
     const size_t budget = fft_smem_budget();
     CoulGeom geo; memset(&geo, 0, sizeof(geo));
-    {
+    if (P.use_dft[2]) {
+        if ((rc = dft_z_r2c(s, in, ldin, (double2*)spec, lds, nvec, nxl * ny, P.dft[2]))) return rc;
+    } else {
         const int LB = pick_lb(P.ax[2].lalloc(), fft_smem_budget(true));
         const size_t smem = 2 * sizeof(double2) * LB * P.ax[2].lalloc();
         dim3 grid((nxl * ny + 2 * LB - 1) / (2 * LB), nvec);
         FFT_RUN_Z((P.ax[2].rader >= 2), fft_z_r2c_kernel, fused_z_r2c, grid, smem, s, in, ldin, (double2*)spec, lds, P.ax[2], nxl * ny, LB);
         CUDA_TRY(cudaGetLastError());
     }
-    {
+    if (P.use_dft[1]) {
+        if ((rc = dft_cols(s, (double2*)spec, lds, nvec, nxl, (long long)ny * nzh, nzh, nzh, P.dft[1], nullptr, 0))) return rc;
+    } else {
         const int CH = std::min(pick_lb(P.ax[1].lalloc(), budget), nzh);
         const size_t smem = 2 * sizeof(double2) * CH * P.ax[1].lalloc();
         dim3 grid((nzh + CH - 1) / CH, nxl, nvec);
@@ -327,7 +427,6 @@ extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int
         CUDA_TRY(cudaGetLastError());
     }
     h->other_launches += 2;
-    CUDA_TRY(cudaFreeAsync(P.d_tw, s));
     return ISDF_OK;
 }
 
@@ -378,14 +477,19 @@ extern "C" int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nv
     if ((rc = make_plans(h, h_mesh, P))) return rc;
     CoulGeom geo; fill_geom(geo, h_mesh, h_a, 1.0);
     geo.col0 = col0;
-    const size_t budget = fft_smem_budget();
-    const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncl);
-    const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
-    dim3 grid((ncl + CH - 1) / CH, 1, nvec);
-    FFT_RUN_COLS((P.ax[0].rader >= 2), 1, grid, smem, h->stream, (double2*)Y, ldy, 0, P.ax[0], ncl, CH, geo);
+    if (P.use_dft[0]) {
+        double* wtab = nullptr;
+        if ((rc = coul_weight_table(h, geo, nx, ncl, &wtab))) return rc;
+        if ((rc = dft_cols(h->stream, (double2*)Y, ldy, nvec, 1, 0, ncl, ncl, P.dft[0], wtab, ncl))) return rc;
+    } else {
+        const size_t budget = fft_smem_budget();
+        const int CH = std::min(pick_lb(P.ax[0].lalloc(), budget), ncl);
+        const size_t smem = 2 * sizeof(double2) * CH * P.ax[0].lalloc();
+        dim3 grid((ncl + CH - 1) / CH, 1, nvec);
+        FFT_RUN_COLS((P.ax[0].rader >= 2), 1, grid, smem, h->stream, (double2*)Y, ldy, 0, P.ax[0], ncl, CH, geo);
+    }
     CUDA_TRY(cudaGetLastError());
     h->other_launches++;
-    CUDA_TRY(cudaFreeAsync(P.d_tw, h->stream));
     return ISDF_OK;
 }
 

@@ -25,6 +25,22 @@ int fused_z_c2r(dim3 grid, size_t smem, cudaStream_t s, const double2* in, long 
 int fused_cols(int mode, dim3 grid, size_t smem, cudaStream_t s, double2* data, long long vec_stride,
                long long outer_stride, FftPlan pl, int ncols, int CH, CoulGeom geo);
 
+// ---- forward passes as dense DFTs on the FP64 tensor pipe (dft_gemm.cu) ----
+constexpr int DFT_NMAX = 128;
+struct DftAxis {
+    int n, ne, hp;          // length, n/2 + 1 output / folded-input rows, (n-1)/2 mirrored pairs
+    int MT, KP, LDA;        // 8-row tiles of the tables, inner dimension padded to 4, (unused) row stride
+    const double* C;        // device table in DMMA fragment order: (cos, sin)(2 pi k j / n) interleaved, see dft_gemm.cu
+    const double* S;        // same pointer (one table)
+};
+bool dft_enabled(int n);
+void dft_build_tables(int n, DftAxis& ax, std::vector<double>& tab, size_t& off_c, size_t& off_s);
+int dft_z_r2c(cudaStream_t s, const double* in, long long ldin, double2* out, long long ldout, int nvec,
+              int nlines, const DftAxis& ax);
+int dft_cols(cudaStream_t s, double2* data, long long vec_stride, int nvec, int nouter, long long outer_stride,
+             int row_stride, int ncols, const DftAxis& ax, const double* wtab, int wld);
+int dft_coul_weights(cudaStream_t s, const CoulGeom& geo, int nx, int ncl, double* w);
+
 }  // namespace isdf_fft
 
 namespace {
