@@ -239,6 +239,15 @@ int isdf_get_jk_block(isdf_handle* h, const double* X, const double* Wrows, long
                       int with_j, int with_k, double* vj, double* vk,
                       void* ws, size_t ws_bytes);
 
+/* isdf_get_jk_block for ONE density matrix given by its occupied orbitals, D = C diag(n) C^T: the mo_coeff /
+ * mo_occ tags the reference's exchange build uses to shrink its work from nao to nocc
+ * (pyscf/pbc/df/fft_jk.py:206-210, :235-238).  Cs[nocc, nao] (row-major) = sqrt(n_i) C[:, i]^T, nocc <= nao.
+ * Same workspace size and outputs ([nao, nao]) as isdf_get_jk_block with nset = 1. */
+int isdf_get_jk_block_occ(isdf_handle* h, const double* X, const double* Wrows, long long ldw,
+                          int p0, int npl, const double* Cs, int nocc, int nao, int np,
+                          int with_j, int with_k, double* vj, double* vk,
+                          void* ws, size_t ws_bytes);
+
 /* isdf_get_jk for callers that cannot allocate (code under CUDA graph capture, tight serving
  * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
  * Same arguments and result as isdf_get_jk without the workspace: the

@@ -78,6 +78,8 @@ SIGNATURES = {
     'isdf_get_jk_ws_bytes': (c_sz, [c_int, c_int]),
     'isdf_get_jk': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int,
                             c_vp, c_vp, c_vp, c_sz]),
+    'isdf_get_jk_block_occ': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_int, c_int, c_int,
+                                      c_int, c_int, c_vp, c_vp, c_vp, c_sz]),
     'isdf_get_jk_static_max_bytes': (c_sz, []),
     'isdf_get_jk_static': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
@@ -431,6 +433,19 @@ class Handle:
                                          c_vp(vj.data_ptr()) if vj is not None else None,
                                          c_vp(vk.data_ptr()) if vk is not None else None,
                                          c_vp(ws.data_ptr()), ws.numel()))
+        return ws
+
+
+    def get_jk_block_occ(self, X, Wrows, ldw, p0, npl, Cs, nocc, nao, npts, with_j, with_k, vj, vk, ws=None):
+        """J/K of D = C diag(n) C^T from Cs[nocc, nao] = sqrt(n) C^T (include/isdf_b200.h)."""
+        nbytes = self.lib.isdf_get_jk_block_ws_bytes(nao, npts, npl)
+        if ws is None:
+            ws = self.workspace(nbytes)
+        check(self.lib.isdf_get_jk_block_occ(self.h, c_vp(X.data_ptr()), c_vp(Wrows.data_ptr()), ldw, p0, npl,
+                                             c_vp(Cs.data_ptr()), nocc, nao, npts, int(with_j), int(with_k),
+                                             c_vp(vj.data_ptr()) if vj is not None else None,
+                                             c_vp(vk.data_ptr()) if vk is not None else None,
+                                             c_vp(ws.data_ptr()), ws.numel()))
         return ws
 
 

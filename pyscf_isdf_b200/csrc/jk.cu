@@ -64,6 +64,39 @@ extern "C" size_t isdf_get_jk_block_ws_bytes(int nao, int np, int npl)
 
 extern "C" size_t isdf_get_jk_ws_bytes(int nao, int np) { return isdf_get_jk_block_ws_bytes(nao, np, np); }
 
+namespace {
+
+// J and K contributions of the row block once the two [r, np] factors of M = L^T R are known
+// (M = X^T D X: L = X, R = D X, r = nao;  occupied orbitals: L = R = T' = (C sqrt(n))^T X, r = nocc):
+//   rho_P = sum_i L[i,P] R[i,P];  J_part = X_b diag(W_b rho) X_b^T;  K_part = X_b ((L_b^T R) o W_b) X^T
+int jk_from_factors(isdf_handle* h, const double* X, const double* Wrows, long long ldw, int p0, int npl,
+                    int nao, int np, const double* L, const double* R, int r, int with_j, int with_k,
+                    double* vj, double* vk, double* Ub, double* Vb, double* Nm, double* rho, double* v)
+{
+    cudaStream_t s = h->stream;
+    const double* Xb = X + p0;                         // columns p0.. of X (row stride np)
+    int rc;
+    if (with_j) {
+        coldot_kernel<<<(np + 255) / 256, 256, 0, s>>>(L, R, r, np, np, rho);
+        gemv_rows_kernel<<<(npl + 7) / 8, 256, 0, s>>>(Wrows, ldw, npl, np, rho, v);
+        dim3 g((npl + 255) / 256, std::min(nao, 1024));
+        scale_cols_kernel<<<g, 256, 0, s>>>(Xb, v, nao, npl, np, npl, Ub);
+        CUDA_TRY(cudaGetLastError());
+        h->other_launches += 3;
+        // J_part = Ub X_b^T
+        if ((rc = gemm6(h, nao, nao, npl, Ub, npl, 0, Xb, np, 0, vj, nao, nullptr, 0, EPI_STORE))) return rc;
+    }
+    if (with_k) {
+        // N_b = (L_b^T R) o W_b ; V_b = N_b X^T ; K_part = X_b V_b
+        if ((rc = gemm6(h, npl, np, r, L + p0, np, 1, R, np, 1, Nm, np, Wrows, ldw, EPI_MUL))) return rc;
+        if ((rc = gemm6(h, npl, nao, np, Nm, np, 0, X, np, 0, Vb, nao, nullptr, 0, EPI_STORE))) return rc;
+        if ((rc = gemm6(h, nao, nao, npl, Xb, np, 0, Vb, nao, 1, vk, nao, nullptr, 0, EPI_STORE))) return rc;
+    }
+    return ISDF_OK;
+}
+
+}  // namespace
+
 // Contribution of the interpolation points [p0, p0+npl) (a row block of W) to J and K:
 //   J_part = X_b diag(W_b rho) X_b^T ,  K_part = X_b ((X_b^T D X) o W_b) X^T
 // Summed over disjoint blocks this is the full J/K (the caller all-reduces).
@@ -86,7 +119,6 @@ extern "C" int isdf_get_jk_block(isdf_handle* h, const double* X, const double* 
     double* Nm = a.get<double>((size_t)npl * np);      // (X_b^T T) o W_b
     double* rho = a.get<double>(np);
     double* v = a.get<double>(npl);
-    const double* Xb = X + p0;                         // columns p0.. of X (row stride np)
     cudaStream_t s = h->stream;
     int rc;
     CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_JK], s));
@@ -94,23 +126,43 @@ extern "C" int isdf_get_jk_block(isdf_handle* h, const double* X, const double* 
         const double* D = dm + (size_t)i * nao * nao;
         // T = D X
         if ((rc = gemm6(h, nao, np, nao, D, nao, 0, X, np, 1, T, np, nullptr, 0, EPI_STORE))) return rc;
-        if (with_j) {
-            coldot_kernel<<<(np + 255) / 256, 256, 0, s>>>(X, T, nao, np, np, rho);
-            gemv_rows_kernel<<<(npl + 7) / 8, 256, 0, s>>>(Wrows, ldw, npl, np, rho, v);
-            dim3 g((npl + 255) / 256, std::min(nao, 1024));
-            scale_cols_kernel<<<g, 256, 0, s>>>(Xb, v, nao, npl, np, npl, Ub);
-            CUDA_TRY(cudaGetLastError());
-            h->other_launches += 3;
-            // J_part = Ub X_b^T
-            if ((rc = gemm6(h, nao, nao, npl, Ub, npl, 0, Xb, np, 0, vj + (size_t)i * nao * nao, nao, nullptr, 0, EPI_STORE))) return rc;
-        }
-        if (with_k) {
-            // N_b = (X_b^T T) o W_b ; V_b = N_b X^T ; K_part = X_b V_b
-            if ((rc = gemm6(h, npl, np, nao, Xb, np, 1, T, np, 1, Nm, np, Wrows, ldw, EPI_MUL))) return rc;
-            if ((rc = gemm6(h, npl, nao, np, Nm, np, 0, X, np, 0, Vb, nao, nullptr, 0, EPI_STORE))) return rc;
-            if ((rc = gemm6(h, nao, nao, npl, Xb, np, 0, Vb, nao, 1, vk + (size_t)i * nao * nao, nao, nullptr, 0, EPI_STORE))) return rc;
-        }
+        if ((rc = jk_from_factors(h, X, Wrows, ldw, p0, npl, nao, np, X, T, nao, with_j, with_k,
+                                  with_j ? vj + (size_t)i * nao * nao : nullptr, with_k ? vk + (size_t)i * nao * nao : nullptr,
+                                  Ub, Vb, Nm, rho, v))) return rc;
     }
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_JK], s));
+    h->ev_used[ISDF_STAGE_JK] = true;
+    return ISDF_OK;
+}
+
+// The same contribution for a density matrix given by its occupied orbitals, D = C diag(n) C^T (the
+// mo_coeff / mo_occ tags the reference's K build reads, pyscf/pbc/df/fft_jk.py:206-210, :235-238):
+// Cs[nocc, nao] = sqrt(n_i) C[:, i]^T.  M = X^T D X = T'^T T' with T' = Cs X, so the first product shrinks
+// from nao x nao x np to nocc x nao x np and the Hadamard product from K = nao to K = nocc.
+extern "C" int isdf_get_jk_block_occ(isdf_handle* h, const double* X, const double* Wrows, long long ldw,
+                                     int p0, int npl, const double* Cs, int nocc, int nao, int np,
+                                     int with_j, int with_k, double* vj, double* vk,
+                                     void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && X && Wrows && Cs && ws && nocc > 0 && nocc <= nao && nao > 0 && np > 0);
+    ARG_CHECK(p0 >= 0 && npl > 0 && p0 + npl <= np && ldw >= np);
+    ARG_CHECK((!with_j || vj) && (!with_k || vk));
+    if (isdf_get_jk_block_ws_bytes(nao, np, npl) > ws_bytes) {
+        isdf_set_error("get_jk workspace too small: need %zu have %zu", isdf_get_jk_block_ws_bytes(nao, np, npl), ws_bytes);
+        return ISDF_ERR_WS;
+    }
+    WsAlloc a(ws, ws_bytes);
+    double* T = a.get<double>((size_t)nao * np);       // T' = Cs X uses the first nocc rows
+    double* Ub = a.get<double>((size_t)nao * npl);
+    double* Vb = a.get<double>((size_t)npl * nao);
+    double* Nm = a.get<double>((size_t)npl * np);
+    double* rho = a.get<double>(np);
+    double* v = a.get<double>(npl);
+    cudaStream_t s = h->stream;
+    int rc;
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_JK], s));
+    if ((rc = gemm6(h, nocc, np, nao, Cs, nao, 0, X, np, 1, T, np, nullptr, 0, EPI_STORE))) return rc;
+    if ((rc = jk_from_factors(h, X, Wrows, ldw, p0, npl, nao, np, T, T, nocc, with_j, with_k, vj, vk, Ub, Vb, Nm, rho, v))) return rc;
     CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_JK], s));
     h->ev_used[ISDF_STAGE_JK] = true;
     return ISDF_OK;

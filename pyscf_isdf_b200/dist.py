@@ -351,8 +351,9 @@ def _congruence_solve(ops, comm, part, U, ldu, M, npts):
     return R.t().contiguous()                           # W[cols, :] by symmetry
 
 
-def get_jk_device(mydf, comm, d_dm, with_j=True, with_k=True, ops=None):
-    """Stage 5: every rank contracts its row block of W, then J and K are all-reduced."""
+def get_jk_device(mydf, comm, d_dm, with_j=True, with_k=True, ops=None, occ=None):
+    """Stage 5: every rank contracts its row block of W, then J and K are all-reduced.
+    occ: device tensor Cs[nocc, nao] = sqrt(n) C^T of a single tagged density matrix (occupied-orbital form)."""
     ops = ops or mydf.handle
     nao, npts = mydf.aoR_ip.shape
     part = mydf._part
@@ -364,7 +365,11 @@ def get_jk_device(mydf, comm, d_dm, with_j=True, with_k=True, ops=None):
     vk = out[1] if with_k else None
     if p1 > p0:
         # mydf.W holds this rank's row block W[p0:p1, :] (the whole matrix on one rank)
-        mydf._jk_ws = ops.get_jk_block(mydf.aoR_ip, mydf.W, npts, p0, p1 - p0, d_dm, nset, nao, npts,
-                                       with_j, with_k, vj, vk, ws=mydf._jk_ws)
+        if occ is not None and nset == 1 and hasattr(ops, 'get_jk_block_occ'):
+            mydf._jk_ws = ops.get_jk_block_occ(mydf.aoR_ip, mydf.W, npts, p0, p1 - p0, occ, occ.shape[0], nao, npts,
+                                               with_j, with_k, vj, vk, ws=mydf._jk_ws)
+        else:
+            mydf._jk_ws = ops.get_jk_block(mydf.aoR_ip, mydf.W, npts, p0, p1 - p0, d_dm, nset, nao, npts,
+                                           with_j, with_k, vj, vk, ws=mydf._jk_ws)
     comm.all_reduce_sum(out)
     return vj, vk

@@ -312,15 +312,28 @@ class ISDF:
         nao, npts = self.aoR_ip.shape
         nset = d_dm.shape[0]
         isdf_j = with_j and not self.exact_j
+        d_cs = None
+        if mo is not None and nset == 1 and (isdf_j or with_k):
+            # occupied orbitals of a tagged density matrix: D = C diag(n) C^T, Cs = sqrt(n) C^T [nocc, nao]
+            C, occ = mo
+            keep = occ > 0
+            if keep.any() and keep.sum() <= nao:
+                cs = np.ascontiguousarray((C[:, keep] * np.sqrt(occ[keep])).T, dtype=np.float64)
+                d_cs = h.from_host(cs)
+        self.last_jk_form = 'occupied-orbital' if d_cs is not None else 'density-matrix'
         if self.comm is not None and (isdf_j or with_k):
             from . import dist                  # self.W is this rank's row block of W
-            vj, vk = dist.get_jk_device(self, self.comm, d_dm, isdf_j, with_k)
+            vj, vk = dist.get_jk_device(self, self.comm, d_dm, isdf_j, with_k, occ=d_cs)
         elif isdf_j or with_k:
             vj = h.empty((nset, nao, nao)) if isdf_j else None
             vk = h.empty((nset, nao, nao)) if with_k else None
             if self._jk_ws is None:
                 self._jk_ws = h.workspace(h.lib.isdf_get_jk_ws_bytes(nao, npts))
-            h.get_jk(self.aoR_ip, self.W, d_dm, nset, nao, npts, isdf_j, with_k, vj, vk, ws=self._jk_ws)
+            if d_cs is not None:
+                h.get_jk_block_occ(self.aoR_ip, self.W, npts, 0, npts, d_cs, d_cs.shape[0], nao, npts,
+                                   isdf_j, with_k, vj, vk, ws=self._jk_ws)
+            else:
+                h.get_jk(self.aoR_ip, self.W, d_dm, nset, nao, npts, isdf_j, with_k, vj, vk, ws=self._jk_ws)
         else:
             vj = vk = None
         if with_j and self.exact_j:

@@ -129,3 +129,36 @@ def test_exact_density_j_matches_reference_fftdf():
     # J-only call does not need (or touch) the ISDF contraction
     j_only, none = mydf.get_jk(dms[0], with_k=False)
     assert none is None and abs(j_only - ref[0]).max() < 1e-10
+
+
+def test_tagged_density_matrix_takes_the_occupied_orbital_path():
+    """A density matrix carrying mo_coeff / mo_occ (pyscf.lib.tag_array, read by the reference's K build at
+    pyscf/pbc/df/fft_jk.py:206-210) goes through isdf_get_jk_block_occ: same J/K as the plain matrix to 1e-10,
+    also with unoccupied columns present, fractional occupations, and exxdiv='ewald'."""
+    class Tagged(np.ndarray):
+        pass
+    cell = diamond_c8([14, 14, 14], basis='gth-dzvp', jitter=0.15)
+    nao = cell.nao
+    rng = np.random.default_rng(5)
+    C = np.linalg.qr(rng.standard_normal((nao, nao)))[0]
+    occ = np.zeros(nao)
+    occ[:16] = 2.0
+    occ[16:19] = [1.3, 0.4, 0.05]
+    dm = (C * occ).dot(C.T)
+    mydf = ISDF(cell, c=6)
+    vj0, vk0 = mydf.get_jk(dm, exxdiv='ewald')
+    tagged = dm.view(Tagged)
+    tagged.mo_coeff, tagged.mo_occ = C, occ
+    assert mydf.last_jk_form == 'density-matrix'
+    vj1, vk1 = mydf.get_jk(tagged, exxdiv='ewald')
+    assert mydf.last_jk_form == 'occupied-orbital'
+    assert abs(vj1 - vj0).max() < 1e-10 and abs(vk1 - vk0).max() < 1e-10
+    # the oracle on the same density matrix
+    orc = oracle.isdf_build(oracle_phi(cell), cell.lattice_vectors(), cell.mesh, 6 * nao)
+    vjo, vko = oracle.isdf_get_jk(orc['X'], orc['W'], dm)
+    vj2, vk2 = mydf.get_jk(tagged, exxdiv=None)
+    assert abs(vj2 - vjo).max() < 1e-8 and abs(vk2 - vko).max() < 1e-8
+    # a stack of matrices or complex orbitals falls back to the density-matrix path
+    vj3, vk3 = mydf.get_jk(np.stack([dm, dm]))
+    assert mydf.last_jk_form == 'density-matrix'
+    assert abs(vk3[1] - vk2).max() < 1e-10

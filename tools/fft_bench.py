@@ -16,8 +16,9 @@ def main():
     h = _lib.Handle(0)
     a = np.eye(3) * 13.0
     cases = (([35] * 3, 1560), ([71] * 3, 1024), ([96] * 3, 512), ([108] * 3, 384))
-    if len(sys.argv) > 1:                       # e.g. `fft_bench.py 71` -> only that mesh
-        cases = [c for c in cases if str(c[0][0]) in sys.argv[1:]]
+    if len(sys.argv) > 1:                       # e.g. `fft_bench.py 71 64` -> only those meshes (any size)
+        known = {c[0][0]: c for c in cases}
+        cases = [known.get(int(a), ([int(a)] * 3, max(64, int(4.0e8 / int(a) ** 3)))) for a in sys.argv[1:]]
     for mesh, nvec in cases:
         ng = int(np.prod(mesh))
         ngh = mesh[0] * mesh[1] * (mesh[2] // 2 + 1)

@@ -28,7 +28,8 @@ def synthetic_phi(h, nao, mesh, seed):
     ld = _lib.pad8(ng)
     g = torch.Generator(device='cpu').manual_seed(seed)
     cen = torch.rand((nao, 3), generator=g, dtype=torch.float64).to(h.torch_device)
-    width = 2.5 + 2.0 * torch.rand((nao,), generator=g, dtype=torch.float64).to(h.torch_device)   # in grid spacings
+    # widths fixed in units of the cell (2.5 .. 4.5 spacings of a 48^3 mesh): the pair space keeps its rank as the mesh grows
+    width = (n / 48.0) * (2.5 + 2.0 * torch.rand((nao,), generator=g, dtype=torch.float64)).to(h.torch_device)
     ax = torch.arange(n, dtype=torch.float64, device=h.torch_device) / n
     phi = h.empty((nao, ld))
     phi[:, ng:] = 0
