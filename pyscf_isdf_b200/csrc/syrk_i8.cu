@@ -702,12 +702,12 @@ int crt_moduli()
     return std::max(8, std::min(nm, (int)isdf_crt::NM_MAX));
 }
 
-// ISDF_SYRK_OVERLAP=1 (opt-in, residue form only): the element-wise kernels of chunk c+1 / c-1 run on a second
+// ISDF_SYRK_OVERLAP (default 1, residue form only): the element-wise kernels of chunk c+1 / c-1 run on a second
 // stream beside the tensor-core products of chunk c (double-buffered residue planes and residue output).
 bool overlap_requested()
 {
-    const char* e = getenv("ISDF_SYRK_OVERLAP");
-    return e && atoi(e) > 0 && crt_moduli() > 0;
+    const char* e = getenv("ISDF_SYRK_OVERLAP");      // default on since round 2 (bit-identical to the one-stream form); 0 = off
+    return (e ? atoi(e) > 0 : true) && crt_moduli() > 0;
 }
 
 int rows_padded(int n, int cl)
