@@ -222,8 +222,24 @@ int pick_lb(int nalloc, size_t budget) { return (int)std::max<size_t>(1, std::mi
 
 // forward 3-D transform of nvec real vectors into half spectra (spec[vec*lds + ...]);
 // xmode selects what the x pass fuses (0 plain, 1 sqrt(w coulG), 2 coulG*scale + inverse x)
+constexpr int MAX_GRID_VEC = 65535;       // the vector index is a grid y / z dimension
+
+int forward_passes_batch(isdf_handle* h, const Plans& P, const int* mesh, const double* in, long long ldin,
+                         int nvec, double2* spec, long long lds, int xmode, const CoulGeom& geo);
+
 int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double* in, long long ldin,
                    int nvec, double2* spec, long long lds, int xmode, const CoulGeom& geo)
+{
+    for (int v0 = 0; v0 < nvec; v0 += MAX_GRID_VEC) {
+        const int rc = forward_passes_batch(h, P, mesh, in + (long long)v0 * ldin, ldin, std::min(MAX_GRID_VEC, nvec - v0),
+                                            spec + (long long)v0 * lds, lds, xmode, geo);
+        if (rc) return rc;
+    }
+    return ISDF_OK;
+}
+
+int forward_passes_batch(isdf_handle* h, const Plans& P, const int* mesh, const double* in, long long ldin,
+                         int nvec, double2* spec, long long lds, int xmode, const CoulGeom& geo)
 {
     const int nx = mesh[0], ny = mesh[1], nz = mesh[2], nzh = nz / 2 + 1;
     cudaStream_t s = h->stream;
@@ -267,8 +283,22 @@ int forward_passes(isdf_handle* h, const Plans& P, const int* mesh, const double
 }
 
 // inverse y and z passes (x already inverted): spectra -> real vectors
+int inverse_yz_batch(isdf_handle* h, const Plans& P, const int* mesh, double2* spec, long long lds,
+                     int nvec, double* out, long long ldout, const CoulGeom& geo);
+
 int inverse_yz(isdf_handle* h, const Plans& P, const int* mesh, double2* spec, long long lds,
                int nvec, double* out, long long ldout, const CoulGeom& geo)
+{
+    for (int v0 = 0; v0 < nvec; v0 += MAX_GRID_VEC) {
+        const int rc = inverse_yz_batch(h, P, mesh, spec + (long long)v0 * lds, lds, std::min(MAX_GRID_VEC, nvec - v0),
+                                        out + (long long)v0 * ldout, ldout, geo);
+        if (rc) return rc;
+    }
+    return ISDF_OK;
+}
+
+int inverse_yz_batch(isdf_handle* h, const Plans& P, const int* mesh, double2* spec, long long lds,
+                     int nvec, double* out, long long ldout, const CoulGeom& geo)
 {
     const int nx = mesh[0], ny = mesh[1], nz = mesh[2], nzh = nz / 2 + 1;
     cudaStream_t s = h->stream;
@@ -403,6 +433,14 @@ extern "C" int isdf_fft_zy(isdf_handle* h, const double* in, long long ldin, int
     ARG_CHECK(h && in && h_mesh && spec && nvec > 0 && nxl > 0 && nxl <= h_mesh[0]);
     const int ny = h_mesh[1], nz = h_mesh[2], nzh = nz / 2 + 1;
     ARG_CHECK(ldin >= (long long)nxl * ny * nz && lds >= (long long)nxl * ny * nzh);
+    if (nvec > MAX_GRID_VEC) {               // the vector index is a grid dimension: batches of <= 65535
+        for (int v0 = 0; v0 < nvec; v0 += MAX_GRID_VEC) {
+            const int rcb = isdf_fft_zy(h, in + (long long)v0 * ldin, ldin, std::min(MAX_GRID_VEC, nvec - v0), nxl, h_mesh,
+                                        (double2*)spec + (long long)v0 * lds, lds);
+            if (rcb) return rcb;
+        }
+        return ISDF_OK;
+    }
     Plans P; int rc;
     if ((rc = make_plans(h, h_mesh, P))) return rc;
     cudaStream_t s = h->stream;
@@ -473,6 +511,14 @@ extern "C" int isdf_fft_x_coulomb(isdf_handle* h, void* Y, long long ldy, int nv
     ARG_CHECK(h && Y && h_mesh && h_a && nvec > 0 && ncl > 0 && col0 >= 0);
     const int nx = h_mesh[0];
     ARG_CHECK(col0 + ncl <= h_mesh[1] * (h_mesh[2] / 2 + 1) && ldy >= (long long)nx * ncl);
+    if (nvec > MAX_GRID_VEC) {
+        for (int v0 = 0; v0 < nvec; v0 += MAX_GRID_VEC) {
+            const int rcb = isdf_fft_x_coulomb(h, (double2*)Y + (long long)v0 * ldy, ldy, std::min(MAX_GRID_VEC, nvec - v0),
+                                               h_mesh, h_a, col0, ncl);
+            if (rcb) return rcb;
+        }
+        return ISDF_OK;
+    }
     Plans P; int rc;
     if ((rc = make_plans(h, h_mesh, P))) return rc;
     CoulGeom geo; fill_geom(geo, h_mesh, h_a, 1.0);

@@ -65,7 +65,9 @@ chol_diag_kernel(double* __restrict__ A, long long ld, int cb, double* __restric
     __syncthreads();
     if (tid < cb) {
         const int c = tid;
-        Vinv[c * CB + c] = 1.0 / S[c * LD + c];
+        const double dcc = S[c * LD + c];
+        if (!(fabs(dcc) > 0.0) || !isfinite(dcc)) atomicCAS(info, 0, block_id * CB + c + 1);   // zero / NaN pivot: reported by the caller
+        Vinv[c * CB + c] = 1.0 / dcc;
         for (int i = c - 1; i >= 0; --i) {
             double s = 0.0;
             for (int j = i + 1; j <= c; ++j) s += S[i * LD + j] * Vinv[j * CB + c];
@@ -278,6 +280,7 @@ extern "C" int isdf_fit_aux_from_factor(isdf_handle* h, double* Lt, long long ld
     const long long ldu = pad8(np);
     if ((rc = isdf_gather_cols(h, Lt, ldl, np, h_ip, np, w.U, ldu))) return rc;
     if ((rc = invert_diag_blocks(h, w.U, ldu, np, w.Vinv, w.info))) return rc;
+    if ((rc = check_info(h, w.info, "isdf_fit_aux_from_factor: zero or non-finite pivot in the selection factor"))) return rc;
     if ((rc = solve_upper(h, w.U, ldu, np, w.Vinv, Lt, ldl, ng, w.tmp))) return rc;
     CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FIT], s));
     h->ev_used[ISDF_STAGE_FIT] = true;
@@ -316,6 +319,7 @@ extern "C" int isdf_fit_aux_from_U(isdf_handle* h, double* U, long long ldu, int
     CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FIT], s));
     CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int) * 4, s));
     if ((rc = invert_diag_blocks(h, U, ldu, np, Vinv, info))) return rc;
+    if ((rc = check_info(h, info, "isdf_fit_aux_from_U: zero or non-finite pivot in the selection factor"))) return rc;
     if (ngl <= 4LL * np) {
         if ((rc = solve_upper_right(h, U, ldu, np, Vinv, Z, ldz, ngl, tmp))) return rc;
     } else {

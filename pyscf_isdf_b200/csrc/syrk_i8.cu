@@ -704,10 +704,13 @@ int crt_moduli()
 
 // ISDF_SYRK_OVERLAP (default 1, residue form only): the element-wise kernels of chunk c+1 / c-1 run on a second
 // stream beside the tensor-core products of chunk c (double-buffered residue planes and residue output).
-bool overlap_requested()
+// The second set of buffers is only taken while it stays small: n <= 16384 rows (18 GB in all for C64's
+// n = 12480; Si216's n = 42120 would need 100 GB and runs the one-stream form).
+constexpr int OVERLAP_MAX_ROWS = 16384;
+bool overlap_requested(int n)
 {
     const char* e = getenv("ISDF_SYRK_OVERLAP");      // default on since round 2 (bit-identical to the one-stream form); 0 = off
-    return (e ? atoi(e) > 0 : true) && crt_moduli() > 0;
+    return (e ? atoi(e) > 0 : true) && crt_moduli() > 0 && n <= OVERLAP_MAX_ROWS;
 }
 
 int rows_padded(int n, int cl)
@@ -771,7 +774,7 @@ extern "C" size_t isdf_syrk_i8_ws_bytes(int n, long long K, int nslices)
     const int cl = cluster_size();
     const int tr = (n + TM - 1) / TM, tc = (n + TN - 1) / TN;
     const int nm = crt_moduli();
-    const size_t nbuf = overlap_requested() ? 2 : 1;
+    const size_t nbuf = overlap_requested(n) ? 2 : 1;
     const size_t crt_extra = nm ? nbuf * align_up((size_t)nm * (size_t)n * align_up((size_t)n, 16), 1024) : 0;    // residues of the products
     return crt_extra + nbuf * align_up((size_t)std::max(nslices, nm) * (size_t)rows_padded(n, cl) * ((c.kc_full / BKB | 1) * BKB), 1024) +
            align_up((size_t)(c.nchunks + 1) * n * sizeof(double), 256) + align_up((size_t)c.nchunks * sizeof(double), 256) +
@@ -798,7 +801,7 @@ extern "C" int isdf_syrk_i8(isdf_handle* h, int n, long long K, const double* A,
     const long long plane_stride = rb_stride * (nrows_pad / TM);
     char* base = (char*)align_up((size_t)ws, 1024);
     const int nm_max = crt_moduli();
-    const bool overlap = overlap_requested();
+    const bool overlap = overlap_requested(n);
     int8_t* planes = (int8_t*)base;
     base += align_up((size_t)std::max(nslices, nm_max) * plane_stride, 1024);
     int8_t* planes2 = planes;                              // second set of residue planes (overlap form)
