@@ -12,8 +12,17 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from pyscf_isdf_b200 import _lib
 
 
+def hbm_peak():
+    import json
+    try:
+        return float(json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'MEASURED_PEAKS.json')))['hbm_gbs'])
+    except (OSError, ValueError, KeyError):
+        return 6537.0
+
+
 def main():
     h = _lib.Handle(0)
+    peak = hbm_peak()
     a = np.eye(3) * 13.0
     cases = (([35] * 3, 1560), ([71] * 3, 1024), ([96] * 3, 512), ([108] * 3, 384))
     if len(sys.argv) > 1:                       # e.g. `fft_bench.py 71 64` -> only those meshes (any size)
@@ -31,8 +40,8 @@ def main():
             torch.cuda.synchronize()
             best = min(best, h.stage_ms(_lib.STAGE_FFT))
         byt = nvec * (8.0 * ng + 16.0 * ngh)
-        print('mesh %3d^3 nvec %5d: fft %8.3f ms  algorithmic %.1f GB -> %.0f GB/s (%.1f%% of 6458)'
-              % (mesh[0], nvec, best, byt / 1e9, byt / best / 1e6, 100 * byt / best / 1e6 / 6458), flush=True)
+        print('mesh %3d^3 nvec %5d: fft %8.3f ms  algorithmic %.1f GB -> %.0f GB/s (%.1f%% of %.0f)'
+              % (mesh[0], nvec, best, byt / 1e9, byt / best / 1e6, 100 * byt / best / 1e6 / peak, peak), flush=True)
         del z, W
 
 
