@@ -263,6 +263,15 @@ int isdf_get_jk_static(isdf_handle* h, const double* X, const double* W,
                        const double* dm, int nset, int nao, int np,
                        int with_j, int with_k, double* vj, double* vk);
 
+/* Non-local GTH projectors of FFTDF.get_pp (pyscf/pbc/df/fft.py:86-141), the part that scales with the number of atoms:
+ * out[r, g] = tab[r, g] * exp(sign * i G_g . R) for one atom at R (host, 3 doubles) from its species' table
+ * tab[nrow, ldt] (device; real plane and optional imaginary plane) over ng reciprocal vectors Gv[ng, 3] (device).
+ * sign = -1: AO transforms times SI (fft.py:100, ft_ao phase); sign = +1: projectors times conj(SI) (fft.py:129).
+ * The contraction over G that follows is isdf_dgemm on the re / im planes. */
+int isdf_phase_expand(isdf_handle* h, const double* tab_re, const double* tab_im, long long ldt, int nrow,
+                      const double* Gv, long long ng, const double* h_R, double sign,
+                      double* out_re, double* out_im, long long ldo);
+
 /* Generic FP64 GEMM used by every stage (exposed for tests / bench):
  * C[m,n] = epi( Cin[m,n] -/+ sum_k opA(k,m) opB(k,n) ), one FMA chain per
  * element in ascending k.  a_kmajor: A[k*lda+m] else A[m*lda+k]; same for B.

@@ -82,6 +82,7 @@ SIGNATURES = {
                                       c_int, c_int, c_vp, c_vp, c_vp, c_sz]),
     'isdf_get_jk_static_max_bytes': (c_sz, []),
     'isdf_get_jk_static': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
+    'isdf_phase_expand': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_vp, c_ll, c_vp, c_dbl, c_vp, c_vp, c_ll]),
     'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
                            c_vp, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_int, c_int]),
     'isdf_set_gemm_tile': (c_int, [c_vp, c_int]),
@@ -339,6 +340,13 @@ class Handle:
                                    c_vp(vj.data_ptr()) if vj is not None else None,
                                    c_vp(vk.data_ptr()) if vk is not None else None,
                                    c_vp(ws.data_ptr()), ws.numel()))
+
+    def phase_expand(self, tab_re, tab_im, ldt, nrow, Gv, ng, R, sign, out_re, out_im, ldo):
+        R = np.ascontiguousarray(R, dtype=np.float64)
+        check(self.lib.isdf_phase_expand(self.h, c_vp(tab_re.data_ptr()),
+                                         c_vp(tab_im.data_ptr()) if tab_im is not None else None, ldt, nrow,
+                                         c_vp(Gv.data_ptr()), ng, hptr(R), float(sign),
+                                         c_vp(out_re.data_ptr()), c_vp(out_im.data_ptr()), ldo))
 
     def get_jk_static(self, X, W, dm, nset, nao, npts, with_j, with_k, vj, vk):
         """isdf_get_jk with the library's built-in scratch array: allocates nothing (include/isdf_b200.h)."""

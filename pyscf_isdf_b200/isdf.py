@@ -438,12 +438,14 @@ class ISDF:
         self._check_gamma(kpts)
         return self.potential_matrix_device(pseudo.pp_loc_on_grid(self.cell, self.mesh)).cpu().numpy()
 
-    def get_pp_nl(self, kpts=None):
-        """Non-local projector part of FFTDF.get_pp (pyscf/pbc/df/fft.py:86-141).  The reference
-        evaluates it on the CPU in reciprocal space from analytic Fourier transforms of the AOs
-        (SURVEY 8f row 2 keeps it there); so does this: pyscf_isdf_b200/pseudo.py on the host,
-        once per geometry.  With several ranks each takes a contiguous range of reciprocal vectors
-        and the projector-AO overlaps are summed over ranks before h_ij is applied."""
+    def get_pp_nl(self, kpts=None, on_device=True):
+        """Non-local projector part of FFTDF.get_pp (pyscf/pbc/df/fft.py:86-141), in reciprocal space from
+        analytic Fourier transforms of the AOs as the reference has it.  The per-species radial x angular
+        tables are closed forms evaluated on the host per batch of G vectors; the structure-factor phases
+        of every atom and the [projectors x G] . [G x nao] contraction run on the device
+        (`isdf_phase_expand` + `isdf_dgemm`; `on_device=False` keeps everything on the host like the
+        reference).  With several ranks each takes a contiguous range of reciprocal vectors and the
+        projector-AO overlaps are summed over ranks before h_ij is applied."""
         from . import pseudo
         self._check_gamma(kpts)
         cell = self.cell
@@ -453,7 +455,16 @@ class ISDF:
         ng = int(np.prod(self.mesh))
         comm = self.comm
         rank, size = (comm.rank, comm.size) if comm is not None else (0, 1)
-        Z = pseudo.pp_nl_overlaps(cell, ng * rank // size, ng * (rank + 1) // size, self.mesh)
+        g0, g1 = ng * rank // size, ng * (rank + 1) // size
+        if on_device:
+            import torch
+            zre, zim = pseudo.pp_nl_overlaps_device(cell, self.handle, g0, g1, self.mesh)
+            buf = torch.stack([zre, zim])
+            if size > 1:
+                comm.all_reduce_sum(buf)
+            zz = buf.cpu().numpy()
+            return pseudo.pp_nl_from_overlaps(cell, zz[0] + 1j * zz[1])
+        Z = pseudo.pp_nl_overlaps(cell, g0, g1, self.mesh)
         if size > 1:
             buf = self.handle.from_host(np.stack([Z.real, Z.imag]))
             comm.all_reduce_sum(buf)

@@ -264,6 +264,67 @@ def pp_nl_overlaps(cell, g0=0, g1=None, mesh=None, max_bytes=1 << 29):
     return Z
 
 
+def pp_nl_overlaps_device(cell, h, g0=0, g1=None, mesh=None, batch=32768):
+    """pp_nl_overlaps with the part that scales with the number of atoms on the device: per batch of G vectors the
+    host prepares the per-SPECIES tables (closed forms above), `isdf_phase_expand` turns them into every atom's
+    rows conj(SI_a) P(G) and SI_a ft_ao(G) (real and imaginary planes), and four `isdf_dgemm` calls accumulate
+    Z = spg . aoG^T over the batches (the chain continues through Cin).  Returns two device tensors
+    (Z_re, Z_im) of shape [nproj_total, nao], the sum over the reciprocal vectors [g0, g1)."""
+    from . import _lib
+    mesh = cell.mesh if mesh is None else mesh
+    Gv = cell.get_Gv(mesh)
+    g1 = len(Gv) if g1 is None else g1
+    coords = cell.atom_coords()
+    nao = cell.nao_nr()
+    syms = [cell.atom_symbol(ia) for ia in range(cell.natm)]
+    pps = [cell._pseudo_for(s) for s in syms]
+    first = {}
+    for ia, sym in enumerate(syms):
+        first.setdefault(sym, ia)
+    nproj = [sum(nl * (2 * l + 1) for l, (_, nl, _) in enumerate(pp['nonlocal_'])) if pp is not None else 0 for pp in pps]
+    nao_atom = [int(sum((2 * cell._bas[ib, 1] + 1) * cell._bas[ib, 3] for ib in np.where(cell._bas[:, 0] == ia)[0]))
+                for ia in range(cell.natm)]
+    ao_off = np.concatenate([[0], np.cumsum(nao_atom)])
+    p_off = np.concatenate([[0], np.cumsum(nproj)])
+    ntot = int(p_off[-1])
+    Zre, Zim = h.zeros((max(ntot, 1), nao)), h.zeros((max(ntot, 1), nao))
+    if ntot == 0 or g1 <= g0:
+        return Zre[:ntot], Zim[:ntot]
+    ld = _lib.pad8(min(batch, g1 - g0))
+    A_re, A_im = h.empty((nao, ld)), h.empty((nao, ld))
+    S_re, S_im = h.empty((ntot, ld)), h.empty((ntot, ld))
+    for b0 in range(g0, g1, batch):
+        b1 = min(b0 + batch, g1)
+        n = b1 - b0
+        q = np.ascontiguousarray(Gv[b0:b1])
+        qq = np.einsum('gx,gx->g', q, q)
+        d_G = h.from_host(q)
+        tabs = {}
+        for sym, ia in first.items():
+            ft = np.zeros((nao_atom[ia], ld), dtype=np.complex128)
+            ft[:, :n] = species_ft_shells(cell, ia, q, qq)
+            pr = None
+            if nproj[ia]:
+                pr = np.zeros((nproj[ia], ld))
+                pr[:, :n] = species_projectors(pps[ia], q, qq)
+            tabs[sym] = (h.from_host(np.ascontiguousarray(ft.real)), h.from_host(np.ascontiguousarray(ft.imag)),
+                         h.from_host(pr) if pr is not None else None)
+        for ia, sym in enumerate(syms):
+            t_re, t_im, t_pr = tabs[sym]
+            h.phase_expand(t_re, t_im, ld, nao_atom[ia], d_G, n, coords[ia], -1.0,
+                           A_re[ao_off[ia]:], A_im[ao_off[ia]:], ld)                       # ft_ao * SI
+            if nproj[ia]:
+                h.phase_expand(t_pr, None, ld, nproj[ia], d_G, n, coords[ia], +1.0,
+                               S_re[p_off[ia]:], S_im[p_off[ia]:], ld)                     # P * conj(SI)
+        # Z += (S_re + i S_im) (A_re + i A_im)^T over this batch
+        h.dgemm(ntot, nao, n, S_re, ld, 0, A_re, ld, 0, Zre, nao, Cin=Zre, ldcin=nao)
+        h.dgemm(ntot, nao, n, S_im, ld, 0, A_im, ld, 0, Zre, nao, Cin=Zre, ldcin=nao, neg=1)
+        h.dgemm(ntot, nao, n, S_re, ld, 0, A_im, ld, 0, Zim, nao, Cin=Zim, ldcin=nao)
+        h.dgemm(ntot, nao, n, S_im, ld, 0, A_re, ld, 0, Zim, nao, Cin=Zim, ldcin=nao)
+        h.synchronize()                               # the species tables of this batch are temporaries
+    return Zre, Zim
+
+
 def pp_nl_from_overlaps(cell, Z):
     """vppnl[nao, nao] = sum_atoms sum_l sum_m  Z^H h_l Z / vol^2  (fft.py:131-139; each ft_ao carries
     1/sqrt(vol) there and the result another 1/vol); real part at the Gamma point (fft.py:144-145)."""

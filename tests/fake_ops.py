@@ -163,6 +163,14 @@ class FakeOps:
         for i in range(nset):
             vj[i] = torch.from_numpy(weight * (P * _np(vR)[i, :ngl]).dot(P.T))
 
+    def phase_expand(self, tab_re, tab_im, ldt, nrow, Gv, ng, R, sign, out_re, out_im, ldo):
+        """isdf_phase_expand: out = tab * exp(sign i G.R) as real / imaginary planes."""
+        t = _np(tab_re)[:nrow, :ng] + (1j * _np(tab_im)[:nrow, :ng] if tab_im is not None else 0.0)
+        ph = np.exp(1j * sign * _np(Gv)[:ng].dot(np.asarray(R, dtype=float)))
+        z = t * ph[None, :]
+        out_re[:nrow, :ng] = torch.from_numpy(np.ascontiguousarray(z.real))
+        out_im[:nrow, :ng] = torch.from_numpy(np.ascontiguousarray(z.imag))
+
     def index(self, idx):
         return torch.as_tensor(np.asarray(idx, dtype=np.int64))
 

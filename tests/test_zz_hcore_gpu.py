@@ -88,3 +88,25 @@ def test_sharded_local_potential():
     for r in range(n):
         assert abs(out[r] - vpp0).max() < 1e-10
         assert abs(full[r] - (vpp0 + vnl0)).max() < 1e-10
+
+
+def test_nonlocal_projectors_device_equals_host_with_p_channels_and_batches():
+    """Si carries two s projectors and a p projector: the device form (isdf_phase_expand + isdf_dgemm, several
+    batches of G vectors, a sub-range as a rank would take it) against the host form, and the matrix against the oracle."""
+    from pyscf_isdf_b200 import pseudo
+    a = 5.431
+    frac = np.array([[0, 0, 0], [.25, .25, .25], [.5, .5, 0], [.75, .75, .25]])
+    cell = Cell(atom=[('Si', tuple(r)) for r in frac * a] + [('C', (0.5 * a, 0.1 * a, 0.6 * a))],
+                a=np.eye(3) * a, basis='gth-dzvp', pseudo='gth-pade', mesh=[13, 12, 11]).build()
+    mydf = ISDF(cell, c=4)
+    h = mydf.handle
+    ng = int(np.prod(cell.mesh))
+    for g0, g1 in ((0, ng), (ng // 3, 2 * ng // 3 + 5)):
+        Z0 = pseudo.pp_nl_overlaps(cell, g0, g1, cell.mesh)
+        zre, zim = pseudo.pp_nl_overlaps_device(cell, h, g0, g1, cell.mesh, batch=257)
+        Z1 = zre.cpu().numpy() + 1j * zim.cpu().numpy()
+        assert Z1.shape == Z0.shape
+        assert abs(Z1 - Z0).max() < 1e-11 * max(1.0, abs(Z0).max())
+    vnl0 = _ref_nl(cell)
+    assert abs(mydf.get_pp_nl() - vnl0).max() < 1e-10
+    assert abs(mydf.get_pp_nl(on_device=False) - vnl0).max() < 1e-10
