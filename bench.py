@@ -45,7 +45,7 @@ def parse_args():
     ap.add_argument('--no-e2e', action='store_true', help='exploratory runs only: skip the host-API leg')
     ap.add_argument('--no-parity', action='store_true', help='skip the C8-vs-oracle parity block (N = 1 only)')
     ap.add_argument('--no-extra', action='store_true',
-                    help='skip the one-off runs of the larger configs (h2o32 at >= 4 GPUs, si216 at 8 GPUs)')
+                    help='skip the one-off runs of the larger configs (h2o32 at every N, si216 at 8 GPUs)')
     ap.add_argument('--exxdiv', default='ewald', choices=['ewald', 'none'],
                     help="exchange divergence treatment of the timed J/K: 'ewald' is the pbc.scf.RHF default")
     ap.add_argument('--xc', default=None,
@@ -474,7 +474,8 @@ def extra_workload(name, args, local, comm, world, torch, dist):
                'n_gpus': world, 'build_s': float(tt[0]) / 1e3, 'jk_s': float(tt[1]) / 1e3,
                'value': (float(tt[0]) + float(tt[1])) / 1e3, 'unit': 's', 'timed': '1 warm-up build, 1 timed build, median of 5 J/K; max over ranks',
                'stages_ms': {k: float(v) for k, v in mydf.timings.items() if k.endswith('_ms')},
-               'fp64_gemm_tflops_rank0': gflops / (gms * 1e-3) / 1e12 if gms > 0 else None}
+               'fp64_gemm_tflops_rank0': gflops / (gms * 1e-3) / 1e12 if gms > 0 else None,
+               'aliased_build_buffers': bool(getattr(mydf, 'timings_flags', {}).get('aliased_arenas', False))}
         mydf.release_buffers()
         del mydf
         torch.cuda.empty_cache()
@@ -623,8 +624,8 @@ def run_b200(args):
         headline = (mydf.n_ip, mydf.timings)
         mydf.reset(); mydf.release_buffers()
         torch.cuda.empty_cache()
-        if world >= 4:
-            extra['h2o32'] = extra_workload('h2o32', args, local, comm, world, torch, dist)
+        # config 3 fits one GPU since round 2 (the spectra overwrite the factor rows: one 80 GB arena instead of two)
+        extra['h2o32'] = extra_workload('h2o32', args, local, comm, world, torch, dist)
         if world >= 8:
             extra['si216'] = extra_workload('si216', args, local, comm, world, torch, dist)
         mydf.n_ip = headline[0]

@@ -153,18 +153,37 @@ def build(mydf, comm, ops=None):
     # size owned by the ISDF object: handing tens of GB back to the caching allocator between
     # rebuilds lets it split the blocks for small requests and map new ones (seen as 0.2-0.5 s
     # stalls in the AO / selection / FFT stages of later builds).
-    nbig = max(npts * ldl, 2 * npts * nx * part.ncol_local(r))
+    ncl_r = part.ncol_local(r)
+    n_lt, n_y = npts * ldl, 2 * npts * nx * ncl_r            # doubles: factor rows, weighted spectra of this rank
+    nbig = max(n_lt, n_y)
+    # One arena or two?  Two (factor rows and spectra side by side) is the fast layout.  When that does not fit the
+    # device next to the other buffers of the build, the spectra overwrite the factor rows as they are consumed
+    # (`alias`): the rows are placed so that spectrum row v ends before factor row v+1 starts (right-aligned when
+    # a spectrum row is the longer one), and every batch goes through a bounce buffer.
+    total = ops.device_mem_bytes() if hasattr(ops, 'device_mem_bytes') else 1 << 62
+    wmode = str(getattr(mydf, 'wgemm', 'i8'))
+    planes = int(wmode.split(':')[1]) if ':' in wmode else 8
+    ws_w = lib.isdf_syrk_i8_ws_bytes(npts, 2 * nx * ncl_r, planes) if (wmode.startswith('i8') and hasattr(lib, 'isdf_syrk_i8_ws_bytes')) else 0
+    other = 8 * (nao * ldl + 3 * npts * _lib.pad8(npts)) + ws_w + (3 << 30)
+    alias = os.environ.get('ISDF_ALIAS_ARENAS')
+    alias = (16 * nbig + other > 0.92 * total) if alias is None else (alias == '1')
     arena = getattr(mydf, '_arena', None)
-    if arena is None or arena[0].numel() < nbig:
-        mydf._arena = arena = None                # release the old pair before mapping a larger one
-        arena = (ops.empty((nbig,)), ops.empty((nbig,)))
+    if arena is None or arena[0].numel() < nbig or (arena[1] is None) != alias:
+        mydf._arena = arena = None                # release the old buffers before mapping larger ones
+        arena = (ops.empty((nbig,)), None if alias else ops.empty((nbig,)))
         # kept by the object across reset()/build() cycles unless that would pin most of the device
-        total = ops.device_mem_bytes() if hasattr(ops, 'device_mem_bytes') else 1 << 62
-        if getattr(mydf, 'keep_buffers', True) and 16 * nbig <= 0.45 * total:
+        if getattr(mydf, 'keep_buffers', True) and (8 if alias else 16) * nbig <= 0.45 * total:
             mydf._arena = arena
     big_lt, big_y = arena
     del arena
-    Lt = big_lt[:npts * ldl].view(npts, ldl)
+    if alias:
+        big_y = big_lt
+        lt_off = big_lt.numel() - n_lt if 2 * nx * ncl_r >= ldl else 0
+        if 2 * nx * ncl_r < ldl and n_y > n_lt:
+            raise RuntimeError('aliased build buffers: inconsistent row sizes')
+    else:
+        lt_off = 0
+    Lt = big_lt[lt_off:lt_off + n_lt].view(npts, ldl)
     ldu = _lib.pad8(npts)
     U = ops.zeros((npts, ldu))
     plan = ops.select_create(nao, ngl, g0, ng, npts)
@@ -237,6 +256,7 @@ def build(mydf, comm, ops=None):
     ldy = nx * ncl
     Yr = big_y[:2 * npts * ldy].view(npts, 2 * ldy)
     Y = ops.as_complex(Yr)
+    mydf.timings_flags = {'aliased_arenas': bool(alias)}
     # vectors per all-to-all batch: computed from rank-independent maxima so that every rank
     # runs the same number of exchanges
     nxl_max = max(part.nx_local(q) for q in range(N))
@@ -247,10 +267,16 @@ def build(mydf, comm, ops=None):
         spec = ops.empty_complex((vb * nxl * ncols,))
         send = ops.empty_complex((vb * nxl * ncols,))
         recv = ops.empty_complex((vb * nx * ncl,))
+    elif alias:
+        spec = ops.empty_complex((vb * ldy,))
     for v0 in range(0, npts, vb):
         nv = min(vb, npts - v0)
         if N == 1:
-            ops.fft_zy(Lt[v0:], ldl, nv, nxl, mesh, Y[v0:], ldy)
+            if alias:      # bounce: the batch's spectra land on its own (already transformed) factor rows
+                ops.fft_zy(Lt[v0:], ldl, nv, nxl, mesh, spec, ldy)
+                Y[v0:v0 + nv].copy_(spec[:nv * ldy].view(nv, ldy))
+            else:
+                ops.fft_zy(Lt[v0:], ldl, nv, nxl, mesh, Y[v0:], ldy)
             continue
         if prof:
             prof = ops.timer()
@@ -278,9 +304,7 @@ def build(mydf, comm, ops=None):
         acc.update(prof.times)
     ev.mark('fft_ms')
     W = ops.empty((npts, npts))
-    wmode = str(getattr(mydf, 'wgemm', 'i8'))
     if wmode.startswith('i8'):
-        planes = int(wmode.split(':')[1]) if ':' in wmode else 8
         ops.syrk_i8(npts, 2 * nx * ncl, Yr, 2 * ldy, W, npts,
                     alpha=cell.vol / (float(ng) * float(ng)), nslices=planes)
     else:

@@ -121,10 +121,20 @@ def test_single_rank_driver_matches_oracle(fit):
     _check(_run_rank(SerialComm(), fit=fit))
 
 
-def _worker(rank, world, port, q):
+def test_single_rank_driver_with_aliased_build_buffers(monkeypatch):
+    """ISDF_ALIAS_ARENAS=1: the spectra overwrite the factor rows as they are consumed (what a build takes when
+    two arenas do not fit the device); same result."""
+    from pyscf_isdf_b200.dist import SerialComm
+    monkeypatch.setenv('ISDF_ALIAS_ARENAS', '1')
+    _check(_run_rank(SerialComm(), fit='implicit'))
+
+
+def _worker(rank, world, port, q, alias=False):
     import torch.distributed as dist
     os.environ['MASTER_ADDR'] = '127.0.0.1'
     os.environ['MASTER_PORT'] = str(port)
+    if alias:
+        os.environ['ISDF_ALIAS_ARENAS'] = '1'
     # several small all-to-all batches: their count must not depend on the rank's slab size
     os.environ['ISDF_A2A_BATCH_BYTES'] = '20000'
     dist.init_process_group('gloo', rank=rank, world_size=world)
@@ -135,8 +145,8 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize('world', [2, 3])
-def test_gloo_ranks_match_oracle(world):
+@pytest.mark.parametrize('world,alias', [(2, False), (3, False), (2, True)])
+def test_gloo_ranks_match_oracle(world, alias):
     import torch.multiprocessing as mp
     s = socket.socket()
     s.bind(('127.0.0.1', 0))
@@ -144,7 +154,7 @@ def test_gloo_ranks_match_oracle(world):
     s.close()
     ctx = mp.get_context('spawn')
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, alias)) for r in range(world)]
     for p in procs:
         p.start()
     got = {}
