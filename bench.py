@@ -65,12 +65,16 @@ class ClockSampler:
         self.index = index
         self.rows = []
         self.proc = None
+        # sampling period (ms); ISDF_BENCH_SMI_MS=0 switches the sampler off (diagnostics only: the contract wants it on)
+        self.period = int(os.environ.get('ISDF_BENCH_SMI_MS', '500'))
 
     def start(self):
+        if self.period <= 0:
+            return self
         try:
             self.proc = subprocess.Popen(
                 ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
-                 '--format=csv,noheader,nounits', '-lms', '200'],
+                 '--format=csv,noheader,nounits', '-lms', str(self.period)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()

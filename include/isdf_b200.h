@@ -272,6 +272,11 @@ int isdf_phase_expand(isdf_handle* h, const double* tab_re, const double* tab_im
                       const double* Gv, long long ng, const double* h_R, double sign,
                       double* out_re, double* out_im, long long ldo);
 
+/* out[cols, rows] = in[rows, cols]^T (row strides ldout, ldin; no overlap): the re-orientation between the two
+ * triangular solves of the congruence W = U^-1 M U^-T (no reference counterpart: NumPy's `.T`). */
+int isdf_transpose(isdf_handle* h, const double* in, long long ldin, int rows, int cols,
+                   double* out, long long ldout);
+
 /* Generic FP64 GEMM used by every stage (exposed for tests / bench):
  * C[m,n] = epi( Cin[m,n] -/+ sum_k opA(k,m) opB(k,n) ), one FMA chain per
  * element in ascending k.  a_kmajor: A[k*lda+m] else A[m*lda+k]; same for B.

@@ -83,6 +83,7 @@ SIGNATURES = {
     'isdf_get_jk_static_max_bytes': (c_sz, []),
     'isdf_get_jk_static': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     'isdf_phase_expand': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_vp, c_ll, c_vp, c_dbl, c_vp, c_vp, c_ll]),
+    'isdf_transpose': (c_int, [c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_ll]),
     'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
                            c_vp, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_int, c_int]),
     'isdf_set_gemm_tile': (c_int, [c_vp, c_int]),
@@ -347,6 +348,10 @@ class Handle:
                                          c_vp(tab_im.data_ptr()) if tab_im is not None else None, ldt, nrow,
                                          c_vp(Gv.data_ptr()), ng, hptr(R), float(sign),
                                          c_vp(out_re.data_ptr()), c_vp(out_im.data_ptr()), ldo))
+
+    def transpose(self, src, ldin, rows, cols, out, ldout):
+        """out[cols, rows] = src[rows, cols]^T on the handle's stream (csrc/fit.cu)."""
+        check(self.lib.isdf_transpose(self.h, c_vp(src.data_ptr()), ldin, rows, cols, c_vp(out.data_ptr()), ldout))
 
     def get_jk_static(self, X, W, dm, nset, nao, npts, with_j, with_k, vj, vk):
         """isdf_get_jk with the library's built-in scratch array: allocates nothing (include/isdf_b200.h)."""

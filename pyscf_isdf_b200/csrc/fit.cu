@@ -233,6 +233,45 @@ int check_info(isdf_handle* h, int* d_info, const char* what)
 
 }  // namespace
 
+namespace {
+
+// out[c, r] = in[r, c] through a 32 x 33 shared-memory tile (both sides coalesced)
+__global__ void transpose_kernel(const double* __restrict__ in, long long ldin, int rows, int cols,
+                                 double* __restrict__ out, long long ldout)
+{
+    __shared__ double tile[32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        if (r < rows && c < cols) tile[i][threadIdx.x] = in[(long long)r * ldin + c];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (r < rows && c < cols) out[(long long)c * ldout + r] = tile[threadIdx.x][i];
+    }
+}
+
+}  // namespace
+
+// out[cols, rows] (row stride ldout) = in[rows, cols]^T (row stride ldin); used between the two triangular
+// solves of the congruence W = U^-1 M U^-T and for the final W[cols, :] block (pyscf_isdf_b200/dist.py)
+extern "C" int isdf_transpose(isdf_handle* h, const double* in, long long ldin, int rows, int cols,
+                              double* out, long long ldout)
+{
+    ARG_CHECK(h && in && out && rows >= 0 && cols >= 0 && ldin >= cols && ldout >= rows && in != out);
+    if (rows == 0 || cols == 0) return ISDF_OK;
+    dim3 blk(32, 8);
+    for (int r0 = 0; r0 < rows; r0 += 32 * 65535) {            // grid.y limit
+        const int nr = std::min(rows - r0, 32 * 65535);
+        dim3 grd((cols + 31) / 32, (nr + 31) / 32);
+        transpose_kernel<<<grd, blk, 0, h->stream>>>(in + (long long)r0 * ldin, ldin, nr, cols, out + r0, ldout);
+    }
+    CUDA_TRY(cudaGetLastError());
+    h->other_launches++;
+    return ISDF_OK;
+}
+
 extern "C" size_t isdf_fit_aux_ws_bytes(int nao, long long ng, int np)
 {
     FitWs w;

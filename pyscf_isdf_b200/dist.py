@@ -168,9 +168,9 @@ def build(mydf, comm, ops=None):
     alias = os.environ.get('ISDF_ALIAS_ARENAS')
     alias = (16 * nbig + other > 0.92 * total) if alias is None else (alias == '1')
     arena = getattr(mydf, '_arena', None)
-    if arena is None or arena[0].numel() < nbig or (arena[1] is None) != alias:
+    if arena is None or arena[0].numel() < nbig + 32 or (arena[1] is None) != alias:
         mydf._arena = arena = None                # release the old buffers before mapping larger ones
-        arena = (ops.empty((nbig,)), None if alias else ops.empty((nbig,)))
+        arena = (ops.empty((nbig + 32,)), None if alias else ops.empty((nbig + 32,)))
         # kept by the object across reset()/build() cycles unless that would pin most of the device
         if getattr(mydf, 'keep_buffers', True) and (8 if alias else 16) * nbig <= 0.45 * total:
             mydf._arena = arena
@@ -178,7 +178,8 @@ def build(mydf, comm, ops=None):
     del arena
     if alias:
         big_y = big_lt
-        lt_off = big_lt.numel() - n_lt if 2 * nx * ncl_r >= ldl else 0
+        # right-aligned (to 256 bytes: the GEMMs want their rows on sector boundaries) when a spectrum row is the longer one
+        lt_off = (nbig - n_lt + 31) // 32 * 32 if 2 * nx * ncl_r >= ldl else 0
         if 2 * nx * ncl_r < ldl and n_y > n_lt:
             raise RuntimeError('aliased build buffers: inconsistent row sizes')
     else:
@@ -243,12 +244,16 @@ def build(mydf, comm, ops=None):
     ev.mark('fit_ms')
 
     # X = Phi[:, ip]: every rank contributes the pivots that live in its slab
-    X = ops.zeros((nao, npts))
     mine = np.nonzero((ip >= g0) & (ip < g1))[0]
-    if len(mine):
-        tmp = ops.empty((nao, len(mine)))
-        ops.gather_cols(phi, ldl, nao, ip[mine] - g0, tmp, len(mine))
-        X[:, ops.index(mine)] = tmp
+    if len(mine) == npts:                       # one rank owns every pivot: gather straight into X
+        X = ops.empty((nao, npts))
+        ops.gather_cols(phi, ldl, nao, ip - g0, X, npts)
+    else:
+        X = ops.zeros((nao, npts))
+        if len(mine):
+            tmp = ops.empty((nao, len(mine)))
+            ops.gather_cols(phi, ldl, nao, ip[mine] - g0, tmp, len(mine))
+            X[:, ops.index(mine)] = tmp
     comm.all_reduce_sum(X)
 
     # stage 4: Coulomb metric W through the slab-decomposed FFT
@@ -351,13 +356,15 @@ def _congruence_solve(ops, comm, part, U, ldu, M, npts):
     off = [int(x) for x in part.ip_off]
     p0, p1 = off[r], off[r + 1]
     ncr = p1 - p0                                       # may be 0 on a rank when Np < 8 N: still take part
-    Z1 = M[:, p0:p1].contiguous()                       # [Np, ncr]
+    Z1 = ops.empty((npts, ncr))
+    if ncr:
+        Z1.copy_(M[:, p0:p1])                           # column block of M: a pitched device-to-device copy
     del M
     if ncr:
         ops.fit_aux_from_U(U, ldu, npts, Z1, ncr, ncr)  # Z1 = U^-1 M[:, cols]
     R = ops.empty((npts, ncr))
     if N == 1:
-        R.copy_(Z1.t())
+        ops.transpose(Z1, ncr, npts, ncr, R, ncr)       # R = Z1^T (square here: ncr == Np)
     else:
         recv = ops.empty((npts * ncr,))
         splits = [(off[s + 1] - off[s]) * ncr for s in range(N)]
@@ -365,14 +372,17 @@ def _congruence_solve(ops, comm, part, U, ldu, M, npts):
         o = 0
         for s in range(N):
             ncs = off[s + 1] - off[s]
-            if ncs and ncr:
-                R[off[s]:off[s + 1]] = recv[o:o + ncr * ncs].view(ncr, ncs).t()
+            if ncs and ncr:                             # rank s sent its Z1[p0:p1, :] = [ncr, ncs]; R[off_s:off_s+ncs, :] is its transpose
+                ops.transpose(recv[o:o + ncr * ncs], ncs, ncr, ncs, R[off[s]:off[s + 1]], ncr)
             o += ncr * ncs
         del recv
     del Z1
     if ncr:
         ops.fit_aux_from_U(U, ldu, npts, R, ncr, ncr)   # R = U^-1 (U^-1 M)^T[:, cols] = W[:, cols]
-    return R.t().contiguous()                           # W[cols, :] by symmetry
+    Wrows = ops.empty((ncr, npts))
+    if ncr:
+        ops.transpose(R, ncr, npts, ncr, Wrows, npts)   # W[cols, :] by symmetry
+    return Wrows
 
 
 def get_jk_device(mydf, comm, d_dm, with_j=True, with_k=True, ops=None, occ=None):

@@ -171,6 +171,12 @@ class FakeOps:
         out_re[:nrow, :ng] = torch.from_numpy(np.ascontiguousarray(z.real))
         out_im[:nrow, :ng] = torch.from_numpy(np.ascontiguousarray(z.imag))
 
+    def transpose(self, src, ldin, rows, cols, out, ldout):
+        """isdf_transpose: out[cols, rows] = src[rows, cols]^T."""
+        a = _np(src).reshape(-1)[:rows * ldin].reshape(rows, ldin)[:, :cols]
+        o = _np(out).reshape(-1)
+        o[:cols * ldout].reshape(cols, ldout)[:, :rows] = a.T
+
     def index(self, idx):
         return torch.as_tensor(np.asarray(idx, dtype=np.int64))
 
