@@ -66,7 +66,7 @@ class ClockSampler:
         self.rows = []
         self.proc = None
         # sampling period (ms); ISDF_BENCH_SMI_MS=0 switches the sampler off (diagnostics only: the contract wants it on)
-        self.period = int(os.environ.get('ISDF_BENCH_SMI_MS', '500'))
+        self.period = int(os.environ.get('ISDF_BENCH_SMI_MS', '200'))
 
     def start(self):
         if self.period <= 0:
@@ -111,7 +111,9 @@ class ClockSampler:
         # median over samples taken under load (power above the idle floor)
         load = [s for s, p in zip(sm, pw) if p > 0.5 * max(pw)] or sm
         return {'sm_mhz': float(np.median(load)), 'sm_max_mhz': float(max(mx)),
-                'power_w_max': float(max(pw)), 'samples': len(sm), 'reasons': sorted(reasons)}
+                'sm_mhz_min_under_load': float(min(load)), 'sm_mhz_p10_under_load': float(np.percentile(load, 10)),
+                'power_w_max': float(max(pw)), 'power_w_median_under_load': float(np.median([p for p in pw if p > 0.5 * max(pw)])),
+                'samples': len(sm), 'period_ms': self.period, 'reasons': sorted(reasons)}
 
 
 # --------------------------------------------------------------------------- CPU arm

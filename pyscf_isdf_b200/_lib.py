@@ -375,13 +375,21 @@ class Handle:
 
 
     # -- stepwise stage 2-5 pieces used by the multi-GPU driver (pyscf_isdf_b200/dist.py) ---------
-    def select_create(self, nao, ngl, g_offset, ng_total, npts):
+    def select_create(self, nao, ngl, g_offset, ng_total, npts, ws=None):
+        """ws: optional caller-kept uint8 device buffer of at least select_ws_bytes(nao, ngl, npts)."""
         nbytes = self.lib.isdf_select_ip_ws_bytes(nao, ngl, npts)
-        ws = self.workspace(nbytes)
+        if ws is None or ws.numel() < nbytes:
+            ws = self.workspace(nbytes)
         plan = c_vp()
         check(self.lib.isdf_select_create(self.h, nao, ngl, g_offset, ng_total, npts,
                                           c_vp(ws.data_ptr()), nbytes, ctypes.byref(plan)))
         return SelectPlan(self, plan, ws)
+
+    def select_ws_bytes(self, nao, ngl, npts):
+        return int(self.lib.isdf_select_ip_ws_bytes(nao, ngl, npts))
+
+    def syrk_i8_ws_bytes(self, n, K, nslices=8):
+        return int(self.lib.isdf_syrk_i8_ws_bytes(n, K, nslices))
 
     def fit_aux_from_U(self, U, ldu, npts, Z, ldz, ngl):
         nbytes = self.lib.isdf_fit_from_U_ws_bytes(ngl, npts)
@@ -412,10 +420,12 @@ class Handle:
     def symmetrize_upper(self, W, ld, n):
         check(self.lib.isdf_symmetrize_upper(self.h, c_vp(W.data_ptr()), ld, n))
 
-    def syrk_i8(self, n, K, A, lda, C, ldc, alpha=1.0, nslices=8):
-        """Upper triangle of C = alpha * A A^T on the int8 tensor cores (csrc/syrk_i8.cu)."""
+    def syrk_i8(self, n, K, A, lda, C, ldc, alpha=1.0, nslices=8, ws=None):
+        """Upper triangle of C = alpha * A A^T on the int8 tensor cores (csrc/syrk_i8.cu).
+        ws: optional caller-kept uint8 device buffer of at least syrk_i8_ws_bytes(n, K, nslices)."""
         nbytes = self.lib.isdf_syrk_i8_ws_bytes(n, K, nslices)
-        ws = self.workspace(nbytes)
+        if ws is None or ws.numel() < nbytes:
+            ws = self.workspace(nbytes)
         check(self.lib.isdf_syrk_i8(self.h, n, K, c_vp(A.data_ptr()), lda, c_vp(C.data_ptr()), ldc,
                                     float(alpha), int(nslices), c_vp(ws.data_ptr()), nbytes))
         self.syrk_i8_ops = float(self.lib.isdf_syrk_i8_last_ops())

@@ -83,6 +83,27 @@ class SerialComm:
         return float(x)
 
 
+def _kept(mydf, ops, name, numel, dtype=None, zero=False):
+    """A work buffer of the build that stays with the ISDF object between builds (ISDF.keep_buffers): handing
+    gigabyte blocks back to the caching allocator after every build lets it split and re-map them, which showed
+    up as sporadic 0.3 - 1 s stalls of a stage.  Returns a flat view of `numel` elements."""
+    keep = getattr(mydf, 'keep_buffers', True)
+    total = ops.device_mem_bytes() if hasattr(ops, 'device_mem_bytes') else 1 << 62
+    nbytes = int(numel) * (1 if dtype is not None else 8)          # dtype is only ever uint8 here
+    keep = keep and nbytes <= 0.15 * total                          # e.g. Si216's 50 GB product workspace stays transient
+    cache = mydf.__dict__.setdefault('_bufs', {}) if keep else {}
+    t = cache.get(name)
+    if t is None or t.numel() < numel or (dtype is not None and t.dtype != dtype):
+        cache.pop(name, None)
+        t = None
+        t = ops.empty((int(numel),), dtype=dtype) if dtype is not None else ops.empty((int(numel),))
+        cache[name] = t
+    v = t[:int(numel)]
+    if zero:
+        v.zero_()
+    return v
+
+
 class SlabPartition:
     """Who owns what: x-planes (stages 1-3 and the z,y FFT passes), (y,z)-columns of
     the half spectrum (x pass, W), rows of W (stage 5)."""
@@ -186,8 +207,11 @@ def build(mydf, comm, ops=None):
         lt_off = 0
     Lt = big_lt[lt_off:lt_off + n_lt].view(npts, ldl)
     ldu = _lib.pad8(npts)
-    U = ops.zeros((npts, ldu))
-    plan = ops.select_create(nao, ngl, g0, ng, npts)
+    import torch
+    U = _kept(mydf, ops, 'U', npts * ldu, zero=True).view(npts, ldu)
+    sel_ws = _kept(mydf, ops, 'select_ws', ops.select_ws_bytes(nao, ngl, npts), dtype=torch.uint8) \
+        if hasattr(ops, 'select_ws_bytes') else None
+    plan = ops.select_create(nao, ngl, g0, ng, npts, ws=sel_ws)
     dmax = comm.max_scalar(plan.begin(phi, ldl), phi)
     tol = mydf.tol if mydf.tol >= 0 else float(ng) * 2.220446049250313e-16 * dmax
     plan.set_tol(tol)
@@ -196,8 +220,8 @@ def build(mydf, comm, ops=None):
     cap = min(lib.isdf_select_max_rows() // N - 1, ngl_min)
     quota = min(lib.isdf_select_first_quota(N), cap)
     rl_max = lib.isdf_select_row_len(nao, npts)
-    blockbuf = ops.empty(((cap + 1) * rl_max,))
-    allbuf = ops.empty((N * (cap + 1) * rl_max,)) if N > 1 else blockbuf
+    blockbuf = _kept(mydf, ops, 'blockbuf', (cap + 1) * rl_max)
+    allbuf = _kept(mydf, ops, 'allbuf', N * (cap + 1) * rl_max) if N > 1 else blockbuf
     k0 = 0
     npanels = 0
     prof = ops.timer() if os.environ.get('ISDF_PROFILE_SELECT') else None      # per-step breakdown
@@ -310,8 +334,10 @@ def build(mydf, comm, ops=None):
     ev.mark('fft_ms')
     W = ops.empty((npts, npts))
     if wmode.startswith('i8'):
+        w_ws = _kept(mydf, ops, 'syrk_ws', ops.syrk_i8_ws_bytes(npts, 2 * nx * ncl, planes), dtype=torch.uint8) \
+            if hasattr(ops, 'syrk_i8_ws_bytes') else None
         ops.syrk_i8(npts, 2 * nx * ncl, Yr, 2 * ldy, W, npts,
-                    alpha=cell.vol / (float(ng) * float(ng)), nslices=planes)
+                    alpha=cell.vol / (float(ng) * float(ng)), nslices=planes, ws=w_ws)
     else:
         ops.dgemm(npts, npts, 2 * nx * ncl, Yr, 2 * ldy, 0, Yr, 2 * ldy, 0, W, npts,
                   alpha=cell.vol / (float(ng) * float(ng)), upper_only=1)
@@ -321,7 +347,7 @@ def build(mydf, comm, ops=None):
     del Y, Yr, big_y
     p0, p1 = int(part.ip_off[r]), int(part.ip_off[r + 1])
     if implicit:
-        W = _congruence_solve(ops, comm, part, U, ldu, W, npts)
+        W = _congruence_solve(ops, comm, part, U, ldu, W, npts, mydf)
         ev.mark('wsolve_ms')
     else:
         W = W[p0:p1]
@@ -348,7 +374,7 @@ def build(mydf, comm, ops=None):
     return mydf
 
 
-def _congruence_solve(ops, comm, part, U, ldu, M, npts):
+def _congruence_solve(ops, comm, part, U, ldu, M, npts, mydf=None):
     """Rows [p0, p1) of W = U^-1 M U^-T for this rank (M symmetric, replicated; U upper
     triangular, replicated).  Both solves act on independent columns, so rank r takes the
     column block [p0, p1); the transposition between them is one all-to-all of Np*Np/N doubles."""
@@ -356,13 +382,13 @@ def _congruence_solve(ops, comm, part, U, ldu, M, npts):
     off = [int(x) for x in part.ip_off]
     p0, p1 = off[r], off[r + 1]
     ncr = p1 - p0                                       # may be 0 on a rank when Np < 8 N: still take part
-    Z1 = ops.empty((npts, ncr))
+    Z1 = _kept(mydf, ops, 'cong_Z1', npts * ncr).view(npts, ncr) if mydf is not None else ops.empty((npts, ncr))
     if ncr:
         Z1.copy_(M[:, p0:p1])                           # column block of M: a pitched device-to-device copy
     del M
     if ncr:
         ops.fit_aux_from_U(U, ldu, npts, Z1, ncr, ncr)  # Z1 = U^-1 M[:, cols]
-    R = ops.empty((npts, ncr))
+    R = _kept(mydf, ops, 'cong_R', npts * ncr).view(npts, ncr) if mydf is not None else ops.empty((npts, ncr))
     if N == 1:
         ops.transpose(Z1, ncr, npts, ncr, R, ncr)       # R = Z1^T (square here: ncr == Np)
     else:

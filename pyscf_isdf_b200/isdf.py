@@ -57,6 +57,7 @@ class ISDF:
         # for the next build() after reset(); release_buffers() drops them
         self.keep_buffers = True
         self._arena = None
+        self._bufs = {}            # other build work buffers kept between builds (dist._kept)
         self._device = device
         self._handle = None
         # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
@@ -98,6 +99,7 @@ class ISDF:
     def release_buffers(self):
         """Give the build-time work buffers back to the allocator (they are only needed by build())."""
         self._arena = None
+        self._bufs = {}
         return self
 
     def dump_flags(self, verbose=None):

@@ -245,7 +245,7 @@ class FakeOps:
         _np(vmat)[:] = (m + m.T).reshape(-1)
 
     # -- stage 2 / 3 ----------------------------------------------------------------
-    def select_create(self, nao, ngl, g_offset, ng_total, npts):
+    def select_create(self, nao, ngl, g_offset, ng_total, npts, ws=None):
         return FakePlan(nao, ngl, g_offset, ng_total, npts)
 
     def fit_aux_from_U(self, U, ldu, npts, Z, ldz, ngl):
@@ -311,7 +311,7 @@ class FakeOps:
         acc = acc * acc if epi == 1 else (acc * _np(E)[:M, :N] if epi == 2 else alpha * acc)
         _np(C)[:M, :N] = acc
 
-    def syrk_i8(self, n, K, A, lda, C, ldc, alpha=1.0, nslices=8):
+    def syrk_i8(self, n, K, A, lda, C, ldc, alpha=1.0, nslices=8, ws=None):
         An = _np(A)[:n, :K]
         _np(C)[:n, :n] = np.triu(alpha * An.dot(An.T))
 
