@@ -84,7 +84,21 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(',')])
+            self.rows.append([x.strip() for x in line.split(',')] + [time.time()])      # arrival time = sample time
+
+    def mean_clock_between(self, marks):
+        """Mean SM clock of the samples that arrived inside each interval marks[i] .. marks[i+1] (host wall times)."""
+        out = []
+        for t0, t1 in zip(marks[:-1], marks[1:]):
+            v = []
+            for r in self.rows:
+                if len(r) >= 8 and t0 <= r[-1] < t1:
+                    try:
+                        v.append(float(r[0]))
+                    except ValueError:
+                        pass
+            out.append(float(np.mean(v)) if v else None)
+        return out
 
     def stop(self):
         if self.proc is None:
@@ -546,6 +560,10 @@ def run_b200(args):
         return mydf.get_jk(dm_host[0], exxdiv=exxdiv)
 
     fp64_peak = measure_fp64_peak(torch, dev) if rank == 0 else None
+    if os.environ.get('ISDF_BENCH_GC') == '0':          # diagnostics: is the interpreter's garbage collector behind outlier steps?
+        import gc
+        gc.collect()
+        gc.disable()
 
     for _ in range(args.warmup):
         step_device()
@@ -556,9 +574,11 @@ def run_b200(args):
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     stage_acc = {}
     marks = []
+    wall = [time.time()]
     e0.record()
     for _ in range(args.steps):
         step_device()
+        wall.append(time.time())       # the build ends with a device synchronisation: host time tracks device time to ~20 ms
         for k, v in mydf.timings.items():
             stage_acc.setdefault(k, []).append(v)
         m = torch.cuda.Event(enable_timing=True)
@@ -572,6 +592,8 @@ def run_b200(args):
     h.gemm_profile(False)
     l1 = h.launches()
     clocks = sampler.stop() if sampler else None
+    if clocks is not None and sampler.rows:
+        clocks['sm_mhz_mean_each_step'] = sampler.mean_clock_between(wall)
 
     # J/K alone (per SCF iteration), device-resident
     jk_ms = []

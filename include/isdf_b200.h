@@ -272,6 +272,13 @@ int isdf_phase_expand(isdf_handle* h, const double* tab_re, const double* tab_im
                       const double* Gv, long long ng, const double* h_R, double sign,
                       double* out_re, double* out_im, long long ldo);
 
+/* W = U^-1 M U^-T in place on the symmetric M[np, np]: both triangular solves of fit='implicit' on one GPU, the second
+ * one restricted to the upper block-trapezoid (4/3 np^3 flops in all), result symmetrised.  Pattern of
+ * pyscf/pbc/df/rsdf_builder.py:226,827 (Cholesky factor applied from both sides).  Workspace:
+ * isdf_fit_from_U_ws_bytes(np, np). */
+int isdf_congruence(isdf_handle* h, double* U, long long ldu, int np, double* M, long long ldm,
+                    void* ws, size_t ws_bytes);
+
 /* out[cols, rows] = in[rows, cols]^T (row strides ldout, ldin; no overlap): the re-orientation between the two
  * triangular solves of the congruence W = U^-1 M U^-T (no reference counterpart: NumPy's `.T`). */
 int isdf_transpose(isdf_handle* h, const double* in, long long ldin, int rows, int cols,

@@ -83,6 +83,7 @@ SIGNATURES = {
     'isdf_get_jk_static_max_bytes': (c_sz, []),
     'isdf_get_jk_static': (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     'isdf_phase_expand': (c_int, [c_vp, c_vp, c_vp, c_ll, c_int, c_vp, c_ll, c_vp, c_dbl, c_vp, c_vp, c_ll]),
+    'isdf_congruence': (c_int, [c_vp, c_vp, c_ll, c_int, c_vp, c_ll, c_vp, c_sz]),
     'isdf_transpose': (c_int, [c_vp, c_vp, c_ll, c_int, c_int, c_vp, c_ll]),
     'isdf_dgemm': (c_int, [c_vp, c_int, c_int, c_int, c_vp, c_ll, c_int, c_vp, c_ll, c_int,
                            c_vp, c_ll, c_vp, c_ll, c_vp, c_ll, c_dbl, c_int, c_int, c_int]),
@@ -348,6 +349,13 @@ class Handle:
                                          c_vp(tab_im.data_ptr()) if tab_im is not None else None, ldt, nrow,
                                          c_vp(Gv.data_ptr()), ng, hptr(R), float(sign),
                                          c_vp(out_re.data_ptr()), c_vp(out_im.data_ptr()), ldo))
+
+    def congruence(self, U, ldu, npts, M, ldm):
+        """M <- U^-1 M U^-T in place (symmetric M, upper-triangular U), csrc/fit.cu."""
+        nbytes = self.lib.isdf_fit_from_U_ws_bytes(npts, npts)
+        ws = self.workspace(nbytes)
+        check(self.lib.isdf_congruence(self.h, c_vp(U.data_ptr()), ldu, npts, c_vp(M.data_ptr()), ldm,
+                                       c_vp(ws.data_ptr()), nbytes))
 
     def transpose(self, src, ldin, rows, cols, out, ldout):
         """out[cols, rows] = src[rows, cols]^T on the handle's stream (csrc/fit.cu)."""

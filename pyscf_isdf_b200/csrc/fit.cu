@@ -233,6 +233,51 @@ int check_info(isdf_handle* h, int* d_info, const char* what)
 
 }  // namespace
 
+// W = U^-1 M U^-T in place on the symmetric M[np, np] (row stride ldm), U upper triangular: the congruence of
+// fit='implicit' on one GPU.  First Z = U^-1 M (blocked back substitution over all np columns, np^3 flops); then
+// W = Z U^-T column block by column block from the right, LEFT-looking and for the rows at or above the block only
+// (W is symmetric, the upper block-trapezoid determines it): per block one GEMM with M = rows above, N = 128,
+// K = columns to the right -- np^3 / 3 flops instead of the np^3 of a second full solve, large-M shapes, and no
+// transposed copies.  The lower triangle is left to isdf_symmetrize_upper (called here).
+// Workspace: isdf_fit_from_U_ws_bytes(np, np).
+extern "C" int isdf_congruence(isdf_handle* h, double* U, long long ldu, int np, double* M, long long ldm,
+                               void* ws, size_t ws_bytes)
+{
+    ARG_CHECK(h && U && M && ws && np > 0 && ldu >= np && ldm >= np);
+    if (isdf_fit_from_U_ws_bytes(np, np) > ws_bytes) {
+        isdf_set_error("isdf_congruence workspace too small: need %zu have %zu", isdf_fit_from_U_ws_bytes(np, np), ws_bytes);
+        return ISDF_ERR_WS;
+    }
+    WsAlloc a(ws, ws_bytes);
+    const int nblk = (np + CB - 1) / CB;
+    double* Vinv = a.get<double>((size_t)nblk * CB * CB);
+    double* tmp = a.get<double>((size_t)CB * pad8(np));
+    int* info = a.get<int>(4);
+    int rc;
+    cudaStream_t s = h->stream;
+    CUDA_TRY(cudaEventRecord(h->ev0[ISDF_STAGE_FIT], s));
+    CUDA_TRY(cudaMemsetAsync(info, 0, sizeof(int) * 4, s));
+    if ((rc = invert_diag_blocks(h, U, ldu, np, Vinv, info))) return rc;
+    if ((rc = check_info(h, info, "isdf_congruence: zero or non-finite pivot in the selection factor"))) return rc;
+    if ((rc = solve_upper_right(h, U, ldu, np, Vinv, M, ldm, np, tmp))) return rc;        // M <- Z = U^-1 M
+    for (int jb = nblk - 1; jb >= 0; --jb) {
+        const int r0 = jb * CB, cb = std::min(CB, np - r0), r1 = r0 + cb;
+        double* Zj = M + r0;                                  // rows 0..r1 of block column jb
+        if (r1 < np)    // Z[0:r1, jb] -= W[0:r1, r1:] U[jb, r1:]^T
+            if ((rc = gemm_call(h, r1, cb, np - r1, M + r1, ldm, 0, U + (long long)r0 * ldu + r1, ldu, 0,
+                                Zj, ldm, Zj, 1, EPI_STORE, 0))) return rc;
+        // W[0:r1, jb] = Z[0:r1, jb] (U_jj^-1)^T   (tmp is [r1, cb])
+        if ((rc = gemm_call(h, r1, cb, cb, Zj, ldm, 0, Vinv + (size_t)jb * CB * CB, CB, 0,
+                            tmp, cb, nullptr, 0, EPI_STORE, 0))) return rc;
+        CUDA_TRY(cudaMemcpy2DAsync(Zj, sizeof(double) * ldm, tmp, sizeof(double) * cb,
+                                   sizeof(double) * cb, r1, cudaMemcpyDeviceToDevice, s));
+    }
+    if ((rc = isdf_symmetrize_upper(h, M, ldm, np))) return rc;
+    CUDA_TRY(cudaEventRecord(h->ev1[ISDF_STAGE_FIT], s));
+    h->ev_used[ISDF_STAGE_FIT] = true;
+    return ISDF_OK;
+}
+
 namespace {
 
 // out[c, r] = in[r, c] through a 32 x 33 shared-memory tile (both sides coalesced)

@@ -379,6 +379,9 @@ def _congruence_solve(ops, comm, part, U, ldu, M, npts, mydf=None):
     triangular, replicated).  Both solves act on independent columns, so rank r takes the
     column block [p0, p1); the transposition between them is one all-to-all of Np*Np/N doubles."""
     N, r = comm.size, comm.rank
+    if N == 1 and hasattr(ops, 'congruence'):           # one GPU: both solves in place, the second on the upper trapezoid only
+        ops.congruence(U, ldu, npts, M, npts)
+        return M
     off = [int(x) for x in part.ip_off]
     p0, p1 = off[r], off[r + 1]
     ncr = p1 - p0                                       # may be 0 on a rank when Np < 8 N: still take part
