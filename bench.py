@@ -505,6 +505,25 @@ def extra_workload(name, args, local, comm, world, torch, dist):
         return {'workload': name, 'error': '%s: %s' % (type(e).__name__, str(e)[:300])}
 
 
+def host_stats():
+    """Host-side facts that explain GPU idle time inside a step: CFS throttling of the container and involuntary
+    context switches of this process."""
+    import resource
+    out = {}
+    try:
+        for line in open('/sys/fs/cgroup/cpu.stat'):
+            k, v = line.split()
+            if k in ('nr_throttled', 'throttled_usec', 'nr_periods'):
+                out[k] = int(v)
+        out['cpu_max'] = open('/sys/fs/cgroup/cpu.max').read().strip()
+    except (OSError, ValueError):
+        pass
+    ru = resource.getrusage(resource.RUSAGE_SELF)
+    out['nvcsw'], out['nivcsw'] = ru.ru_nvcsw, ru.ru_nivcsw
+    out['utime_s'], out['stime_s'] = ru.ru_utime, ru.ru_stime
+    return out
+
+
 def kernel_traffic(kernel):
     """DRAM bytes per launch of the roofline kernel, read from the committed ncu summary of this round."""
     path = os.path.join(ROOT, 'profiles', 'kernel_traffic.json')
@@ -574,6 +593,7 @@ def run_b200(args):
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     stage_acc = {}
     marks = []
+    host0 = host_stats()
     wall = [time.time()]
     e0.record()
     for _ in range(args.steps):
@@ -587,6 +607,9 @@ def run_b200(args):
     e1.record()
     barrier()
     total_ms = e0.elapsed_time(e1)
+    host1 = host_stats()
+    host_delta = {k: (host1[k] - host0[k] if isinstance(host1.get(k), (int, float)) and k in host0 else host1.get(k)) for k in host1}
+    host_delta['wall_s'] = wall[-1] - wall[0]
     each_ms = [a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks)]
     gflops, gms, gcount = h.gemm_profile_read()
     h.gemm_profile(False)
@@ -695,7 +718,7 @@ def run_b200(args):
         'flop_model': fm,
         'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
         'gpu_launches': int((l1[0] - l0[0]) + (l1[1] - l0[1])),
-        'roofline': roofline, 'clocks': clocks,
+        'roofline': roofline, 'clocks': clocks, 'host': host_delta,
     }
     if args.wgemm.startswith('i8') and stages_ms.get('wgemm_ms'):
         planes = int(args.wgemm.split(':')[1]) if ':' in args.wgemm else 8
