@@ -69,6 +69,20 @@ __host__ __device__ inline int centred_mod(long long x)
     return r;
 }
 
+// centred residue of an integer-valued double |y| <= 2^53: q = rint(y / P) in FP64 is off by at most one
+// (|y / P| 2^-52 < 0.05), y - q P is a small integer and therefore exact in one fma, one correction step.
+// Same value as centred_mod<P>((long long)y); ~8 FP64 / integer instructions instead of a 64-bit
+// constant division (ncu: the split kernel was issue-bound at 28 instructions per residue).
+template <int P>
+__host__ __device__ inline int centred_mod_f64(double y)
+{
+    const double q = rint(y * (1.0 / (double)P));
+    int r = (int)fma(-q, (double)P, y);
+    if (r > (P - 1) / 2) r -= P;
+    else if (r < -(P / 2)) r += P;
+    return r;
+}
+
 // centred residue of an int32 accumulator modulo a run-time modulus (epilogue of the product kernel):
 // q = rint(v / p) in FP64 is off by at most one for |v| < 2^31, one correction step
 __host__ __device__ inline int centred_mod_rt(int v, int p, double inv_p)
@@ -132,14 +146,14 @@ constexpr int BLOCK_BYTES = 128 * 128;
 // other, so that only the 16 integers stay live)
 template <int K>
 struct PlaneLoop {
-    __host__ __device__ static inline void run(const long long* x, int8_t* dst, long long plane_stride, int nm)
+    __host__ __device__ static inline void run(const double* x, int8_t* dst, long long plane_stride, int nm)
     {
         PlaneLoop<K - 1>::run(x, dst, plane_stride, nm);
         if (K - 1 < nm) {
             uint32_t w[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-                w[j >> 2] |= ((uint32_t)centred_mod<modulus(K - 1)>(x[j]) & 0xffu) << (8 * (j & 3));
+                w[j >> 2] |= ((uint32_t)centred_mod_f64<modulus(K - 1)>(x[j]) & 0xffu) << (8 * (j & 3));
             uint32_t* o = reinterpret_cast<uint32_t*>(dst + (long long)(K - 1) * plane_stride);     // 16-byte aligned
             o[0] = w[0]; o[1] = w[1]; o[2] = w[2]; o[3] = w[3];
         }
@@ -147,7 +161,7 @@ struct PlaneLoop {
 };
 template <>
 struct PlaneLoop<0> {
-    __host__ __device__ static inline void run(const long long*, int8_t*, long long, int) {}
+    __host__ __device__ static inline void run(const double*, int8_t*, long long, int) {}
 };
 
 // item idx = (row i, group of 16 consecutive k): residue plane m of rint(A[i, k0+k] / sc[i] * 2^bits)
@@ -159,15 +173,15 @@ __host__ __device__ inline void split_item(long long idx, const double* A, long 
     const int groups = kcpad / 16;
     if (idx >= (long long)nrows_pad * groups) return;
     const int i = (int)(idx / groups), kg = (int)(idx - (long long)i * groups) * 16;
-    long long x[16];
+    double x[16];                                           // integer-valued, |x| <= 2^bits <= 2^53
     if (i < n) {
         const double mult = ldexp(1.0, bits) / sc[i];       // exact: powers of two
         const double* src = A + (long long)i * lda + k0 + kg;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) x[j] = (kg + j < kc) ? llrint(src[j] * mult) : 0ll;
+        for (int j = 0; j < 16; ++j) x[j] = (kg + j < kc) ? rint(src[j] * mult) : 0.0;
     } else {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) x[j] = 0ll;
+        for (int j = 0; j < 16; ++j) x[j] = 0.0;
     }
     const int r = i & 127, c = (kg & 127) >> 4;
     int8_t* dst = planes + (long long)(i >> 7) * rb_stride + (long long)(kg >> 7) * BLOCK_BYTES + r * 128 + ((c ^ (r & 7)) << 4);

@@ -733,11 +733,16 @@ __global__ void mark_selected_kernel(const long long* __restrict__ ip_dev, int k
 
 // Per-grid-point triangular sweep over the panel columns + residual update.
 // rows: Lt_panel[k * ldl + g], k < nb.  Divisor of column k is sqrt(resid[k]).
+// A thread carries PT grid points (g, g + 128, ...): every triangle entry read from shared memory (a broadcast
+// load, the kernel's bound: one per FMA with PT = 1) feeds PT independent chains.  The chain of each point is
+// unchanged (ascending column index), so the bits are those of the one-point form.
+constexpr int SWEEP_PT = 2;
 __global__ void __launch_bounds__(128)
 panel_sweep_kernel(double* __restrict__ Ltp, long long ldl, long long ng, int nb,
                    const double* __restrict__ LppP, const double* __restrict__ resid,
                    double* __restrict__ d)
 {
+    constexpr int PT = SWEEP_PT;
     extern __shared__ double s_l[];            // packed lower triangle, then nb pivots
     double* s_piv = s_l + NB * (NB + 1) / 2;
     for (int i = threadIdx.x; i < nb * nb; i += blockDim.x) {
@@ -746,40 +751,62 @@ panel_sweep_kernel(double* __restrict__ Ltp, long long ldl, long long ng, int nb
     }
     for (int i = threadIdx.x; i < nb; i += blockDim.x) s_piv[i] = sqrt(resid[i]);
     __syncthreads();
-    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= ng) return;
-    double dd = d[g];
-    double* col = Ltp + g;
+    const long long g0 = (long long)blockIdx.x * (blockDim.x * PT) + threadIdx.x;
+    if (g0 >= ng) return;
+    // points beyond the grid are clamped to the thread's first point and never stored
+    long long gp[PT]; bool ok[PT]; double dd[PT];
+#pragma unroll
+    for (int p = 0; p < PT; ++p) {
+        const long long g = g0 + (long long)p * blockDim.x;
+        ok[p] = g < ng; gp[p] = ok[p] ? g : g0; dd[p] = d[gp[p]];
+    }
     constexpr int SB = 16;      // rows per register block: earlier rows are re-read nb/(2*SB) times
     for (int kb = 0; kb < nb; kb += SB) {
-        double acc[SB], res[SB];
+        double acc[PT][SB], res[PT][SB];
 #pragma unroll
-        for (int i = 0; i < SB; ++i) acc[i] = (kb + i < nb) ? col[(long long)(kb + i) * ldl] : 0.0;
+        for (int p = 0; p < PT; ++p)
+#pragma unroll
+            for (int i = 0; i < SB; ++i) acc[p][i] = (kb + i < nb) ? Ltp[(long long)(kb + i) * ldl + gp[p]] : 0.0;
         // kb is a multiple of SB: fetch 8 earlier rows at a time so the loads overlap
         for (int j0 = 0; j0 < kb; j0 += 8) {
-            double x[8];
+            double x[PT][8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) x[u] = -col[(long long)(j0 + u) * ldl];
+            for (int p = 0; p < PT; ++p)
+#pragma unroll
+                for (int u = 0; u < 8; ++u) x[p][u] = -Ltp[(long long)(j0 + u) * ldl + gp[p]];
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
 #pragma unroll
                 for (int i = 0; i < SB; ++i)
-                    if (kb + i < nb) acc[i] = fma(x[u], s_l[(kb + i) * (kb + i + 1) / 2 + j0 + u], acc[i]);
+                    if (kb + i < nb) {
+                        const double l = s_l[(kb + i) * (kb + i + 1) / 2 + j0 + u];
+#pragma unroll
+                        for (int p = 0; p < PT; ++p) acc[p][i] = fma(x[p][u], l, acc[p][i]);
+                    }
             }
         }
 #pragma unroll
         for (int i = 0; i < SB; ++i) {
             if (kb + i < nb) {
 #pragma unroll
-                for (int jj = 0; jj < i; ++jj)
-                    acc[i] = fma(-res[jj], s_l[(kb + i) * (kb + i + 1) / 2 + kb + jj], acc[i]);
-                res[i] = acc[i] / s_piv[kb + i];
-                col[(long long)(kb + i) * ldl] = res[i];
-                dd = fma(-res[i], res[i], dd);
+                for (int jj = 0; jj < i; ++jj) {
+                    const double l = s_l[(kb + i) * (kb + i + 1) / 2 + kb + jj];
+#pragma unroll
+                    for (int p = 0; p < PT; ++p) acc[p][i] = fma(-res[p][jj], l, acc[p][i]);
+                }
+                const double pv = s_piv[kb + i];
+#pragma unroll
+                for (int p = 0; p < PT; ++p) {
+                    res[p][i] = acc[p][i] / pv;
+                    if (ok[p]) Ltp[(long long)(kb + i) * ldl + gp[p]] = res[p][i];
+                    dd[p] = fma(-res[p][i], res[p][i], dd[p]);
+                }
             }
         }
     }
-    d[g] = dd;
+#pragma unroll
+    for (int p = 0; p < PT; ++p)
+        if (ok[p]) d[gp[p]] = dd[p];
 }
 
 struct SelWs {
@@ -1094,7 +1121,7 @@ extern "C" int isdf_select_flush(isdf_select_plan* pl, const double* phi, long l
     if ((rc = gemm_kc(h, nb, (int)ngl, pl->nao, w.PivRows + META, rl, phi, ldphi, 1, Ltp, ldl, nullptr, 0, EPI_SQUARE))) return rc;
     if (k0 > 0)
         if ((rc = gemm_kc(h, nb, (int)ngl, k0, w.PivRows + META + naop, rl, Lt, ldl, 1, Ltp, ldl, Ltp, 1, EPI_STORE))) return rc;
-    panel_sweep_kernel<<<(unsigned)((ngl + 127) / 128), 128, sweep_smem, s>>>(
+    panel_sweep_kernel<<<(unsigned)((ngl + 128 * SWEEP_PT - 1) / (128 * SWEEP_PT)), 128, sweep_smem, s>>>(
         Ltp, ldl, ngl, nb, w.LppP, w.resid_dev + k0, w.d);
     mark_selected_kernel<<<1, NB, 0, s>>>(w.ip_dev, k0, nb, pl->g_offset, ngl, w.d);
     CUDA_TRY(cudaGetLastError());
