@@ -468,6 +468,26 @@ def extra_workload(name, args, local, comm, world, torch, dist):
         nao = cell.nao
         mydf = ISDF(cell, c=args.c, fit=args.fit, device=local, keep_aoR=False, comm=comm, wgemm=args.wgemm)
         h = mydf.handle
+        # does it fit these ranks?  Decided by ALL ranks before anything is allocated: a rank that ran out of
+        # memory alone would leave the others waiting in a collective.
+        from pyscf_isdf_b200.dist import SlabPartition
+        from pyscf_isdf_b200 import _lib
+        ng = int(np.prod(cell.mesh))
+        npts = min(int(args.c * nao), ng)
+        rank = comm.rank if comm is not None else 0
+        part = SlabPartition(cell.mesh, world, npts)
+        g0, g1 = part.grid_range(rank)
+        ldl = _lib.pad8(g1 - g0)
+        nbig = max(npts * ldl, 2 * npts * int(cell.mesh[0]) * part.ncol_local(rank))
+        ws_w = int(h.lib.isdf_syrk_i8_ws_bytes(npts, 2 * int(cell.mesh[0]) * part.ncol_local(rank), 8)) if args.wgemm.startswith('i8') else 0
+        need = 8 * nbig + 8 * (nao * ldl + 3 * npts * _lib.pad8(npts)) + ws_w + (3 << 30)
+        free = torch.cuda.mem_get_info(dev)[0]
+        fits = torch.tensor([1.0 if need <= 0.95 * free else 0.0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(fits, op=dist.ReduceOp.MIN)
+        if float(fits.item()) < 0.5:
+            return {'workload': workloads.describe(name), 'n_gpus': world,
+                    'skipped': 'needs %.0f GB per rank on %d GPU(s), %.0f GB free' % (need / 1e9, world, free / 1e9)}
         d_dm = torch.from_numpy(workloads.synthetic_dm(nao)[None]).to(dev)
         mydf.build()
         mydf.reset()
