@@ -80,6 +80,38 @@ def test_plugin_surface_errors():
             return True
     mf = mydf.update_mf(FakeMF())
     assert mf.with_df is mydf and mf._eri is None and mf._is_mem_enough() is False
+    # the rest of FFTDF's surface (pyscf/pbc/df/fft.py:246-272, :317-359) that pbc.scf can reach on with_df
+    # (hf.py:676-679 get_ao_eri when the in-core shortcut is not patched; post-SCF ao2mo; molecular DF.loop):
+    # a reason, not an AttributeError
+    for name, args in (('get_ao_eri', ()), ('get_eri', ()), ('ao2mo', (np.eye(cell.nao),)), ('get_mo_eri', (dm,)),
+                       ('ao2mo_7d', (dm,)), ('get_ao_pairs_G', ()), ('get_ao_pairs', ()), ('get_mo_pairs_G', (dm,)),
+                       ('get_mo_pairs', (dm,)), ('aoR_loop', ()), ('loop', ()), ('range_coulomb', (0.3,)),
+                       ('get_jk_e1', (dm,)), ('get_j_e1', (dm,)), ('get_k_e1', (dm,))):
+        with pytest.raises(NotImplementedError, match='ISDF'):
+            getattr(mydf, name)(*args)
+    with pytest.raises(NotImplementedError):
+        mydf.grids
+    assert mydf.get_naoaux() == 3 * cell.nao
+    with pytest.raises(NotImplementedError):
+        mydf.get_nuc(np.array([0.1, 0.0, 0.0]))
+    with pytest.raises(NotImplementedError):
+        mydf.nr_rks('pbe', dm, kpts=np.array([0.1, 0.0, 0.0]))
+    with pytest.raises(RuntimeError):
+        mydf.save('/tmp/never_written.npz')            # nothing built yet
+    # tagged density matrices: which ones take the occupied-orbital form
+    C = np.linalg.qr(np.random.default_rng(0).standard_normal((cell.nao, cell.nao)))[0]
+    occ = np.zeros(cell.nao); occ[:4] = 2
+    tags = ISDF._mo_tags
+    class T(np.ndarray):
+        pass
+    t = dm.view(T); t.mo_coeff, t.mo_occ = C, occ
+    assert tags(t, dm, 1, cell.nao) is not None
+    assert tags(t, dm, 2, cell.nao) is None                              # a set of matrices
+    assert tags(dm, dm, 1, cell.nao) is None                             # no tags
+    t.mo_coeff = C.astype(complex)
+    assert tags(t, dm, 1, cell.nao) is None                              # complex orbitals
+    t.mo_coeff, t.mo_occ = C[None], occ[None]                            # k-point style leading axis of length 1
+    assert tags(t, dm, 1, cell.nao) is not None
 
 
 def test_cell_model_matches_reference_conventions():
