@@ -332,6 +332,12 @@ class Cell:
     def get_SI(self, Gv):
         return np.exp(-1j * np.dot(self.atom_coords(), Gv.T))
 
+    def make_kpts(self, nks):
+        """Gamma-centred uniform k-point mesh in absolute units, x slowest (pyscf/pbc/gto/cell.py
+        Cell.make_kpts with its default options: scaled k = j / n, j = 0 .. n-1)."""
+        ks = [np.arange(int(n), dtype=float) / int(n) for n in nks]
+        return cartesian_prod(ks).dot(self.reciprocal_vectors())
+
     def get_scaled_atom_coords(self):
         return np.dot(self.atom_coords(), np.linalg.inv(self._a))
 
@@ -489,9 +495,10 @@ def madelung(cell):
     return -2 * probe.ewald()
 
 
-def super_cell(cell, ncopy):
+def super_cell(cell, ncopy, mesh=None):
     """ncopy[0] x ncopy[1] x ncopy[2] supercell, images stacked in +
-    direction, odd mesh (pyscf/pbc/tools/pbc.py:595-639)."""
+    direction, odd mesh (pyscf/pbc/tools/pbc.py:595-639) unless ``mesh``
+    is given (kmesh.py wants exactly ncopy * cell.mesh)."""
     a = cell.lattice_vectors()
     Ts = cartesian_prod([np.arange(n) for n in ncopy])
     shifts = np.dot(Ts, a)
@@ -500,10 +507,12 @@ def super_cell(cell, ncopy):
     for L in shifts:
         for ia in range(cell.natm):
             atoms.append((cell.atom_symbol(ia), tuple(xyz[ia] + L)))
-    mesh = np.asarray(ncopy) * np.asarray(cell.mesh)
+    if mesh is None:
+        mesh = np.asarray(ncopy) * np.asarray(cell.mesh)
+        mesh = (mesh // 2) * 2 + 1
     sup = Cell(atom=atoms, a=np.einsum('i,ij->ij', np.asarray(ncopy, float), a),
                basis=cell.basis, pseudo=cell.pseudo, unit='B',
-               mesh=(mesh // 2) * 2 + 1, precision=cell.precision)
+               mesh=[int(m) for m in mesh], precision=cell.precision)
     return sup.build()
 
 

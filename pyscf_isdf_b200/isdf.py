@@ -63,6 +63,8 @@ class ISDF:
         # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
         self.comm = comm
         self._rsh_df = {}
+        self._kmesh = None         # kmesh.KMesh when self.kpts is a uniform mesh (served by the supercell's ISDF)
+        self._sc = None
         self.h2d_bytes = self.d2h_bytes = 0      # bytes the last get_jk() copied over PCIe (counted at the copies)
         self.timings = {}
         self.reset()
@@ -94,6 +96,10 @@ class ISDF:
         self._slab = None
         self._aoR4 = None          # AO values + gradients of nr_rks
         self._pinned = None        # pinned host staging buffers of get_jk
+        if getattr(self, '_sc', None) is not None:
+            self._sc.reset()
+        if cell is not None:
+            self._kmesh = self._sc = None
         return self
 
     def release_buffers(self):
@@ -122,8 +128,9 @@ class ISDF:
             raise NotImplementedError("fit='cholesky' is single-GPU only; use 'implicit' or 'pivot_factor'")
         if getattr(self.cell, 'dimension', 3) != 3:
             raise RuntimeError('ISDF supports 3-D periodic cells only')   # cf. fft.py:216-220
-        if abs(self.kpts).sum() > 1e-9:
-            raise NotImplementedError('ISDF is Gamma-point only')
+        if abs(self.kpts).sum() > 1e-9 and self._kmesh is None:
+            from .kmesh import KMesh
+            self._kmesh = KMesh(self.cell, self.kpts)     # NotImplementedError unless a complete uniform mesh
         return self
 
     def update_mf(self, mf):
@@ -145,6 +152,19 @@ class ISDF:
     def build(self):
         import torch
         self.check_sanity()
+        if self._kmesh is not None:
+            # k-point mesh: the Gamma-point ISDF of the supercell does all the work (kmesh.py)
+            if self._sc is None:
+                self._sc = ISDF(self._kmesh.supercell, c=self.c, n_ip=None, select=self.select, fit=self.fit,
+                                tol=self.tol, device=self._device, keep_aoR=self.keep_aoR, comm=self.comm,
+                                wgemm=self.wgemm, exact_j=self.exact_j)
+                if self.n_ip:
+                    self._sc.n_ip = int(self.n_ip) * self._kmesh.nk
+                self._sc.verbose, self._sc.stdout = self.verbose, self.stdout
+            self._sc.build()
+            self.ip_index, self.ip_resid, self.W = self._sc.ip_index, self._sc.ip_resid, self._sc.W
+            self.timings = self._sc.timings
+            return self
         if self.comm is not None or self.fit == 'implicit':
             from . import dist
             return dist.build(self, self.comm if self.comm is not None else dist.SerialComm())
@@ -248,10 +268,23 @@ class ISDF:
             raise NotImplementedError('range-separated Coulomb (omega) is not supported by ISDF')
         if kpts_band is not None:
             raise NotImplementedError('kpts_band is not supported by ISDF')
-        if kpts is not None and abs(np.asarray(kpts)).sum() > 1e-9:
-            raise NotImplementedError('ISDF is Gamma-point only')
         if exxdiv not in (None, 'ewald'):
             raise NotImplementedError('exxdiv=%s' % exxdiv)
+        if self._kmesh is None and abs(self.kpts).sum() > 1e-9:
+            self.check_sanity()
+        if self._kmesh is not None:
+            # a uniform k-point mesh (KSCF.get_jk, pyscf/pbc/scf/khf.py:519-532) through its supercell
+            kpts = self.kpts if kpts is None else np.reshape(kpts, (-1, 3))
+            if kpts.shape != self.kpts.shape or abs(kpts - self.kpts).max() > 1e-9:
+                raise NotImplementedError('ISDF at k-points: get_jk serves exactly the mesh it was built for')
+            if self.W is None:
+                self.build()
+            from .kmesh import get_jk_kmesh
+            out = get_jk_kmesh(self, dm, hermi, with_j, with_k, exxdiv)
+            self.h2d_bytes, self.d2h_bytes = self._sc.h2d_bytes, self._sc.d2h_bytes
+            return out
+        if kpts is not None and abs(np.asarray(kpts)).sum() > 1e-9:
+            raise NotImplementedError('ISDF is Gamma-point only unless built for a uniform k-point mesh')
         if self.W is None:
             self.build()                       # SCF never calls build() itself
         h = self.handle
@@ -382,6 +415,8 @@ class ISDF:
 
     # -- hcore pieces on the same device-resident AO values ("next" row 2 of SURVEY 8f) ----------
     def _check_gamma(self, kpts):
+        if self._kmesh is not None or abs(self.kpts).sum() > 1e-9:
+            raise NotImplementedError('ISDF at k-points serves get_jk / get_j / get_k only')
         if kpts is not None and abs(np.asarray(kpts)).sum() > 1e-9:
             raise NotImplementedError('ISDF is Gamma-point only')
 

@@ -143,3 +143,76 @@ def test_golden_files_consistent():
     assert abs(oracle.fp(phi) - float(z['phi_fp'])) < 1e-9
     ip, resid = c_oracle.select_ip_chain(phi, int(z['c']) * cell.nao)
     assert np.array_equal(ip, z['ip']) and np.array_equal(resid, z['resid'])
+
+
+def _bloch_ao(cell, kpts):
+    rcut, Ls = cell.ao_eval_params()
+    return oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, kpts=kpts)
+
+
+def test_fftdf_k_kpts_golden():
+    # pyscf/pbc/df/test/test_fft.py:536-544 (kpts), :664-676 (kpts_band, occupied-orbital tags): the k-point
+    # oracle K is pinned to the reference's known answer, both through the tags and through the plain matrices
+    from oracle.fftdf_jk import fftdf_get_k_kpts
+    cell = he_c_cell()
+    nao = cell.nao
+    np.random.seed(1)
+    kpts = np.random.random((4, 3))
+    kpts[3] = kpts[0] - kpts[1] + kpts[2]
+    np.random.seed(1)
+    kpts_band = np.random.random((2, 3))
+    mo_coeff = np.random.random((4, nao, nao))
+    mo_occ = np.array(np.random.random((4, nao)) > .6, dtype=np.double)
+    dms = np.einsum('kpi,ki,kqi->kpq', mo_coeff, mo_occ, mo_coeff)
+    ao_k, ao_b = _bloch_ao(cell, kpts), _bloch_ao(cell, kpts_band)
+    a, mesh, coords = cell.lattice_vectors(), cell.mesh, cell.get_uniform_grids()
+    gold = 10.239828255099447 + 2.1190549216896182j
+    vk = fftdf_get_k_kpts(ao_k, dms, a, mesh, kpts, coords, ao_band=ao_b, kpts_band=kpts_band, mo=(mo_coeff, mo_occ))
+    assert abs(oracle.fp(vk) - gold) < 1e-8
+    vk = fftdf_get_k_kpts(ao_k, dms, a, mesh, kpts, coords, ao_band=ao_b, kpts_band=kpts_band)
+    assert abs(oracle.fp(vk) - gold) < 1e-8
+
+
+def test_kmesh_supercell_equivalence():
+    # pyscf/pbc/tools/k2gamma.py: J and K on a uniform k-point mesh are the Bloch transforms of the supercell's
+    # Gamma-point J and K (the product's route to k-points, pyscf_isdf_b200/kmesh.py), here with both sides exact
+    from oracle.fftdf_jk import fftdf_get_j_kpts, fftdf_get_k_kpts
+    from pyscf_isdf_b200.kmesh import KMesh, detect_kmesh
+    cell = Cell(atom='He 1. .5 .5; He .1 1.3 2.1', basis={'He': [(0, (2.5, 1)), (0, (1., 1))]}, pseudo=None,
+                a=np.eye(3) * 2.5 + 0.1, mesh=[7, 9, 7], unit='B').build()
+    nao = cell.nao
+    assert detect_kmesh(cell, cell.make_kpts([3, 1, 2]))[0] == (3, 1, 2)
+    kpts = cell.make_kpts([3, 1, 3])
+    perm = np.array([2, 0, 5, 1, 4, 3, 8, 7, 6])
+    kpts = kpts[perm]                                  # any order
+    assert detect_kmesh(cell, kpts)[0] == (3, 1, 3)
+    assert detect_kmesh(cell, kpts[:5]) is None and detect_kmesh(cell, kpts + 0.01) is None
+    km = KMesh(cell, kpts)
+    sc = km.supercell
+    assert list(sc.mesh) == [21, 9, 21] and sc.nao == 9 * nao      # all odd: exact up to the AO lattice-sum cutoff (cell.precision)
+    rng = np.random.default_rng(3)
+    dms = rng.random((9, nao, nao)) + 1j * rng.random((9, nao, nao))
+    dms = dms + dms.conj().transpose(0, 2, 1)          # hermitian, no time-reversal symmetry: D_sc is complex
+    ao_k = _bloch_ao(cell, kpts)
+    a, mesh, coords = cell.lattice_vectors(), cell.mesh, cell.get_uniform_grids()
+    vj_ref = fftdf_get_j_kpts(ao_k, dms, a, mesh)
+    vk_ref = fftdf_get_k_kpts(ao_k, dms, a, mesh, kpts, coords)
+
+    D = km.dm_to_supercell(dms)
+    assert abs(D - D.conj().T).max() < 1e-12 and abs(D.imag).max() > 1e-3
+    ao_sc = oracle_phi(sc).T
+
+    class ExactSupercellDF:                    # stands where the supercell's ISDF object stands in the product
+        def get_jk(self, dm, hermi=1, with_j=True, with_k=True, exxdiv=None):
+            assert dm.dtype == np.float64 and dm.shape == (2, 9 * nao, 9 * nao) and hermi == 0
+            return oracle.fftdf_get_jk(ao_sc, dm, sc.lattice_vectors(), sc.mesh, with_j, with_k)
+
+    class Stub:
+        _kmesh, _sc = km, ExactSupercellDF()
+
+    from pyscf_isdf_b200.kmesh import get_jk_kmesh
+    vj, vk = get_jk_kmesh(Stub(), dms)
+    assert vj.shape == vk.shape == dms.shape
+    assert get_jk_kmesh(Stub(), dms, with_k=False)[1] is None
+    assert abs(vj - vj_ref).max() < 1e-8, abs(vj - vj_ref).max()
+    assert abs(vk - vk_ref).max() < 1e-8, abs(vk - vk_ref).max()

@@ -1,0 +1,72 @@
+"""GPU: J and K on a uniform k-point mesh, served by the Gamma-point ISDF of the supercell (pyscf_isdf_b200/kmesh.py).
+
+Checked against the k-point FFTDF oracle (oracle/fftdf_jk.py, pinned to pyscf/pbc/df/test/test_fft.py:664-676 in
+tests/test_oracle_golden.py) in the exact limit: number of interpolation points >= rank of the supercell's pair space.
+"""
+import numpy as np
+import pytest
+import oracle
+from oracle.fftdf_jk import fftdf_get_j_kpts, fftdf_get_k_kpts
+from util import he_c_cell
+from pyscf_isdf_b200.isdf import ISDF
+from pyscf_isdf_b200.cell import madelung
+
+pytestmark = pytest.mark.gpu
+
+
+def _bloch_ao(cell, kpts):
+    rcut, Ls = cell.ao_eval_params()
+    return oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, kpts=kpts)
+
+
+def test_kmesh_get_jk_exact_limit_matches_kpoint_fftdf():
+    cell = he_c_cell()                                  # mesh 21^3, nao 6
+    nao = cell.nao
+    kpts = cell.make_kpts([3, 1, 1])                    # supercell: nao 18, mesh 63 x 21 x 21 (all odd)
+    # 180 points offered, the pair space has dimension <= 171.  The default stop (ng eps max d, the reference's
+    # pyscf/lib/scipy_helper.py:88-90) drops pair products of norm ~1e-5 and leaves 1e-6 in J; tol = 1e-15 keeps them
+    # (tools/kmesh_tol_scan.py: 1.4e-6 / 4e-8 / 5e-9 at the default / 1e-14 / 1e-15)
+    mydf = ISDF(cell, kpts=kpts, n_ip=60, tol=1e-15)
+    rng = np.random.default_rng(11)
+    dms = rng.random((3, nao, nao)) + 1j * rng.random((3, nao, nao))
+    dms = dms + dms.conj().transpose(0, 2, 1)           # hermitian, not time-reversal symmetric
+    vj, vk = mydf.get_jk(dms, kpts=kpts, exxdiv=None)
+    assert vj.shape == vk.shape == (3, nao, nao) and vj.dtype == vk.dtype == np.complex128   # test_fft.py:654-655
+    assert mydf._sc.n_ip < 180                          # stopped by the residual, not by the count
+
+    ao_k = _bloch_ao(cell, kpts)
+    a, mesh, coords = cell.lattice_vectors(), cell.mesh, cell.get_uniform_grids()
+    vj0 = fftdf_get_j_kpts(ao_k, dms, a, mesh)
+    vk0 = fftdf_get_k_kpts(ao_k, dms, a, mesh, kpts, coords)
+    assert abs(vj - vj0).max() < 1e-7, abs(vj - vj0).max()
+    assert abs(vk - vk0).max() < 1e-7, abs(vk - vk0).max()
+
+    # exxdiv='ewald': + madelung(cell, kpts) S_k D_k S_k with the Madelung constant of the supercell
+    # (pyscf/pbc/df/df_jk.py:1425-1455, pyscf/pbc/tools/pbc.py:483-493)
+    vk_e = mydf.get_jk(dms, kpts=kpts, with_j=False, exxdiv='ewald')[1]
+    w = cell.vol / len(coords)
+    mad = madelung(mydf._kmesh.supercell)
+    for k in range(3):
+        s = w * ao_k[k].conj().T.dot(ao_k[k])
+        assert abs(vk_e[k] - vk0[k] - mad * s.dot(dms[k]).dot(s)).max() < 1e-7
+
+    # sets of density matrices, J only, and the order of the k-points
+    perm = [2, 0, 1]
+    df2 = ISDF(cell, kpts=kpts[perm], n_ip=60, tol=1e-15)
+    vj2 = df2.get_j(np.stack([dms[perm], 2 * dms[perm]]), kpts=kpts[perm])
+    assert vj2.shape == (2, 3, nao, nao)
+    assert abs(vj2[0] - vj[perm]).max() < 1e-9 and abs(vj2[1] - 2 * vj[perm]).max() < 1e-9
+
+
+def test_kmesh_rejects_what_the_supercell_cannot_serve():
+    cell = he_c_cell()
+    with pytest.raises(NotImplementedError):
+        ISDF(cell, kpts=np.array([[0.1, 0.2, 0.3]])).build()                 # not a uniform mesh
+    kpts = cell.make_kpts([3, 1, 1])
+    mydf = ISDF(cell, kpts=kpts, n_ip=60)
+    with pytest.raises(NotImplementedError):
+        mydf.get_jk(np.zeros((2, cell.nao, cell.nao)), kpts=kpts[:2])       # a different k-point list
+    with pytest.raises(NotImplementedError):
+        mydf.get_jk(np.zeros((3, cell.nao, cell.nao)), kpts=kpts, kpts_band=kpts[:1])
+    with pytest.raises(NotImplementedError):
+        mydf.get_nuc(kpts)
