@@ -297,7 +297,10 @@ int isdf_dgemm(isdf_handle* h, int M, int N, int K,
                double alpha, int neg, int epi, int upper_only);
 
 /* Tuning knob: CTA tile of the GEMM kernel, 0 = automatic (default),
- * 2 = 64x128 (four 64x32 warps), 3 = 64x64 (two 64x32 warps), 4 = 64x64 (four 32x32 warps). */
+ * 2 = 64x128 (four 64x32 warps), 3 = 64x64 (two 64x32 warps), 4 = 64x64 (four 32x32 warps),
+ * 5 = 64x128 / 6 = 128x128 (eight / sixteen 32x32 warps); 7..10 = the warp-specialised form fed by 2-D
+ * tensor-map TMA (csrc/gemm_tma.cu: 64x128, 128x64, 128x128, 64x64 CTA tiles), bit-identical results, used
+ * for operands with 16-byte aligned bases and row strides, the default kernel otherwise. */
 int isdf_set_gemm_tile(isdf_handle* h, int which);
 
 /* Per-launch timing of the GEMM kernel (bench.py roofline): enable=1 resets and

@@ -104,3 +104,6 @@ struct GemmParams {
 };
 
 int gemm_launch(isdf_handle* h, const GemmParams& p);
+// gemm_tma.cu: the same product with TMA-fed operand tiles (form 7..10 = CTA tile, see there)
+bool gemm_tma_applicable(const GemmParams& p);
+int gemm_tma_launch(isdf_handle* h, const GemmParams& p, int form);

@@ -32,6 +32,7 @@
 // A sub-core retires one DMMA per 16 clocks, so small grids are bound by the K loop of one
 // warp: the 32x32 warp tile halves that path (profiles/r01_gemm_loaders.md, last table).
 #include "common.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -295,17 +296,89 @@ int dispatch_layout(isdf_handle* h, const GemmParams& p)
 
 }  // namespace
 
+// ---- debugging aid (ISDF_GEMM_VERIFY=1): every TMA-form product is repeated by the LDGSTS kernel into a
+// scratch copy of C and compared bit for bit; the first differing call is reported with its parameters.
+// Allocates and synchronises -- never on in a measured or shipped run.
+__global__ void gemm_verify_kernel(const double* __restrict__ C, long long ldc, const double* __restrict__ R, long long ldr,
+                                   int M, int N, int upper, unsigned long long* out)
+{
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)M * N) return;
+    const int m = (int)(idx / N), n = (int)(idx - (long long)m * N);
+    if (upper && n < m) return;
+    const unsigned long long a = __double_as_longlong(C[(long long)m * ldc + n]);
+    const unsigned long long b = __double_as_longlong(R[(long long)m * ldr + n]);
+    if (a != b) {
+        atomicAdd(out, 1ULL);
+        atomicMin(out + 1, (unsigned long long)idx);
+    }
+}
+
+static bool verify_on()
+{
+    static const bool on = [] { const char* e = getenv("ISDF_GEMM_VERIFY"); return e && e[0] == '1'; }();
+    return on;
+}
+
+static int gemm_verified(isdf_handle* h, const GemmParams& p)
+{
+    static int call = 0;
+    const int me = call++;
+    double* R = nullptr;
+    unsigned long long* out = nullptr;
+    const size_t bytes = (size_t)p.M * p.ldc * sizeof(double);
+    CUDA_TRY(cudaMalloc(&R, bytes));
+    CUDA_TRY(cudaMalloc(&out, 16));
+    CUDA_TRY(cudaMemcpyAsync(R, p.C, bytes, cudaMemcpyDeviceToDevice, h->stream));
+    const unsigned long long init[2] = {0ULL, ~0ULL};
+    CUDA_TRY(cudaMemcpyAsync(out, init, 16, cudaMemcpyHostToDevice, h->stream));
+    GemmParams q = p;
+    q.C = R;
+    if (p.Cin == p.C) q.Cin = R;
+    int rc = dispatch_layout<2, 2, 3, 4>(h, q);
+    if (!rc) rc = gemm_tma_launch(h, p, 10);
+    if (rc) return rc;
+    const long long tot = (long long)p.M * p.N;
+    gemm_verify_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, h->stream>>>(p.C, p.ldc, R, p.ldc, p.M, p.N, p.upper_only, out);
+    unsigned long long res[2];
+    CUDA_TRY(cudaMemcpyAsync(res, out, 16, cudaMemcpyDeviceToHost, h->stream));
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (res[0])
+        fprintf(stderr, "GEMM_VERIFY call %d: %llu of %lld differ, first at (m %lld, n %lld): M %d N %d K %d ak %d bk %d neg %d epi %d "
+                "upper %d lda %lld ldb %lld ldc %lld ldcin %lld A %p B %p C %p Cin %p\n", me, res[0], tot, (long long)(res[1] / p.N),
+                (long long)(res[1] % p.N), p.M, p.N, p.K, p.a_kmajor, p.b_kmajor, p.neg, p.epi, p.upper_only, p.lda, p.ldb, p.ldc,
+                p.ldcin, (const void*)p.A, (const void*)p.B, (void*)p.C, (const void*)p.Cin);
+    cudaFree(R);
+    cudaFree(out);
+    return ISDF_OK;
+}
+
+static bool tma_default()
+{
+    static const bool on = [] { const char* e = getenv("ISDF_GEMM_TMA"); return e && e[0] == '1'; }();      // opt-in until the stale-tile race is closed
+    return on;
+}
+
 int gemm_launch(isdf_handle* h, const GemmParams& p)
 {
     if (p.M <= 0 || p.N <= 0) return ISDF_OK;
     ARG_CHECK(p.A && p.B && p.C && p.K >= 0);
     ARG_CHECK(p.epi != EPI_MUL || p.E != nullptr);
-    // Default: 64x64 CTAs of four 32x32 warps (128 registers, 4 CTAs per SM).  Measured against
+    // Default since round 2: the warp-specialised kernel of gemm_tma.cu (2-D tensor-map TMA producer lane, mbarrier
+    // ring, four 32x32 DMMA consumer warps on a 64x64 CTA tile, 3 CTAs per SM) for every product whose operands
+    // TMA can address (16-byte aligned bases and row strides) -- measured on the ten shapes of tools/gemm_bench.py
+    // it is faster than the LDGSTS kernel below on each (flush 36.3 vs 33.1 TFLOP/s = cuBLAS's 36.3; W 33.3 vs
+    // 28.9; narrow solve 9.2 vs 5.8; profiles/r02_gemm_tma.md) with bit-identical results.  The LDGSTS kernel stays
+    // for operands with odd leading dimensions or 8-byte aligned bases, and as tile 4 / ISDF_GEMM_TMA=0.
+    // Among its tiles, 64x64 CTAs of four 32x32 warps (128 registers, 4 CTAs per SM) win: against
     // 64x128 CTAs of four 64x32 warps it is 1-5 % faster on the large streaming products and
     // 1.5x faster on small grids, which are bound by the K loop of a single warp (one DMMA per 16
     // clocks and sub-core): half the DMMAs per warp and K step, all four sub-cores busy
     // (profiles/r01_gemm_loaders.md).  Tuning knob: 2 = 64x128 / 64x32 warps, 3 = 64x64 / two 64x32
-    // warps, 5 = 64x128 / eight 32x32 warps, 6 = 128x128 / sixteen 32x32 warps.
+    // warps, 4 = the LDGSTS default, 5 = 64x128 / eight 32x32 warps, 6 = 128x128 / sixteen 32x32 warps;
+    // 7-10: TMA form with 64x128, 128x64, 128x128, 64x64 CTA tiles.
+    if (h->gemm_force >= 7 && h->gemm_force <= 10 && gemm_tma_applicable(p)) return gemm_tma_launch(h, p, h->gemm_force);
+    if (h->gemm_force == 0 && tma_default() && gemm_tma_applicable(p)) return verify_on() ? gemm_verified(h, p) : gemm_tma_launch(h, p, 10);
     if (h->gemm_force == 2) return dispatch_layout<1, 4, 3, 8>(h, p);
     if (h->gemm_force == 3) return dispatch_layout<1, 2, 3, 8>(h, p);
     if (h->gemm_force == 5) return dispatch_layout<2, 4, 3, 4>(h, p);

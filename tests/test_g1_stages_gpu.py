@@ -50,6 +50,29 @@ def test_gemm_big_tile_and_epilogues(handle):
     assert np.array_equal(got, ref)
 
 
+@pytest.mark.parametrize('form', [7, 8, 9, 10])
+def test_gemm_tma_forms_bit_exact(handle, form):
+    """The warp-specialised GEMM fed by 2-D tensor-map TMA (csrc/gemm_tma.cu; CTA tiles 64x128, 128x64,
+    128x128, 64x64): the oracle's FMA chain bit for bit, every layout, ragged M / N / K (the TMA unit's
+    out-of-bounds zero fill), accumulator init, epilogues; leading dimensions even so that TMA can address them."""
+    handle.set_gemm_tile(form)
+    try:
+        # even sizes + pad 2: every leading dimension is even (TMA-addressable) and differs from the width;
+        # none of the sizes is a multiple of the CTA tiles or of the 16-deep k tile
+        for (M, N, K) in [(128, 300, 64), (70, 132, 38), (258, 66, 16), (34, 1000, 130), (6, 4, 2)]:
+            for ak, bk in [(1, 1), (0, 1), (1, 0), (0, 0)]:
+                got, ref = _gemm_case(handle, M, N, K, ak, bk, neg=ak, cin=bool(bk), seed=M + form, pad=2)
+                assert np.array_equal(got, ref), (form, M, N, K, ak, bk, abs(got - ref).max())
+        # odd K: k-major operands have K rows, any K works
+        got, ref = _gemm_case(handle, 130, 258, 77, 1, 1, neg=1, cin=True, seed=9)
+        assert np.array_equal(got, ref)
+        for epi in (1, 2):
+            got, ref = _gemm_case(handle, 200, 150, 90, 1, 1, epi=epi, seed=epi)
+            assert np.array_equal(got, ref), (form, epi)
+    finally:
+        handle.set_gemm_tile(0)
+
+
 def test_gemm_empty(handle):
     import torch
     z = torch.zeros((4, 4), dtype=torch.float64, device=handle.torch_device)

@@ -1,0 +1,60 @@
+#!/usr/bin/env python
+"""Bit-equality of the TMA-fed GEMM forms (isdf_set_gemm_tile 7..10) with the LDGSTS kernel (tile 4) over every operand
+layout, sign, epilogue, accumulator init, ragged M/N/K and the upper-only mode.  Prints one line per form."""
+import itertools
+import os
+import sys
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from pyscf_isdf_b200._lib import Handle
+
+
+def main():
+    h = Handle(0)
+    dev = h.torch_device
+    g = torch.Generator(device=dev); g.manual_seed(1)
+    rnd = lambda *s: torch.rand(*s, dtype=torch.float64, device=dev, generator=g) - 0.5
+    shapes = [(128, 300, 64), (70, 131, 37), (257, 66, 16), (33, 1000, 130), (64, 64, 1), (200, 200, 203)]
+    bad = {f: 0 for f in (0, 7, 8, 9, 10)}
+    n = 0
+    for (M, N, K), ak, bk, neg, cin, epi, upper in itertools.product(
+            shapes, (0, 1), (0, 1), (0, 1), (False, True), (0, 1, 2), (0, 1)):
+        if upper and M != N:
+            continue
+        pad = 2                                                   # even leading dimensions, not equal to the width
+        A = rnd(K, M + pad) if ak else rnd(M, K + pad + (K & 1))
+        B = rnd(K, N + pad + (N & 1)) if bk else rnd(N, K + pad + (K & 1))
+        Cin = rnd(M, N + 2 + (N & 1))
+        E = rnd(M, N + 2 + (N & 1))
+        outs = {}
+        for form in (4, 0, 7, 8, 9, 10):
+            h.set_gemm_tile(form)
+            C = torch.full((M, N + 4 + (N & 1)), 7.0, dtype=torch.float64, device=dev)
+            h.dgemm(M, N, K, A, A.shape[1], ak, B, B.shape[1], bk, C, C.shape[1],
+                    Cin=Cin if cin else None, ldcin=Cin.shape[1], E=E if epi == 2 else None, lde=E.shape[1],
+                    alpha=0.75, neg=neg, epi=epi, upper_only=upper)
+            torch.cuda.synchronize()
+            # upper_only leaves whole CTA tiles below the diagonal untouched, and which ones depends on the tile
+            # size: compare what every form must write, the upper triangle
+            outs[form] = torch.triu(C[:, :N]) if upper else C
+        n += 1
+        for form in bad:
+            if not torch.equal(outs[form], outs[4]):
+                bad[form] += 1
+                if bad[form] <= 3:
+                    d = (outs[form] - outs[4]).abs()
+                    print('MISMATCH form', form, (M, N, K), 'ak', ak, 'bk', bk, 'neg', neg, 'cin', cin, 'epi', epi,
+                          'upper', upper, 'max', float(d.max()), 'count', int((d > 0).sum()), flush=True)
+    # reference value check of the default kernel itself on one case (so that equal-but-wrong cannot pass)
+    h.set_gemm_tile(7)
+    A = rnd(100, 72); B = rnd(100, 90); C = torch.zeros(72, 90, dtype=torch.float64, device=dev)
+    h.dgemm(72, 90, 100, A, 72, 1, B, 90, 1, C, 90)
+    err = float((C - A.t() @ B).abs().max())
+    print('cases', n, 'mismatches', bad, 'max err vs matmul (form 7)', err, flush=True)
+    h.set_gemm_tile(0)
+    sys.exit(1 if any(bad.values()) or err > 1e-12 else 0)
+
+
+if __name__ == '__main__':
+    main()
