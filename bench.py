@@ -124,7 +124,7 @@ class ClockSampler:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['no samples']}
         # median over samples taken under load (power above the idle floor)
         load = [s for s, p in zip(sm, pw) if p > 0.5 * max(pw)] or sm
-        return {'sm_mhz': float(np.median(load)), 'sm_max_mhz': float(max(mx)),
+        return {'sm_mhz': float(np.median(load)), 'sm_mhz_mean': float(np.mean(load)), 'sm_max_mhz': float(max(mx)),
                 'sm_mhz_min_under_load': float(min(load)), 'sm_mhz_p10_under_load': float(np.percentile(load, 10)),
                 'power_w_max': float(max(pw)), 'power_w_median_under_load': float(np.median([p for p in pw if p > 0.5 * max(pw)])),
                 'samples': len(sm), 'period_ms': self.period, 'reasons': sorted(reasons)}
@@ -667,14 +667,17 @@ def run_b200(args):
     if args.no_e2e:
         vj, vk = mydf.get_jk(dm_host[0], exxdiv=exxdiv)
         e2e_s = float('nan')
+        clocks_e2e = None
     else:
         step_e2e()
         barrier()
+        sampler2 = ClockSampler(local).start() if rank == 0 else None
         t0 = time.perf_counter()
         for _ in range(args.steps):                  # all K steps, every one a full build + J/K through host buffers
             vj, vk = step_e2e()
         barrier()
         e2e_s = (time.perf_counter() - t0) / args.steps
+        clocks_e2e = sampler2.stop() if sampler2 else None
     # bytes that cross the PCIe link per step: the cell tables and lattice images isdf_eval_ao takes as host
     # arrays, the density matrix through the object's pinned staging buffer (counted where it is copied,
     # ISDF.get_jk) on the way in; J, K (counted likewise) and the selected points + residuals on the way out
@@ -711,16 +714,17 @@ def run_b200(args):
     fm = workloads.flop_model(nao, ng, mydf.n_ip, cell.mesh, args.fit)
     achieved = gflops / (gms * 1e-3) / 1e12 if gms > 0 else 0.0
     roofline = {
-        'kernel': 'dgemm_kernel (FP64 FMA GEMM, all layouts/epilogues)', 'bound': 'tensor',
+        'kernel': 'dgemm_tma_kernel (FP64 DMMA GEMM fed by 2-D tensor-map TMA, all layouts/epilogues; '
+                  'dgemm_kernel for operands TMA cannot address)', 'bound': 'tensor',
         'achieved': achieved, 'peak': fp64_peak, 'unit': 'TFLOP/s',
         'frac': achieved / fp64_peak if fp64_peak else None,
         'peak_source': 'cuBLAS DGEMM 8192^3 best-of-10 measured in this run (MEASURED_PEAKS.json has no FP64 entry)',
         'launches_per_step': gcount / args.steps, 'flops_per_step': gflops / args.steps,
         'gemm_ms_per_step': gms / args.steps, 'gemm_share_of_step': gms / total_ms,
         # DRAM bytes of one representative launch of this kernel from an `ncu --set full` capture
-        # (flush GEMM M=128 N=357912 K=6240: 19.3 GB against 18.6 GB algorithmic, profiles/r01_ncu_final.md)
+        # (flush GEMM M=128 N=357912 K=6240: 19.1 GB against 18.6 GB algorithmic, profiles/r02_gemm_tma.md)
     }
-    tr = kernel_traffic('dgemm_kernel') if name == 'c64' else None
+    tr = kernel_traffic('dgemm_tma_kernel') if name == 'c64' else None
     roofline['traffic'] = tr['dram_bytes'] if tr else None
     roofline['traffic_launch'] = ('%s: algorithmic %.3g B (%s)' % (tr['launch'], tr['algorithmic_bytes'], tr['source'])) if tr else None
     line = {
@@ -736,7 +740,8 @@ def run_b200(args):
         'each_step_ms': each_ms,
         'stages_ms_each': {k: [float(x) for x in v] for k, v in stage_acc.items() if k.endswith('_ms')},
         'flop_model': fm,
-        'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
+        'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+                'sm_mhz_mean': (clocks_e2e or {}).get('sm_mhz_mean'), 'sm_mhz_median': (clocks_e2e or {}).get('sm_mhz')},
         'gpu_launches': int((l1[0] - l0[0]) + (l1[1] - l0[1])),
         'roofline': roofline, 'clocks': clocks, 'host': host_delta,
     }

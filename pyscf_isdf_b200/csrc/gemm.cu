@@ -355,7 +355,7 @@ static int gemm_verified(isdf_handle* h, const GemmParams& p)
 
 static bool tma_default()
 {
-    static const bool on = [] { const char* e = getenv("ISDF_GEMM_TMA"); return e && e[0] == '1'; }();      // opt-in until the stale-tile race is closed
+    static const bool on = [] { const char* e = getenv("ISDF_GEMM_TMA"); return !(e && e[0] == '0'); }();
     return on;
 }
 

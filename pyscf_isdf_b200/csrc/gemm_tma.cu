@@ -1,6 +1,6 @@
 // FP64 GEMM, warp-specialised form: operand tiles arrive by 2-D tensor-map TMA (cp.async.bulk.tensor.2d, SASS
 // UTMALDG) from ONE producer lane into an mbarrier ring; the DMMA consumer warps never meet a CTA-wide barrier
-// in the K loop.  Same arithmetic contract as gemm.cu (every C element is one ascending-k FMA chain from Cin,
+// in the K loop (they release a stage with fence.proxy.async + mbarrier.arrive, see the loop).  Same arithmetic contract as gemm.cu (every C element is one ascending-k FMA chain from Cin,
 // K tail and ragged edges zero-filled -- here by the TMA unit's out-of-bounds fill), so results are
 // bit-identical to dgemm_kernel; tests/test_g1_stages_gpu.py compares the two forms bit for bit.
 //
@@ -22,12 +22,6 @@
 namespace {
 
 constexpr int BK = 16;
-#ifndef TMA_VARIANT
-#define TMA_VARIANT 0
-#endif
-#ifndef TMA_NSTAGE
-#define TMA_NSTAGE 4
-#endif
 constexpr long long WAIT_LIMIT = 4000000000LL;      // ~2 s of SM clocks
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -178,38 +172,36 @@ dgemm_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
     }
 
-    // Fragments are single-buffered (64 accumulator + 16 fragment registers fit the 96 a CTA pair leaves per
-    // thread); the LDS latency of one warp is covered by the other three warps of its sub-core, which own the
-    // DMMA pipe meanwhile -- no CTA-wide barrier ever lines them up.
-    constexpr int dbg = TMA_VARIANT;
+    // Fragments are single-buffered (64 accumulator + 16 fragment registers); the LDS latency of one warp is
+    // covered by the other warps of its sub-core, which own the DMMA pipe meanwhile -- no CTA-wide barrier ever
+    // lines them up.
+    //
+    // Handing a stage back: the tiles are written by the async proxy (TMA) and read by the generic proxy (LDS).
+    // The mbarrier alone orders the two only in the RAW direction (the completion of a bulk copy carries an
+    // implicit proxy fence); for WAR -- our reads, then the next TMA write into the same stage -- every lane
+    // issues fence.proxy.async after its last read and before the warp's arrive on the empty barrier.  Without
+    // it co-resident CTAs (>= 2 per SM) read stale rows of the previous tile of a stage: 199 of 200 products
+    // of a flush shape differed from the LDGSTS kernel; with it 0 of 1800 (tools/gpu_tma_variants.sh,
+    // profiles/r02_gemm_tma.md).  A fence on the acquire side does not help, nor does arriving after the
+    // DMMAs that consumed the fragments.
     for (int kt = 0; kt < nk; ++kt) {
         const int s = kt % NSTAGE;
         const double* As = tiles + s * STAGE;
         mbar_wait(bar_full + 8 * s, (kt / NSTAGE) & 1);
-        if (dbg & 4) __syncwarp();
-        if (dbg & 16) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
             double a[4], b[4];
             load_frag<AK>(As, wm, 4 * ks, g, t, a);
             load_frag<BKM>(As + A_SZ, wn, 4 * ks, g, t, b);
-            if (ks == 3 && !(dbg & 1)) {
-                if (dbg & 2) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            if (ks == 3) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 __syncwarp();
-                if (lane == 0) {
-                    if (dbg & 8) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    mbar_arrive(bar_empty + 8 * s);
-                }
+                if (lane == 0) mbar_arrive(bar_empty + 8 * s);
             }
 #pragma unroll
             for (int i = 0; i < 4; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) dmma884(acc[i][j], NEG ? -a[i] : a[i], b[j]);
-            if (ks == 3 && (dbg & 1)) {
-                if (dbg & 2) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_empty + 8 * s);
-            }
         }
     }
 
@@ -343,7 +335,7 @@ int gemm_tma_launch(isdf_handle* h, const GemmParams& p, int form)
     switch (form) {
     case 8: return dispatch_tma<4, 2, 4>(h, p);
     case 9: return dispatch_tma<4, 4, 4>(h, p);
-    case 10: return dispatch_tma<2, 2, TMA_NSTAGE>(h, p);
+    case 10: return dispatch_tma<2, 2, 4>(h, p);
     default: return dispatch_tma<2, 4, 4>(h, p);
     }
 }

@@ -63,6 +63,7 @@ class ISDF:
         # comm: a pyscf_isdf_b200.dist.Comm (one process per GPU, grid sharded by x-planes)
         self.comm = comm
         self._rsh_df = {}
+        self._pinned = None        # pinned host staging buffers of get_jk, kept across reset()
         self._kmesh = None         # kmesh.KMesh when self.kpts is a uniform mesh (served by the supercell's ISDF)
         self._sc = None
         self.h2d_bytes = self.d2h_bytes = 0      # bytes the last get_jk() copied over PCIe (counted at the copies)
@@ -95,7 +96,8 @@ class ISDF:
         self._part = None
         self._slab = None
         self._aoR4 = None          # AO values + gradients of nr_rks
-        self._pinned = None        # pinned host staging buffers of get_jk
+        # (the pinned host staging buffers of get_jk, self._pinned, depend on nao only and are re-checked there:
+        # re-pinning 17 MB per geometry step costs more than the copies they serve)
         if getattr(self, '_sc', None) is not None:
             self._sc.reset()
         if cell is not None:

@@ -73,6 +73,38 @@ def test_gemm_tma_forms_bit_exact(handle, form):
         handle.set_gemm_tile(0)
 
 
+def test_gemm_tma_many_ctas_per_sm(handle):
+    """Flush-shaped products (C and B are rows of one matrix, in place) wide enough for three CTAs per SM and
+    several waves: the default kernel (TMA-fed where it applies) bit-equal to the LDGSTS kernel, ten times each, and to
+    the oracle's FMA chain once.  This is the case a missing generic->async proxy fence corrupts (gemm_tma.cu)."""
+    import torch
+    dev = handle.torch_device
+    g = torch.Generator(device=dev); g.manual_seed(3)
+    N, ld = 42875, 42880
+    for M, K, ak in [(64, 192, 0), (52, 194, 0), (128, 400, 1)]:
+        A = torch.rand((K, M + 2) if ak else (M, K + 2), dtype=torch.float64, device=dev, generator=g) - 0.5
+        Lt = torch.rand((K + M, ld), dtype=torch.float64, device=dev, generator=g) - 0.5
+        C0 = Lt[K:].clone()
+        ref = None
+        try:
+            for rep, form in enumerate([4] + [0] * 10):
+                handle.set_gemm_tile(form)
+                Lt[K:].copy_(C0)
+                torch.cuda.synchronize()
+                handle.dgemm(M, N, K, A, A.shape[1], ak, Lt, ld, 1, Lt[K:], ld, Cin=Lt[K:], ldcin=ld, neg=1)
+                torch.cuda.synchronize()
+                if form == 4:
+                    ref = Lt[K:, :N].clone()
+                else:
+                    assert torch.equal(Lt[K:, :N], ref), (M, K, rep, int((Lt[K:, :N] != ref).sum()))
+        finally:
+            handle.set_gemm_tile(0)
+        if M == 52:
+            a = A[:, :M].cpu().numpy() if ak else A[:, :K].cpu().numpy()
+            chain = c_oracle.gemm_chain(a, ak, Lt[:K, :N].cpu().numpy(), 1, Cin=C0[:, :N].cpu().numpy(), alpha=1.0, neg=1)
+            assert np.array_equal(ref.cpu().numpy(), chain)
+
+
 def test_gemm_empty(handle):
     import torch
     z = torch.zeros((4, 4), dtype=torch.float64, device=handle.torch_device)

@@ -46,6 +46,31 @@ def main():
                     d = (outs[form] - outs[4]).abs()
                     print('MISMATCH form', form, (M, N, K), 'ak', ak, 'bk', bk, 'neg', neg, 'cin', cin, 'epi', epi,
                           'upper', upper, 'max', float(d.max()), 'count', int((d > 0).sum()), flush=True)
+    # many CTAs per SM and several waves, in place like the selection flush (C and B rows of one matrix): the
+    # shapes on which a missing proxy fence between the consumers' reads and the next TMA write shows (stale rows
+    # of a stage; no small shape ever showed it)
+    waves = 0
+    for (M, K), (ak, bk) in itertools.product([(64, 192), (52, 194), (128, 400), (64, 1560)], [(0, 1), (1, 1), (0, 0), (1, 0)]):
+        N, ld = 42875, 42880
+        A = rnd(K, M + 2) if ak else rnd(M, K + 2)
+        Lt = rnd(K + M, ld) if bk else None
+        B = Lt if bk else rnd(N, K + 2)
+        C0 = rnd(M, ld)
+        ref = None
+        for form in (4, 0, 0, 0, 7, 8, 9, 10, 10, 10):
+            h.set_gemm_tile(form)
+            C = Lt[K:] if bk else torch.empty(M, ld, dtype=torch.float64, device=dev)
+            C.copy_(C0)
+            torch.cuda.synchronize()
+            h.dgemm(M, N, K, A, A.shape[1], ak, B, B.shape[1], bk, C, ld, Cin=C, ldcin=ld, neg=1)
+            torch.cuda.synchronize()
+            if form == 4:
+                ref = C[:, :N].clone()
+            elif not torch.equal(C[:, :N], ref):
+                bad[form] += 1
+                print('MISMATCH (many CTAs) form', form, (M, N, K), 'ak', ak, 'bk', bk, 'count', int((C[:, :N] != ref).sum()), flush=True)
+        waves += 1
+    print('multi-wave cases', waves, flush=True)
     # reference value check of the default kernel itself on one case (so that equal-but-wrong cannot pass)
     h.set_gemm_tile(7)
     A = rnd(100, 72); B = rnd(100, 90); C = torch.zeros(72, 90, dtype=torch.float64, device=dev)
