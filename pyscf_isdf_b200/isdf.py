@@ -156,13 +156,7 @@ class ISDF:
         self.check_sanity()
         if self._kmesh is not None:
             # k-point mesh: the Gamma-point ISDF of the supercell does all the work (kmesh.py)
-            if self._sc is None:
-                self._sc = ISDF(self._kmesh.supercell, c=self.c, n_ip=None, select=self.select, fit=self.fit,
-                                tol=self.tol, device=self._device, keep_aoR=self.keep_aoR, comm=self.comm,
-                                wgemm=self.wgemm, exact_j=self.exact_j)
-                if self.n_ip:
-                    self._sc.n_ip = int(self.n_ip) * self._kmesh.nk
-                self._sc.verbose, self._sc.stdout = self.verbose, self.stdout
+            self._supercell_df()
             self._sc.build()
             self.ip_index, self.ip_resid, self.W = self._sc.ip_index, self._sc.ip_resid, self._sc.W
             self.timings = self._sc.timings
@@ -418,9 +412,37 @@ class ISDF:
     # -- hcore pieces on the same device-resident AO values ("next" row 2 of SURVEY 8f) ----------
     def _check_gamma(self, kpts):
         if self._kmesh is not None or abs(self.kpts).sum() > 1e-9:
-            raise NotImplementedError('ISDF at k-points serves get_jk / get_j / get_k only')
+            raise NotImplementedError('ISDF at k-points: not served through the supercell')
         if kpts is not None and abs(np.asarray(kpts)).sum() > 1e-9:
             raise NotImplementedError('ISDF is Gamma-point only')
+
+    def _supercell_df(self):
+        """The Gamma-point ISDF object of the k-mesh's supercell (kmesh.py), created on first use, not built."""
+        if self._sc is None:
+            self._sc = ISDF(self._kmesh.supercell, c=self.c, n_ip=None, select=self.select, fit=self.fit,
+                            tol=self.tol, device=self._device, keep_aoR=self.keep_aoR, comm=self.comm,
+                            wgemm=self.wgemm, exact_j=self.exact_j)
+            if self.n_ip:
+                self._sc.n_ip = int(self.n_ip) * self._kmesh.nk
+            self._sc.verbose, self._sc.stdout = self.verbose, self.stdout
+        return self._sc
+
+    def _on_kmesh(self, kpts):
+        """True when the call is for the uniform k-point mesh this object was made for (then the supercell
+        serves it); raises for any other k-point list."""
+        if self._kmesh is None and abs(self.kpts).sum() > 1e-9:
+            self.check_sanity()
+        if self._kmesh is None:
+            return False
+        kpts = self.kpts if kpts is None else np.reshape(kpts, (-1, 3))
+        if kpts.shape != self.kpts.shape or abs(kpts - self.kpts).max() > 1e-9:
+            raise NotImplementedError('ISDF at k-points serves exactly the uniform mesh it was made for')
+        return True
+
+    def _folded(self, name, *args):
+        """A lattice-periodic one-electron operator at the mesh's k-points from the supercell's Gamma-point
+        matrix: V_k = 1/Nk sum_RR' exp(ik.(R'-R)) V_sc[(R mu),(R' nu)]  (kmesh.KMesh.mat_to_kpts)."""
+        return self._kmesh.mat_to_kpts(getattr(self._supercell_df(), name)(*args))
 
     def _ao_on_grid(self):
         """AO values of this rank's grid slab: the build's copy when it was kept, else stage 1 alone
@@ -468,12 +490,16 @@ class ISDF:
     def get_nuc(self, kpts=None):
         """Nuclear attraction of point charges -Z, G=0 removed (FFTDF.get_nuc, pyscf/pbc/df/fft.py:39-62)."""
         from . import pseudo
+        if self._on_kmesh(kpts):
+            return self._folded('get_nuc')
         self._check_gamma(kpts)
         return self.potential_matrix_device(pseudo.nuc_on_grid(self.cell, self.mesh)).cpu().numpy()
 
     def get_pp_loc(self, kpts=None):
         """Local part of the GTH pseudopotential matrix (pyscf/pbc/df/fft.py:70-84)."""
         from . import pseudo
+        if self._on_kmesh(kpts):
+            return self._folded('get_pp_loc')
         self._check_gamma(kpts)
         return self.potential_matrix_device(pseudo.pp_loc_on_grid(self.cell, self.mesh)).cpu().numpy()
 
@@ -486,6 +512,8 @@ class ISDF:
         reference).  With several ranks each takes a contiguous range of reciprocal vectors and the
         projector-AO overlaps are summed over ranks before h_ij is applied."""
         from . import pseudo
+        if self._on_kmesh(kpts):
+            return self._folded('get_pp_nl', None, on_device)
         self._check_gamma(kpts)
         cell = self.cell
         nao = cell.nao_nr()
@@ -554,6 +582,14 @@ class ISDF:
         The AO values and gradients of the slab (32 nao ngl bytes) are kept between calls when they fit in
         ``max_bytes`` (default ``XC_CACHE_BYTES``); a larger slab is walked in chunks of that size whose AO
         gradients are re-evaluated on every call, the way the reference's ``block_loop`` does (numint.py:354-356)."""
+        if self._on_kmesh(kpts):
+            # KNumInt.nr_rks (pyscf/pbc/dft/numint.py:1090-1204) for a uniform mesh: the density of the k-point
+            # density matrices is the supercell density of D_sc (only its real symmetric part reaches rho with
+            # real AOs); electrons and energy come per unit cell, the potential matrix is folded back
+            km = self._kmesh
+            dsc = km.dm_to_supercell(np.asarray(dm).reshape(km.nk, km.nao, km.nao))
+            ne, exc, vsc = self._supercell_df().nr_rks(xc_code, np.ascontiguousarray(dsc.real), None, max_bytes)
+            return ne / km.nk, exc / km.nk, km.mat_to_kpts(vsc)
         self._check_gamma(kpts)
         h = self.handle
         dm = np.asarray(dm, dtype=np.float64)

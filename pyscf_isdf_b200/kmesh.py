@@ -14,7 +14,8 @@ odd kmesh * mesh, Nyquist-plane differences otherwise).  Every flop runs in the 
 (pyscf_isdf_b200/isdf.py) -- this module is host-side bookkeeping: mesh detection, the two Bloch transformations,
 and the split of a complex supercell density matrix into its real symmetric and real antisymmetric parts (J and K
 are linear, the device path is real).  It does NOT exploit translational symmetry: cost and memory are those of the
-supercell.  Arbitrary k-point lists, kpts_band and twisted meshes raise NotImplementedError.
+supercell.  The one-electron pieces (ISDF.get_nuc / get_pp / nr_rks) fold the same way (isdf.py: _folded).
+Arbitrary k-point lists, kpts_band and twisted meshes raise NotImplementedError.
 """
 import numpy as np
 

@@ -153,3 +153,40 @@ def test_projector_overlaps_equal_the_real_space_integrals():
     ov_G = np.array([(1j)**l * z for l, z in zip(ls, Z)])      # the reference drops the projector's (-i)^l: it cancels in Z^H h Z
     assert abs(ov_real).max() > 0.1
     assert abs(ov_G.imag).max() < 1e-12 and abs(ov_G.real - ov_real).max() < 1e-8
+
+
+def test_kmesh_fold_of_hcore_matches_the_kpoint_oracle():
+    """get_nuc / get_pp on a uniform k-point mesh are served by the supercell (ISDF._folded, kmesh.py): the
+    supercell's Gamma-point matrices -- here from the product's host routines and a NumPy contraction where the
+    device contraction stands in the product -- folded to the k-points equal the k-point oracle, which reproduces
+    the reference's fingerprints (test above)."""
+    import oracle
+    from pyscf_isdf_b200.kmesh import KMesh
+    # The local parts fold exactly on any mesh (same real-space points).  The projector part is a sum over the
+    # mesh's plane waves k + G (pyscf/pbc/df/fft.py:100-141): the union of those sets over the k-mesh is the
+    # supercell's set shifted by less than one primitive reciprocal vector at the edge, so the two agree to the
+    # projectors' weight at the plane-wave cutoff -- 1e-3 on an 11-point mesh, below 1e-8 on this one (21 points)
+    cell = he_c_cell()
+    kpts = cell.make_kpts([3, 1, 1])
+    km = KMesh(cell, kpts)
+    sc = km.supercell
+    rcut, Ls = sc.ao_eval_params()
+    ao_sc = oracle.eval_ao(sc._atm, sc._bas, sc._env, sc.get_uniform_grids(), Ls, rcut)
+    w_sc = sc.vol / ao_sc.shape[0]
+    contract = lambda v: w_sc * (ao_sc.T * v).dot(ao_sc)
+    nuc_k = km.mat_to_kpts(contract(pseudo.nuc_on_grid(sc)))
+    pp_k = km.mat_to_kpts(contract(pseudo.pp_loc_on_grid(sc)) + pseudo.pp_nl_matrix(sc))
+
+    rcut, Ls = cell.ao_eval_params()
+    ao = oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, kpts=kpts)
+    coords, charges, pps = _atoms(cell)
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    w = cell.vol / ao.shape[1]
+    vne = opp.nuc_on_grid(a, mesh, coords, charges)
+    vloc = opp.pp_loc_on_grid(a, mesh, coords, charges, pps)
+    for k in range(3):
+        A = ao[k]
+        ref_nuc = w * (A.conj().T * vne).dot(A)
+        ref_pp = w * (A.conj().T * vloc).dot(A) + opp.pp_nl_matrix(a, mesh, cell._atm, cell._bas, cell._env, coords, pps, kpts[k])
+        assert abs(nuc_k[k] - ref_nuc).max() < 1e-8, abs(nuc_k[k] - ref_nuc).max()
+        assert abs(pp_k[k] - ref_pp).max() < 1e-8, abs(pp_k[k] - ref_pp).max()

@@ -69,4 +69,48 @@ def test_kmesh_rejects_what_the_supercell_cannot_serve():
     with pytest.raises(NotImplementedError):
         mydf.get_jk(np.zeros((3, cell.nao, cell.nao)), kpts=kpts, kpts_band=kpts[:1])
     with pytest.raises(NotImplementedError):
-        mydf.get_nuc(kpts)
+        mydf.get_nuc(kpts[:2])
+
+
+def test_kmesh_hcore_and_xc_match_the_kpoint_oracle():
+    """get_nuc / get_pp / nr_rks on the k-mesh: the supercell's device results folded to the k-points, against the
+    k-point oracle (pinned to the reference's get_nuc / get_pp fingerprints and nr_rks numbers in the CPU tests)."""
+    from oracle import pseudo as opp, xc
+    cell = he_c_cell()
+    nao = cell.nao
+    kpts = cell.make_kpts([3, 1, 1])
+    mydf = ISDF(cell, kpts=kpts, n_ip=60)
+    vnuc, vpp = mydf.get_nuc(kpts), mydf.get_pp(kpts)
+    assert vnuc.shape == vpp.shape == (3, nao, nao)
+
+    rcut, Ls = cell.ao_eval_params()
+    coords_g = cell.get_uniform_grids()
+    ao = oracle.eval_ao(cell._atm, cell._bas, cell._env, coords_g, Ls, rcut, kpts=kpts, deriv=1)
+    a, mesh = cell.lattice_vectors(), cell.mesh
+    coords = cell.atom_coords()
+    charges = [float(z) for z in cell.atom_charges()]
+    pps = [cell._pseudo_for(cell.atom_symbol(i)) for i in range(cell.natm)]
+    w = cell.vol / len(coords_g)
+    vne = opp.nuc_on_grid(a, mesh, coords, charges)
+    vloc = opp.pp_loc_on_grid(a, mesh, coords, charges, pps)
+    for k in range(3):
+        A = ao[k][0]
+        assert abs(vnuc[k] - w * (A.conj().T * vne).dot(A)).max() < 1e-8
+        ref = w * (A.conj().T * vloc).dot(A) + opp.pp_nl_matrix(a, mesh, cell._atm, cell._bas, cell._env, coords, pps, kpts[k])
+        assert abs(vpp[k] - ref).max() < 1e-8
+
+    rng = np.random.default_rng(5)
+    dms = rng.random((3, nao, nao)) + 1j * rng.random((3, nao, nao))
+    dms = 0.2 * (dms + dms.conj().transpose(0, 2, 1)) + np.eye(nao)          # positive density
+    ne, exc, vmat = mydf.nr_rks('pbe', dms, kpts)
+    rho = sum(xc.eval_rho(ao[k], dms[k]) for k in range(3)) / 3
+    assert rho[0].min() > 0
+    sigma = np.einsum('xg,xg->g', rho[1:], rho[1:])
+    e, vrho, vsigma = xc.eval_xc('pbe', rho[0], sigma)
+    wv = np.empty_like(rho)
+    wv[0] = w * vrho * .5
+    wv[1:] = w * 2 * vsigma * rho[1:]
+    assert abs(ne - w * rho[0].sum()) < 1e-8 and abs(exc - w * rho[0].dot(e)) < 1e-8
+    for k in range(3):
+        mat = ao[k][0].conj().T.dot(np.einsum('npi,np->pi', ao[k], wv))
+        assert abs(vmat[k] - (mat + mat.conj().T)).max() < 1e-8
