@@ -256,8 +256,9 @@ EncodeTiledFn encode_fn()
 // operand [rows of k | rows of x] -> 2-D map with 128-byte inner boxes, zero fill outside (K tail, ragged x edge)
 int make_map(CUtensorMap* map, const double* ptr, long long ld, int dimX, int K, bool kmajor, int bx)
 {
+    // returns 1 (not an error code) when the map cannot be made: the caller then takes the LDGSTS kernel
     EncodeTiledFn enc = encode_fn();
-    if (!enc) { isdf_set_error("cuTensorMapEncodeTiled is not available from this driver"); return ISDF_ERR_CUDA; }
+    if (!enc) return 1;
     cuuint64_t dims[2] = {(cuuint64_t)(kmajor ? dimX : K), (cuuint64_t)(kmajor ? K : dimX)};
     cuuint64_t strides[1] = {(cuuint64_t)ld * 8};
     cuuint32_t box[2] = {16, (cuuint32_t)(kmajor ? BK : bx)};
@@ -265,8 +266,7 @@ int make_map(CUtensorMap* map, const double* ptr, long long ld, int dimX, int K,
     CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)ptr, dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) { isdf_set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return ISDF_ERR_CUDA; }
-    return ISDF_OK;
+    return r == CUDA_SUCCESS ? ISDF_OK : 1;
 }
 
 template <int WM, int WN, int NSTAGE, bool AK, bool BKM, bool NEG>
@@ -328,6 +328,7 @@ bool gemm_tma_applicable(const GemmParams& p)
            p.lda * 8 < (1LL << 40) && p.ldb * 8 < (1LL << 40);
 }
 
+// returns 1 when a tensor map could not be encoded (nothing launched): gemm_launch falls back to dgemm_kernel.
 // form: 7 = 64x128 CTA tile (2x4 consumer warps, 2 CTAs per SM), 8 = 128x64 (4x2), 9 = 128x128 (4x4, one CTA per SM),
 // 10 = 64x64 (2x2, 3 CTAs per SM)
 int gemm_tma_launch(isdf_handle* h, const GemmParams& p, int form)

@@ -172,8 +172,7 @@ def test_kmesh_fold_of_hcore_matches_the_kpoint_oracle():
     sc = km.supercell
     rcut, Ls = sc.ao_eval_params()
     ao_sc = oracle.eval_ao(sc._atm, sc._bas, sc._env, sc.get_uniform_grids(), Ls, rcut)
-    w_sc = sc.vol / ao_sc.shape[0]
-    contract = lambda v: w_sc * (ao_sc.T * v).dot(ao_sc)
+    contract = lambda v: (ao_sc.T * v).dot(ao_sc)          # fft.py:55-56, :79-81: the grid potentials carry the weight
     nuc_k = km.mat_to_kpts(contract(pseudo.nuc_on_grid(sc)))
     pp_k = km.mat_to_kpts(contract(pseudo.pp_loc_on_grid(sc)) + pseudo.pp_nl_matrix(sc))
 
@@ -181,12 +180,11 @@ def test_kmesh_fold_of_hcore_matches_the_kpoint_oracle():
     ao = oracle.eval_ao(cell._atm, cell._bas, cell._env, cell.get_uniform_grids(), Ls, rcut, kpts=kpts)
     coords, charges, pps = _atoms(cell)
     a, mesh = cell.lattice_vectors(), cell.mesh
-    w = cell.vol / ao.shape[1]
     vne = opp.nuc_on_grid(a, mesh, coords, charges)
     vloc = opp.pp_loc_on_grid(a, mesh, coords, charges, pps)
     for k in range(3):
         A = ao[k]
-        ref_nuc = w * (A.conj().T * vne).dot(A)
-        ref_pp = w * (A.conj().T * vloc).dot(A) + opp.pp_nl_matrix(a, mesh, cell._atm, cell._bas, cell._env, coords, pps, kpts[k])
+        ref_nuc = (A.conj().T * vne).dot(A)
+        ref_pp = (A.conj().T * vloc).dot(A) + opp.pp_nl_matrix(a, mesh, cell._atm, cell._bas, cell._env, coords, pps, kpts[k])
         assert abs(nuc_k[k] - ref_nuc).max() < 1e-8, abs(nuc_k[k] - ref_nuc).max()
         assert abs(pp_k[k] - ref_pp).max() < 1e-8, abs(pp_k[k] - ref_pp).max()
