@@ -668,15 +668,19 @@ def run_b200(args):
         vj, vk = mydf.get_jk(dm_host[0], exxdiv=exxdiv)
         e2e_s = float('nan')
         clocks_e2e = None
+        e2e_each = None
     else:
         step_e2e()
         barrier()
         sampler2 = ClockSampler(local).start() if rank == 0 else None
         t0 = time.perf_counter()
+        e2e_marks = [t0]
         for _ in range(args.steps):                  # all K steps, every one a full build + J/K through host buffers
             vj, vk = step_e2e()
+            e2e_marks.append(time.perf_counter())
         barrier()
         e2e_s = (time.perf_counter() - t0) / args.steps
+        e2e_each = [b - a for a, b in zip(e2e_marks[:-1], e2e_marks[1:])]     # rank 0's view; `value` is the mean over all
         clocks_e2e = sampler2.stop() if sampler2 else None
     # bytes that cross the PCIe link per step: the cell tables and lattice images isdf_eval_ao takes as host
     # arrays, the density matrix through the object's pinned staging buffer (counted where it is copied,
@@ -741,7 +745,8 @@ def run_b200(args):
         'stages_ms_each': {k: [float(x) for x in v] for k, v in stage_acc.items() if k.endswith('_ms')},
         'flop_model': fm,
         'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                'sm_mhz_mean': (clocks_e2e or {}).get('sm_mhz_mean'), 'sm_mhz_median': (clocks_e2e or {}).get('sm_mhz')},
+                'sm_mhz_mean': (clocks_e2e or {}).get('sm_mhz_mean'), 'sm_mhz_median': (clocks_e2e or {}).get('sm_mhz'),
+                'each_step_s': e2e_each},
         'gpu_launches': int((l1[0] - l0[0]) + (l1[1] - l0[1])),
         'roofline': roofline, 'clocks': clocks, 'host': host_delta,
     }
