@@ -140,7 +140,7 @@ extern "C" int isdf_stage_time_ms(isdf_handle* h, int stage, float* out)
 
 extern "C" int isdf_set_gemm_tile(isdf_handle* h, int which)
 {
-    ARG_CHECK(h != nullptr && (which == 0 || (which >= 2 && which <= 10)));
+    ARG_CHECK(h != nullptr && (which == 0 || (which >= 2 && which <= 11)));
     h->gemm_force = which;
     return ISDF_OK;
 }

@@ -376,10 +376,10 @@ int gemm_launch(isdf_handle* h, const GemmParams& p)
     // clocks and sub-core): half the DMMAs per warp and K step, all four sub-cores busy
     // (profiles/r01_gemm_loaders.md).  Tuning knob: 2 = 64x128 / 64x32 warps, 3 = 64x64 / two 64x32
     // warps, 4 = the LDGSTS default, 5 = 64x128 / eight 32x32 warps, 6 = 128x128 / sixteen 32x32 warps;
-    // 7-10: TMA form with 64x128, 128x64, 128x128, 64x64 CTA tiles.
-    if (((h->gemm_force >= 7 && h->gemm_force <= 10) || (h->gemm_force == 0 && tma_default())) && gemm_tma_applicable(p)) {
+    // 7-11: TMA form with 64x128, 128x64, 128x128, 64x64, 32x128 CTA tiles (default: 64x64, 32x128 when M <= 32).
+    if (((h->gemm_force >= 7 && h->gemm_force <= 11) || (h->gemm_force == 0 && tma_default())) && gemm_tma_applicable(p)) {
         if (h->gemm_force == 0 && verify_on()) return gemm_verified(h, p);
-        const int rc = gemm_tma_launch(h, p, h->gemm_force ? h->gemm_force : 10);
+        const int rc = gemm_tma_launch(h, p, h->gemm_force ? h->gemm_force : (p.M <= 32 ? 11 : 10));
         if (rc != 1) return rc;                 // 1: no tensor map for these operands, nothing launched
     }
     if (h->gemm_force == 2) return dispatch_layout<1, 4, 3, 8>(h, p);

@@ -330,13 +330,15 @@ bool gemm_tma_applicable(const GemmParams& p)
 
 // returns 1 when a tensor map could not be encoded (nothing launched): gemm_launch falls back to dgemm_kernel.
 // form: 7 = 64x128 CTA tile (2x4 consumer warps, 2 CTAs per SM), 8 = 128x64 (4x2), 9 = 128x128 (4x4, one CTA per SM),
-// 10 = 64x64 (2x2, 3 CTAs per SM)
+// 10 = 64x64 (2x2, 3 CTAs per SM), 11 = 32x128 (1x4, 3 stages, 3 CTAs per SM: products with M <= 32, e.g. the
+// row blocks of the panel sweep)
 int gemm_tma_launch(isdf_handle* h, const GemmParams& p, int form)
 {
     switch (form) {
     case 8: return dispatch_tma<4, 2, 4>(h, p);
     case 9: return dispatch_tma<4, 4, 4>(h, p);
     case 10: return dispatch_tma<2, 2, 4>(h, p);
+    case 11: return dispatch_tma<1, 4, 3>(h, p);
     default: return dispatch_tma<2, 4, 4>(h, p);
     }
 }

@@ -738,18 +738,22 @@ __global__ void mark_selected_kernel(const long long* __restrict__ ip_dev, int k
 // unchanged (ascending column index), so the bits are those of the one-point form.
 constexpr int SWEEP_PT = 2;
 __global__ void __launch_bounds__(128)
-panel_sweep_kernel(double* __restrict__ Ltp, long long ldl, long long ng, int nb,
+panel_sweep_kernel(double* __restrict__ Ltp, long long ldl, long long ng, int row0, int nb,
                    const double* __restrict__ LppP, const double* __restrict__ resid,
                    double* __restrict__ d)
 {
+    // Rows row0 .. row0 + nb of the panel: the terms of the earlier rows j < row0 have already been subtracted
+    // (by the GEMM of isdf_select_flush, in ascending j), the chain of every entry continues here with
+    // j = row0, row0 + 1, ...: same order, same bits as one sweep over the whole panel.
     constexpr int PT = SWEEP_PT;
-    extern __shared__ double s_l[];            // packed lower triangle, then nb pivots
+    extern __shared__ double s_l[];            // packed lower triangle of the window, then nb pivots
     double* s_piv = s_l + NB * (NB + 1) / 2;
+    Ltp += (long long)row0 * ldl;
     for (int i = threadIdx.x; i < nb * nb; i += blockDim.x) {
         const int k = i / nb, j = i - k * nb;
-        if (j < k) s_l[k * (k + 1) / 2 + j] = LppP[k * NB + j];
+        if (j < k) s_l[k * (k + 1) / 2 + j] = LppP[(row0 + k) * NB + row0 + j];
     }
-    for (int i = threadIdx.x; i < nb; i += blockDim.x) s_piv[i] = sqrt(resid[i]);
+    for (int i = threadIdx.x; i < nb; i += blockDim.x) s_piv[i] = sqrt(resid[row0 + i]);
     __syncthreads();
     const long long g0 = (long long)blockIdx.x * (blockDim.x * PT) + threadIdx.x;
     if (g0 >= ng) return;
@@ -972,6 +976,18 @@ extern "C" int isdf_select_candidates(isdf_select_plan* pl, const double* phi, l
     return ISDF_OK;
 }
 
+// rows per block of the panel sweep (ISDF_SWEEP_BLOCK: 16 .. 128, a multiple of 16; 128 = one scalar sweep)
+static int sweep_block()
+{
+    static const int v = [] {
+        const char* e = getenv("ISDF_SWEEP_BLOCK");
+        int b = e ? atoi(e) : 32;
+        if (b < 16 || b > NB || (b & 15)) b = 32;
+        return b;
+    }();
+    return v;
+}
+
 static int gemm_kc(isdf_handle* h, int M, int N, int K, const double* A, long long lda,
                    const double* B, long long ldb, int b_kmajor, double* C, long long ldc,
                    const double* Cin, int neg, int epi, int upper_only = 0)
@@ -1121,11 +1137,23 @@ extern "C" int isdf_select_flush(isdf_select_plan* pl, const double* phi, long l
     if ((rc = gemm_kc(h, nb, (int)ngl, pl->nao, w.PivRows + META, rl, phi, ldphi, 1, Ltp, ldl, nullptr, 0, EPI_SQUARE))) return rc;
     if (k0 > 0)
         if ((rc = gemm_kc(h, nb, (int)ngl, k0, w.PivRows + META + naop, rl, Lt, ldl, 1, Ltp, ldl, Ltp, 1, EPI_STORE))) return rc;
-    panel_sweep_kernel<<<(unsigned)((ngl + 128 * SWEEP_PT - 1) / (128 * SWEEP_PT)), 128, sweep_smem, s>>>(
-        Ltp, ldl, ngl, nb, w.LppP, w.resid_dev + k0, w.d);
+    // Triangular sweep over the panel's own columns, in row blocks: the part of a block's chains that runs over
+    // earlier blocks is a product with the panel factor -- on the FP64 tensor pipe, in place, ascending column
+    // index -- and only the block's own triangle goes through the scalar kernel (a quarter of the FMAs at 32
+    // rows per block).  Every entry's chain keeps its order: flush columns, earlier blocks, own block.
+    const int bs = sweep_block();
+    for (int r0 = 0; r0 < nb; r0 += bs) {
+        const int nr = nb - r0 < bs ? nb - r0 : bs;
+        if (r0 > 0)
+            if ((rc = gemm_kc(h, nr, (int)ngl, r0, w.LppP + (long long)r0 * NB, NB, Ltp, ldl, 1,
+                              Ltp + (long long)r0 * ldl, ldl, Ltp + (long long)r0 * ldl, 1, EPI_STORE))) return rc;
+        panel_sweep_kernel<<<(unsigned)((ngl + 128 * SWEEP_PT - 1) / (128 * SWEEP_PT)), 128, sweep_smem, s>>>(
+            Ltp, ldl, ngl, r0, nr, w.LppP, w.resid_dev + k0, w.d);
+        h->other_launches++;
+    }
     mark_selected_kernel<<<1, NB, 0, s>>>(w.ip_dev, k0, nb, pl->g_offset, ngl, w.d);
     CUDA_TRY(cudaGetLastError());
-    h->other_launches += 2;
+    h->other_launches += 1;
     return ISDF_OK;
 }
 

@@ -50,10 +50,10 @@ def test_gemm_big_tile_and_epilogues(handle):
     assert np.array_equal(got, ref)
 
 
-@pytest.mark.parametrize('form', [7, 8, 9, 10])
+@pytest.mark.parametrize('form', [7, 8, 9, 10, 11])
 def test_gemm_tma_forms_bit_exact(handle, form):
     """The warp-specialised GEMM fed by 2-D tensor-map TMA (csrc/gemm_tma.cu; CTA tiles 64x128, 128x64,
-    128x128, 64x64): the oracle's FMA chain bit for bit, every layout, ragged M / N / K (the TMA unit's
+    128x128, 64x64, 32x128): the oracle's FMA chain bit for bit, every layout, ragged M / N / K (the TMA unit's
     out-of-bounds zero fill), accumulator init, epilogues; leading dimensions even so that TMA can address them."""
     handle.set_gemm_tile(form)
     try:

@@ -16,7 +16,7 @@ def main():
     g = torch.Generator(device=dev); g.manual_seed(1)
     rnd = lambda *s: torch.rand(*s, dtype=torch.float64, device=dev, generator=g) - 0.5
     shapes = [(128, 300, 64), (70, 131, 37), (257, 66, 16), (33, 1000, 130), (64, 64, 1), (200, 200, 203)]
-    bad = {f: 0 for f in (0, 7, 8, 9, 10)}
+    bad = {f: 0 for f in (0, 7, 8, 9, 10, 11)}
     n = 0
     for (M, N, K), ak, bk, neg, cin, epi, upper in itertools.product(
             shapes, (0, 1), (0, 1), (0, 1), (False, True), (0, 1, 2), (0, 1)):
@@ -28,7 +28,7 @@ def main():
         Cin = rnd(M, N + 2 + (N & 1))
         E = rnd(M, N + 2 + (N & 1))
         outs = {}
-        for form in (4, 0, 7, 8, 9, 10):
+        for form in (4, 0, 7, 8, 9, 10, 11):
             h.set_gemm_tile(form)
             C = torch.full((M, N + 4 + (N & 1)), 7.0, dtype=torch.float64, device=dev)
             h.dgemm(M, N, K, A, A.shape[1], ak, B, B.shape[1], bk, C, C.shape[1],
@@ -57,7 +57,7 @@ def main():
         B = Lt if bk else rnd(N, K + 2)
         C0 = rnd(M, ld)
         ref = None
-        for form in (4, 0, 0, 0, 7, 8, 9, 10, 10, 10):
+        for form in (4, 0, 0, 0, 7, 8, 9, 10, 10, 10, 11, 11):
             h.set_gemm_tile(form)
             C = Lt[K:] if bk else torch.empty(M, ld, dtype=torch.float64, device=dev)
             C.copy_(C0)
