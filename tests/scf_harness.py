@@ -97,3 +97,41 @@ def rks_gamma(hcore, ovlp, nelec, enuc, get_j, nr_rks, conv_tol=1e-10, max_cycle
                 pass
         dm = density(f)
     raise RuntimeError('SCF not converged')
+
+
+def krks_kmesh(hcore_k, ovlp_k, nelec_cell, enuc_cell, get_j, nr_rks, conv_tol=1e-10, max_cycle=40):
+    """Restricted Kohn-Sham on a k-point mesh (the caller of the plugin in pyscf/pbc/dft/krks.py, pyscf/pbc/scf/khf.py:
+    get_occ fills the lowest nelec/2 * nk orbitals over all k-points; energies per unit cell, k-averaged).
+    hcore_k, ovlp_k: [nk, nao, nao] hermitian; get_j(dm_k) -> vj_k; nr_rks(dm_k) -> (nelec, exc, vxc_k) per cell.
+    Plain Roothaan iteration with 50 % damping after the first cycle (small symmetric test systems).
+    Returns (e_tot per cell, dm_k, ncycle)."""
+    nk = len(hcore_k)
+    nocc_total = nelec_cell * nk // 2
+
+    def density(f_k):
+        es, cs = [], []
+        for k in range(nk):
+            e, c = scipy.linalg.eigh(f_k[k], ovlp_k[k])
+            es.append(e)
+            cs.append(c)
+        order = np.argsort(np.concatenate(es), kind='stable')[:nocc_total]
+        nao = hcore_k.shape[1]
+        dm = np.zeros_like(hcore_k, dtype=np.complex128)
+        for idx in order:
+            k, i = divmod(int(idx), nao)
+            dm[k] += 2 * np.outer(cs[k][:, i], cs[k][:, i].conj())
+        return dm
+
+    dm = density(hcore_k)
+    e_last = None
+    for it in range(max_cycle):
+        vj = get_j(dm)
+        _, exc, vxc = nr_rks(dm)
+        f = hcore_k + vj + vxc
+        e_tot = (np.einsum('kij,kji->', dm, hcore_k) + 0.5 * np.einsum('kij,kji->', dm, vj)).real / nk + exc + enuc_cell
+        if e_last is not None and abs(e_tot - e_last) < conv_tol:
+            return e_tot, dm, it + 1
+        e_last = e_tot
+        new = density(f)
+        dm = new if it == 0 else 0.5 * (dm + new)
+    raise RuntimeError('k-mesh SCF not converged')

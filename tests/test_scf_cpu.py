@@ -164,3 +164,56 @@ def test_rhf_energy_of_diamond_with_pseudopotential_reproduces_the_reference():
     e = rhf_gamma(hcore, S, cell.nelectron, cell.ewald(),
                   lambda dm: oracle.fftdf_get_jk(ao4[0], dm, a, mesh, exxdiv='ewald', ovlp=S, madelung=mad))[0]
     assert abs(e - E_RHF_C2_PRIMITIVE) < 1e-8
+
+
+# ---------------------------------------------------------------------------
+# k-point mesh: the reference's KRKS number through the supercell equivalence (pyscf_isdf_b200/kmesh.py)
+# ---------------------------------------------------------------------------
+E_KLDA_H2_KPTS_221 = -0.3846075202893169      # pyscf/pbc/dft/test/test_krks.py:83-88 (KRKS 'lda,vwn', kpts 2x2x1)
+
+
+def h2_kmesh_fixture():
+    """Cell and k-points of test_krks.py:84-86 (all-electron H2, one s Gaussian each, default mesh)."""
+    cell = Cell(atom='H 0 0 0; H 1 0 0', a=np.eye(3) * 2, basis=[[0, [1, 1]]], pseudo=None).build()
+    return cell, cell.make_kpts([2, 2, 1])
+
+
+def test_kmesh_lda_energy_through_the_supercell_reproduces_the_reference():
+    """The reference's k-point Kohn-Sham energy on a Gamma-centred 2 x 2 x 1 mesh, two ways, both through the
+    2 x 2 x 1 supercell on the mesh kmesh * cell.mesh with the oracle's pieces: (i) a Gamma-point SCF of the supercell,
+    energy per cell; (ii) a k-space SCF (tests/scf_harness.krks_kmesh) whose h, S, J and Vxc are the supercell's
+    matrices folded to the k-points with the product's own Bloch transformations -- the stand-ins of what
+    ISDF.get_nuc / get_j / nr_rks return on a k-mesh (tests/test_zz_kmesh_gpu.py swaps the device results in).
+    Observed: 8e-12 Ha from the reference's number (it asserts 7 places)."""
+    from oracle import xc
+    from scf_harness import rks_gamma, krks_kmesh
+    from pyscf_isdf_b200.kmesh import KMesh
+    cell, kpts = h2_kmesh_fixture()
+    assert list(cell.mesh) == [19, 19, 19]
+    km = KMesh(cell, kpts)
+    sc = km.supercell
+    nk = km.nk
+    a, mesh = sc.lattice_vectors(), sc.mesh
+    S, T = int1e.overlap_kinetic(a, sc._atm, sc._bas, sc._env)
+    rcut, Ls = sc.ao_eval_params()
+    ao4 = oracle.eval_ao(sc._atm, sc._bas, sc._env, sc.get_uniform_grids(), Ls, rcut, deriv=1)
+    charges = [float(z) for z in sc.atom_charges()]
+    vne = opp.potential_matrix(ao4[0], opp.nuc_on_grid(a, mesh, sc.atom_coords(), charges))
+    w = sc.vol / ao4.shape[1]
+    e_sc, _, _ = rks_gamma(T + vne, S, sc.nelectron, sc.ewald(),
+                           lambda dm: oracle.fftdf_get_j(ao4[0], dm, a, mesh),
+                           lambda dm: xc.nr_rks(ao4, w, 'lda,vwn', dm))
+    assert abs(e_sc / nk - E_KLDA_H2_KPTS_221) < 1e-8, e_sc / nk - E_KLDA_H2_KPTS_221
+
+    def get_j(dm_k):
+        d = km.dm_to_supercell(dm_k)
+        vj = oracle.fftdf_get_j(ao4[0], np.stack([d.real, d.imag]), a, mesh)
+        return km.mat_to_kpts(vj[0] + 1j * vj[1])
+
+    def nr_rks(dm_k):
+        ne, exc, v = xc.nr_rks(ao4, w, 'lda,vwn', np.ascontiguousarray(km.dm_to_supercell(dm_k).real))
+        return ne / nk, exc / nk, km.mat_to_kpts(v)
+
+    e_k, dm_k, ncyc = krks_kmesh(km.mat_to_kpts(T + vne), km.mat_to_kpts(S), cell.nelectron, cell.ewald(), get_j, nr_rks)
+    assert abs(e_k - E_KLDA_H2_KPTS_221) < 1e-8, e_k - E_KLDA_H2_KPTS_221
+    assert abs(np.einsum('kij,kji->', dm_k, km.mat_to_kpts(S)).real / nk - cell.nelectron) < 1e-10

@@ -114,3 +114,25 @@ def test_kmesh_hcore_and_xc_match_the_kpoint_oracle():
     for k in range(3):
         mat = ao[k][0].conj().T.dot(np.einsum('npi,np->pi', ao[k], wv))
         assert abs(vmat[k] - (mat + mat.conj().T)).max() < 1e-8
+
+
+def test_kmesh_lda_energy_on_the_device_reproduces_the_reference():
+    """KRKS 'lda,vwn' on the reference's 2 x 2 x 1 mesh (pyscf/pbc/dft/test/test_krks.py:83-88: -0.3846075202893169 Ha)
+    with every plugin call on the device path: ISDF.get_nuc, get_j (exact-density route) and nr_rks at the k-points,
+    each served by the supercell and folded back; kinetic and overlap matrices from the oracle's integrals folded
+    the same way (they belong to the SCF driver's side).  The CPU twin with oracle stand-ins is
+    tests/test_scf_cpu.py::test_kmesh_lda_energy_through_the_supercell_reproduces_the_reference."""
+    from oracle import int1e
+    from scf_harness import krks_kmesh
+    from test_scf_cpu import h2_kmesh_fixture, E_KLDA_H2_KPTS_221
+    cell, kpts = h2_kmesh_fixture()
+    mydf = ISDF(cell, kpts=kpts, exact_j=True)
+    mydf.check_sanity()
+    km = mydf._kmesh
+    sc = km.supercell
+    S, T = int1e.overlap_kinetic(sc.lattice_vectors(), sc._atm, sc._bas, sc._env)
+    hcore_k = km.mat_to_kpts(T) + mydf.get_nuc(kpts)
+    e, dm_k, ncyc = krks_kmesh(hcore_k, km.mat_to_kpts(S), cell.nelectron, cell.ewald(),
+                               lambda dm: mydf.get_j(dm, kpts=kpts),
+                               lambda dm: mydf.nr_rks('lda,vwn', dm, kpts))
+    assert abs(e - E_KLDA_H2_KPTS_221) < 1e-7, e - E_KLDA_H2_KPTS_221
